@@ -1,0 +1,133 @@
+// extern "C" boundary of libefgp_b200 (see include/efgp_b200.h).
+#include "../../include/efgp_b200.h"
+#include "toeplitz.cuh"
+
+namespace efgp {
+static thread_local std::string g_last_error;
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+}  // namespace efgp
+
+struct efgp_nufft {
+  efgp::Nufft nu;
+};
+struct efgp_toeplitz {
+  efgp::Toeplitz t;
+};
+
+#define EFGP_TRY(body)                                  \
+  try {                                                 \
+    body;                                               \
+    return 0;                                           \
+  } catch (const efgp::Error& e) {                      \
+    efgp::set_last_error(e.what());                     \
+    return e.code;                                      \
+  } catch (const std::exception& e) {                   \
+    efgp::set_last_error(e.what());                     \
+    return 99;                                          \
+  }
+
+extern "C" {
+
+int efgp_version(void) { return 100; }
+
+const char* efgp_last_error(void) { return efgp::g_last_error.c_str(); }
+
+int efgp_nufft_create(efgp_nufft** out, int dim, int dtype) {
+  EFGP_TRY({
+    EFGP_CHECK(out != nullptr, "null output handle");
+    EFGP_CHECK(dim >= 1 && dim <= efgp::kMaxDim, "dim must be 1, 2 or 3");
+    EFGP_CHECK(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    efgp_nufft* h = new efgp_nufft();
+    h->nu.dim = dim;
+    h->nu.dtype = dtype;
+    *out = h;
+  })
+}
+
+int efgp_nufft_set_points(efgp_nufft* nu, const void* x, int64_t npts, double h, const double* xcen,
+                          void* stream) {
+  (void)stream;
+  EFGP_TRY({
+    EFGP_CHECK(nu != nullptr, "null handle");
+    EFGP_CHECK(npts >= 0, "npts must be >= 0");
+    EFGP_CHECK(npts == 0 || x != nullptr, "null points");
+    nu->nu.x = x;
+    nu->nu.N = npts;
+    nu->nu.h = h;
+    for (int a = 0; a < efgp::kMaxDim; ++a) nu->nu.xcen[a] = (xcen && a < nu->nu.dim) ? xcen[a] : 0.0;
+    nu->nu.sorted.clear();
+  })
+}
+
+void efgp_nufft_destroy(efgp_nufft* nu) { delete nu; }
+
+int efgp_nufft_type1(efgp_nufft* nu, const void* strengths, int is_complex, int batch,
+                     const int64_t* out_shape, double eps, int isign, int modeord, const void* scale,
+                     void* out, void* stream) {
+  EFGP_TRY({
+    EFGP_CHECK(nu != nullptr && out != nullptr && out_shape != nullptr, "null argument");
+    efgp::nufft_type1(nu->nu, strengths, is_complex, batch, out_shape, eps, isign, modeord, scale, out,
+                      (cudaStream_t)stream);
+  })
+}
+
+int efgp_nufft_type2(efgp_nufft* nu, const void* modes, int batch, const int64_t* shape, double eps,
+                     int isign, int modeord, const void* scale, int real_out, void* out, void* stream) {
+  EFGP_TRY({
+    EFGP_CHECK(nu != nullptr && modes != nullptr && shape != nullptr, "null argument");
+    EFGP_CHECK(nu->nu.N == 0 || out != nullptr, "null output");
+    efgp::nufft_type2(nu->nu, modes, batch, shape, eps, isign, modeord, scale, real_out, out,
+                      (cudaStream_t)stream);
+  })
+}
+
+int efgp_nufft_plan_info(efgp_nufft* nu, const int64_t* shape, double eps, int64_t* nf_out, int* width_out) {
+  EFGP_TRY({
+    EFGP_CHECK(nu != nullptr && shape != nullptr, "null argument");
+    if (nu->nu.dtype == 0 && eps < 1e-7) eps = 1e-7;
+    int w0 = efgp::es_width_for(eps, 2.0, efgp::kMaxW);
+    for (int a = 0; a < nu->nu.dim; ++a)
+      if (nf_out) nf_out[a] = efgp::next_smooth_even(std::max<int64_t>(2 * shape[a], 2 * w0));
+    if (width_out) *width_out = w0;
+  })
+}
+
+int efgp_toeplitz_create(efgp_toeplitz** out, const void* v, int dim, const int64_t* Ls, int dtype,
+                         int force_pow2, void* stream) {
+  EFGP_TRY({
+    EFGP_CHECK(out != nullptr && v != nullptr && Ls != nullptr, "null argument");
+    EFGP_CHECK(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    std::unique_ptr<efgp_toeplitz> h(new efgp_toeplitz());
+    efgp::toeplitz_create(h->t, v, dim, Ls, dtype, force_pow2, (cudaStream_t)stream);
+    *out = h.release();
+  })
+}
+
+void efgp_toeplitz_destroy(efgp_toeplitz* t) { delete t; }
+
+int efgp_toeplitz_fft_shape(efgp_toeplitz* t, int64_t* shape_out) {
+  EFGP_TRY({
+    EFGP_CHECK(t != nullptr && shape_out != nullptr, "null argument");
+    for (int a = 0; a < t->t.dim; ++a) shape_out[a] = t->t.F[a];
+  })
+}
+
+int efgp_toeplitz_apply(efgp_toeplitz* t, const void* x, int batch, const void* ws, double sigmasq,
+                        int mode, void* y, void* stream) {
+  EFGP_TRY({
+    EFGP_CHECK(t != nullptr && x != nullptr && y != nullptr, "null argument");
+    efgp::toeplitz_apply(t->t, x, batch, ws, sigmasq, mode, y, (cudaStream_t)stream);
+  })
+}
+
+int efgp_cg_solve(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, const void* minv,
+                  const void* b, void* x, int batch, double tol, int max_iter, int early_stopping,
+                  int batched_semantics, int* iters_completed, void* stream) {
+  EFGP_TRY({
+    EFGP_CHECK(t != nullptr && b != nullptr && x != nullptr, "null argument");
+    efgp::cg_solve(t->t, ws, sigmasq, mode, minv, b, x, batch, tol, max_iter, early_stopping,
+                   batched_semantics, iters_completed, (cudaStream_t)stream);
+  })
+}
+
+}  // extern "C"

@@ -1,0 +1,172 @@
+// Host-side construction of the spreading kernel: width/beta selection, piecewise-polynomial
+// fit (Chebyshev interpolation -> monomials in s=2u), and its Fourier transform by
+// Gauss-Legendre quadrature (the deconvolution factors).
+//
+// The reference delegates all of this to FINUFFT (efgpnd.py:1496-1499, 1533-1549); only the
+// eps contract is observable, so width, beta and upsampling are this library's own choices.
+#include "common.cuh"
+#include <cmath>
+#include <algorithm>
+
+namespace efgp {
+
+static const double kPi = 3.14159265358979323846264338327950288;
+
+int64_t next_pow2(int64_t n) {
+  int64_t p = 1;
+  while (p < n) p <<= 1;
+  return p;
+}
+
+static bool is_smooth(int64_t n) {
+  for (int p : {2, 3, 5}) while (n % p == 0) n /= p;
+  return n == 1;
+}
+int64_t next_smooth(int64_t n) {
+  if (n < 1) n = 1;
+  while (!is_smooth(n)) ++n;
+  return n;
+}
+int64_t next_smooth_even(int64_t n) {
+  if (n < 2) n = 2;
+  if (n & 1) ++n;
+  while (!is_smooth(n)) n += 2;
+  return n;
+}
+
+int es_width_for(double eps, double sigma, int max_w) {
+  if (eps < 1e-15) eps = 1e-15;
+  if (sigma < 1.2) sigma = 1.2;
+  // kernel aliasing error ~ exp(-pi W sqrt(1-1/sigma)); one extra point of margin
+  int w = (int)std::ceil(-std::log(eps) / (kPi * std::sqrt(1.0 - 1.0 / sigma))) + 1;
+  w = std::max(w, 2);
+  w = std::min(w, max_w);
+  return w;
+}
+
+static inline double es_phi(double beta, double z) {
+  double a = 1.0 - z * z;
+  if (a < 0) a = 0;  // rounding at the support edge
+  return std::exp(beta * (std::sqrt(a) - 1.0));
+}
+
+double es_eval_exact(const ESKernel& k, double z) {
+  if (std::fabs(z) > 1.0) return 0.0;
+  return es_phi(k.beta, z);
+}
+
+// Chebyshev interpolation of f on s in [-1,1] with n+1 nodes, returned as monomial coefficients.
+static void cheb_fit_monomial(int n, const std::vector<double>& fvals /* at nodes */, double* mono) {
+  // Chebyshev coefficients c_j, f ~ sum' c_j T_j(s)
+  std::vector<long double> c(n + 1, 0.0L);
+  for (int j = 0; j <= n; ++j) {
+    long double acc = 0;
+    for (int m = 0; m <= n; ++m)
+      acc += (long double)fvals[m] * cosl((long double)kPi * j * (m + 0.5L) / (n + 1));
+    c[j] = acc * 2.0L / (n + 1);
+  }
+  c[0] *= 0.5L;
+  // T_j in monomials by recurrence
+  std::vector<long double> Tm2(n + 1, 0.0L), Tm1(n + 1, 0.0L), T(n + 1, 0.0L), out(n + 1, 0.0L);
+  Tm2[0] = 1.0L;  // T0
+  for (int q = 0; q <= n; ++q) out[q] += c[0] * Tm2[q];
+  if (n >= 1) {
+    Tm1[1] = 1.0L;  // T1
+    for (int q = 0; q <= n; ++q) out[q] += c[1] * Tm1[q];
+  }
+  for (int j = 2; j <= n; ++j) {
+    std::fill(T.begin(), T.end(), 0.0L);
+    for (int q = 0; q < n; ++q) T[q + 1] += 2.0L * Tm1[q];
+    for (int q = 0; q <= n; ++q) T[q] -= Tm2[q];
+    for (int q = 0; q <= n; ++q) out[q] += c[j] * T[q];
+    Tm2 = Tm1;
+    Tm1 = T;
+  }
+  for (int q = 0; q <= n; ++q) mono[q] = (double)out[q];
+}
+
+void es_build(ESKernel& k, int W, double sigma, double target_err) {
+  EFGP_CHECK(W >= 2 && W <= kMaxW, "spreading width out of range");
+  k.W = W;
+  if (sigma < 1.2) sigma = 1.2;
+  if (sigma > 4.0) sigma = 4.0;  // beta saturates: wider upsampling only helps
+  k.beta = 0.97 * kPi * W * (1.0 - 1.0 / (2.0 * sigma));
+  const int nhalf = (W + 1) / 2;
+  const double halfW = 0.5 * W;
+  std::memset(k.coef, 0, sizeof(k.coef));
+  // Degree is tied to the width (W+2): the device Horner loops are unrolled at compile time.
+  // Beyond ~W+1 the fit error plateaus at ~0.4*exp(-beta) (sqrt edge singularity), i.e. below eps.
+  (void)target_err;
+  int deg = std::min(W + 2, kMaxDeg);
+  double err = 0;
+  for (; deg <= std::min(W + 2, kMaxDeg); ++deg) {
+    err = 0;
+    for (int i = 0; i < nhalf; ++i) {
+      std::vector<double> fv(deg + 1);
+      for (int m = 0; m <= deg; ++m) {
+        double s = std::cos(kPi * (m + 0.5) / (deg + 1));  // node in [-1,1]; u = s/2
+        double z = (i - 0.5 * (W - 1) - 0.5 * s) / halfW;
+        fv[m] = es_phi(k.beta, z);
+      }
+      double mono[kMaxDeg + 1] = {0};
+      cheb_fit_monomial(deg, fv, mono);
+      for (int j = 0; j <= kMaxDeg; ++j) k.coef[i][j] = (j <= deg) ? mono[j] : 0.0;
+      for (int t = 0; t <= 64; ++t) {
+        double s = -1.0 + 2.0 * t / 64.0;
+        double z = (i - 0.5 * (W - 1) - 0.5 * s) / halfW;
+        double p = 0;
+        for (int j = deg; j >= 0; --j) p = p * s + mono[j];
+        err = std::max(err, std::fabs(p - es_phi(k.beta, z)));
+      }
+    }
+  }
+  deg = std::min(W + 2, kMaxDeg);
+  k.deg = deg;
+  k.fit_err = err;
+}
+
+// Gauss-Legendre nodes/weights on [-1,1]
+static void gauss_legendre(int n, std::vector<double>& x, std::vector<double>& w) {
+  x.resize(n);
+  w.resize(n);
+  for (int i = 0; i < (n + 1) / 2; ++i) {
+    long double z = cosl((long double)kPi * (i + 0.75L) / (n + 0.5L));
+    long double pp = 0;
+    for (int it = 0; it < 100; ++it) {
+      long double p1 = 1.0L, p2 = 0.0L;
+      for (int j = 0; j < n; ++j) {
+        long double p3 = p2;
+        p2 = p1;
+        p1 = ((2.0L * j + 1.0L) * z * p2 - j * p3) / (j + 1.0L);
+      }
+      pp = n * (z * p1 - p2) / (z * z - 1.0L);
+      long double dz = p1 / pp;
+      z -= dz;
+      if (fabsl(dz) < 1e-19L) break;
+    }
+    x[i] = (double)(-z);
+    x[n - 1 - i] = (double)z;
+    w[i] = w[n - 1 - i] = (double)(2.0L / ((1.0L - z * z) * pp * pp));
+  }
+}
+
+void es_fourier_series(const ESKernel& k, int64_t nf, int64_t kmax, std::vector<double>& out) {
+  // psi_hat(xi) = (W/2) * int_{-1}^{1} phi(s) cos(pi W xi s) ds,  xi = k/nf
+  const int nq = 128;
+  std::vector<double> gx, gw;
+  gauss_legendre(nq, gx, gw);
+  std::vector<double> s(nq / 2), f(nq / 2);
+  for (int q = 0; q < nq / 2; ++q) {
+    s[q] = gx[nq / 2 + q];  // positive half; integrand even
+    f[q] = 2.0 * gw[nq / 2 + q] * es_phi(k.beta, s[q]);
+  }
+  out.resize(kmax + 1);
+  for (int64_t kk = 0; kk <= kmax; ++kk) {
+    double xi = (double)kk / (double)nf;
+    double acc = 0;
+    for (int q = 0; q < nq / 2; ++q) acc += f[q] * std::cos(kPi * k.W * xi * s[q]);
+    out[kk] = 0.5 * k.W * acc;
+  }
+}
+
+}  // namespace efgp

@@ -1,0 +1,247 @@
+// Type-2 interpolation: real fine grid -> values at bin-sorted nonuniform points.
+//
+// This is the arithmetic FINUFFT performs inside pff.finufft_type2 (reference call sites
+// efgpnd.py:1533-1536, 1546-1549, 1679); the algorithm here is this library's own.
+//
+// Mirror image of spread.cu: a thread walks a contiguous slice of the cell-sorted points and
+// keeps the W x W patch of fine-grid values it needs in REGISTERS, reloading it (through the
+// read-only path; the whole fine grid lives in L2) only when the cell changes.  Per point the
+// work is the kernel evaluation plus W^2 FMAs, and one scattered store of the result.
+#include "nufft.cuh"
+
+namespace efgp {
+
+template <typename T, int W>
+__device__ __forceinline__ void es_eval_i(const ESDev<T>& es, T s, T* __restrict__ k) {
+  constexpr int DEG = W + 2;
+  constexpr int NE = DEG / 2 + 1;
+  constexpr int NO = (DEG + 1) / 2;
+  const T v = s * s;
+#pragma unroll
+  for (int i = 0; i < W / 2; ++i) {
+    T e = es.c[i][2 * (NE - 1)];
+#pragma unroll
+    for (int j = NE - 2; j >= 0; --j) e = fma(e, v, es.c[i][2 * j]);
+    T o = es.c[i][2 * NO - 1];
+#pragma unroll
+    for (int j = NO - 2; j >= 0; --j) o = fma(o, v, es.c[i][2 * j + 1]);
+    o *= s;
+    k[i] = e + o;
+    k[W - 1 - i] = e - o;
+  }
+  if (W & 1) {
+    constexpr int i = W / 2;
+    T e = es.c[i][2 * (NE - 1)];
+#pragma unroll
+    for (int j = NE - 2; j >= 0; --j) e = fma(e, v, es.c[i][2 * j]);
+    k[i] = e;
+  }
+}
+
+__device__ __forceinline__ int wrap_i(int i, int n) {
+  if (i < 0) i += n;
+  if (i >= n) i -= n;
+  return i;
+}
+
+template <typename T, int W>
+__global__ void __launch_bounds__(256)
+interp1d_kernel(const T* __restrict__ xs0, const uint32_t* __restrict__ perm, int64_t N, int P, int nf0,
+                const T* __restrict__ grid, T* __restrict__ out, int64_t ostride,
+                const __grid_constant__ ESDev<T> es) {
+  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t s = tid * P, e = s + P < N ? s + P : N;
+  if (s >= N) return;
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  T g[W];
+  int cur = -1;
+  for (int64_t n = s; n < e; ++n) {
+    T X = xs0[n];
+    int c0 = (int)X;
+    if (c0 != cur) {
+#pragma unroll
+      for (int i = 0; i < W; ++i) g[i] = __ldg(grid + wrap_i(c0 - OFF + i, nf0));
+      cur = c0;
+    }
+    T k0[W];
+    es_eval_i<T, W>(es, T(2) * (X - (T)c0) - T(1), k0);
+    T acc = 0;
+#pragma unroll
+    for (int i = 0; i < W; ++i) acc = fma(g[i], k0[i], acc);
+    out[(int64_t)perm[n] * ostride] = acc;
+  }
+}
+
+template <typename T, int W>
+__global__ void __launch_bounds__(256, 1)
+interp2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const uint32_t* __restrict__ perm,
+                int64_t N, int P, int nf0, int nf1, const T* __restrict__ grid, T* __restrict__ out,
+                int64_t ostride, const __grid_constant__ ESDev<T> es) {
+  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t s = tid * P, e = s + P < N ? s + P : N;
+  if (s >= N) return;
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  T g[W][W];
+  int cur0 = -1, cur1 = -1;
+  T X0 = xs0[s], X1 = xs1[s];
+  uint32_t pn = perm[s];
+  for (int64_t n = s; n < e; ++n) {
+    T nX0 = X0, nX1 = X1;
+    uint32_t npn = pn;
+    if (n + 1 < e) {
+      nX0 = xs0[n + 1];
+      nX1 = xs1[n + 1];
+      npn = perm[n + 1];
+    }
+    int c0 = (int)X0, c1 = (int)X1;
+    if (c0 != cur0 || c1 != cur1) {
+      int cols[W];
+#pragma unroll
+      for (int j = 0; j < W; ++j) cols[j] = wrap_i(c1 - OFF + j, nf1);
+#pragma unroll
+      for (int i = 0; i < W; ++i) {
+        const T* row = grid + (int64_t)wrap_i(c0 - OFF + i, nf0) * nf1;
+#pragma unroll
+        for (int j = 0; j < W; ++j) g[i][j] = __ldg(row + cols[j]);
+      }
+      cur0 = c0;
+      cur1 = c1;
+    }
+    T k0[W], k1[W];
+    es_eval_i<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
+    es_eval_i<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
+    T acc = 0;
+#pragma unroll
+    for (int i = 0; i < W; ++i) {
+      T r = 0;
+#pragma unroll
+      for (int j = 0; j < W; ++j) r = fma(g[i][j], k1[j], r);
+      acc = fma(r, k0[i], acc);
+    }
+    out[(int64_t)pn * ostride] = acc;
+    X0 = nX0;
+    X1 = nX1;
+    pn = npn;
+  }
+}
+
+// generic: wide 2-D kernels and 3-D, one point per thread, gathers through L1/L2
+template <typename T, int W, int D>
+__global__ void __launch_bounds__(256)
+interp_direct_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* __restrict__ xs2,
+                     const uint32_t* __restrict__ perm, int64_t N, int nf0, int nf1, int nf2,
+                     const T* __restrict__ grid, T* __restrict__ out, int64_t ostride,
+                     const __grid_constant__ ESDev<T> es) {
+  int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  T k0[W], k1[W], k2[W];
+  T X0 = xs0[n];
+  int c0 = (int)X0;
+  es_eval_i<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
+  T X1 = xs1[n];
+  int c1 = (int)X1;
+  es_eval_i<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
+  int c2 = 0;
+  if (D == 3) {
+    T X2 = xs2[n];
+    c2 = (int)X2;
+    es_eval_i<T, W>(es, T(2) * (X2 - (T)c2) - T(1), k2);
+  }
+  T acc = 0;
+  if (D == 2) {
+#pragma unroll
+    for (int i = 0; i < W; ++i) {
+      const T* row = grid + (int64_t)wrap_i(c0 - OFF + i, nf0) * nf1;
+      T r = 0;
+#pragma unroll
+      for (int j = 0; j < W; ++j) r = fma(__ldg(row + wrap_i(c1 - OFF + j, nf1)), k1[j], r);
+      acc = fma(r, k0[i], acc);
+    }
+  } else {
+    int cols[W];
+#pragma unroll
+    for (int l = 0; l < W; ++l) cols[l] = wrap_i(c2 - OFF + l, nf2);
+#pragma unroll 1
+    for (int i = 0; i < W; ++i) {
+      int64_t r0 = (int64_t)wrap_i(c0 - OFF + i, nf0) * nf1;
+      T ri = 0;
+#pragma unroll 1
+      for (int j = 0; j < W; ++j) {
+        const T* row = grid + (r0 + wrap_i(c1 - OFF + j, nf1)) * nf2;
+        T r = 0;
+#pragma unroll
+        for (int l = 0; l < W; ++l) r = fma(__ldg(row + cols[l]), k2[l], r);
+        ri = fma(r, k1[j], ri);
+      }
+      acc = fma(ri, k0[i], acc);
+    }
+  }
+  out[(int64_t)perm[n] * ostride] = acc;
+}
+
+static int pick_ppt(int64_t N) {
+  int64_t P = N / (148 * 256 * 4);
+  if (P < 1) P = 1;
+  if (P > 64) P = 64;
+  return (int)P;
+}
+
+template <typename T, int W>
+static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* grid, T* out, int64_t ostride,
+                     cudaStream_t st) {
+  ESDev<T> es;
+  es_to_dev<T>(k, es);
+  const int64_t N = sp.N;
+  const T* x0 = (const T*)sp.xs[0];
+  const T* x1 = (const T*)sp.xs[1];
+  const T* x2 = (const T*)sp.xs[2];
+  constexpr int kRegMaxW = sizeof(T) == 8 ? 9 : 10;
+  if (sp.dim == 1) {
+    int P = pick_ppt(N);
+    interp1d_kernel<T, W><<<div_up(div_up(N, P), 256), 256, 0, st>>>(x0, sp.perm, N, P, (int)sp.nf[0], grid, out,
+                                                                     ostride, es);
+  } else if (sp.dim == 2) {
+    if constexpr (W <= kRegMaxW) {
+      int P = pick_ppt(N);
+      interp2d_kernel<T, W><<<div_up(div_up(N, P), 256), 256, 0, st>>>(x0, x1, sp.perm, N, P, (int)sp.nf[0],
+                                                                       (int)sp.nf[1], grid, out, ostride, es);
+    } else {
+      interp_direct_kernel<T, W, 2><<<div_up(N, 256), 256, 0, st>>>(x0, x1, x2, sp.perm, N, (int)sp.nf[0],
+                                                                    (int)sp.nf[1], 1, grid, out, ostride, es);
+    }
+  } else {
+    interp_direct_kernel<T, W, 3><<<div_up(N, 256), 256, 0, st>>>(x0, x1, x2, sp.perm, N, (int)sp.nf[0],
+                                                                  (int)sp.nf[1], (int)sp.nf[2], grid, out, ostride,
+                                                                  es);
+  }
+  EFGP_CUDA(cudaGetLastError());
+}
+
+template <typename T>
+static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* grid, T* out, int64_t ostride,
+                     cudaStream_t st) {
+  switch (k.W) {
+#define EFGP_CASE(w) \
+  case w:            \
+    launch_w<T, w>(sp, k, grid, out, ostride, st); \
+    break;
+    EFGP_CASE(2) EFGP_CASE(3) EFGP_CASE(4) EFGP_CASE(5) EFGP_CASE(6) EFGP_CASE(7) EFGP_CASE(8) EFGP_CASE(9)
+    EFGP_CASE(10) EFGP_CASE(11) EFGP_CASE(12) EFGP_CASE(13) EFGP_CASE(14) EFGP_CASE(15) EFGP_CASE(16)
+#undef EFGP_CASE
+    default:
+      throw Error(1, "unsupported interpolation width");
+  }
+}
+
+void launch_interp(const SortedPoints& sp, const ESKernel& k, const void* grid, void* out, int64_t ostride,
+                   cudaStream_t st) {
+  if (sp.N == 0) return;
+  EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
+  if (sp.dtype == 0)
+    launch_t<float>(sp, k, (const float*)grid, (float*)out, ostride, st);
+  else
+    launch_t<double>(sp, k, (const double*)grid, (double*)out, ostride, st);
+}
+
+}  // namespace efgp

@@ -1,0 +1,429 @@
+// NUFFT plans: type-1 (nonuniform -> modes) and type-2 (modes -> nonuniform) built from the
+// spread / interp kernels, cuFFT real<->complex transforms on the fine grid, and fused
+// deconvolve+crop(+spectral-weight) / pre-correct+pad(+spectral-weight) kernels.
+//
+// Replaces pff.finufft_type1 / finufft_type2 as used by efgpnd.py:1496-1499 (isign=-1,
+// centred modes), :1533-1549 (isign=+1) and :1679 (modeord=True).  Mode conventions follow
+// those call sites: per axis k = -(n//2) .. (n-1)//2, C-order, or FFT order when modeord != 0.
+//
+// All spreading is done with REAL strengths on a REAL fine grid (complex strengths are two real
+// transforms; complex type-2 outputs are the transforms of the Hermitian and anti-Hermitian parts
+// of the mode array), so every FFT is R2C/C2R on half the data of a complex transform.
+#include "nufft.cuh"
+#include <cmath>
+#include <algorithm>
+
+namespace efgp {
+
+// ------------------------------------------------------------------ cuFFT plan cache
+cufftHandle FftCache::get(int dim, const int64_t* n, cufftType type, int batch, cudaStream_t st) {
+  FftPlanKey key;
+  key.dim = dim;
+  key.type = (int)type;
+  key.batch = batch;
+  for (int a = 0; a < kMaxDim; ++a) key.n[a] = a < dim ? n[a] : 1;
+  auto it = plans.find(key);
+  cufftHandle h;
+  if (it == plans.end()) {
+    if (plans.size() > 24) {  // bound the cache
+      for (auto& kv : plans) cufftDestroy(kv.second);
+      plans.clear();
+    }
+    EFGP_CUFFT(cufftCreate(&h));
+    EFGP_CUFFT(cufftSetAutoAllocation(h, 0));
+    long long nn[kMaxDim];
+    for (int a = 0; a < dim; ++a) nn[a] = n[a];
+    size_t ws = 0;
+    EFGP_CUFFT(cufftMakePlanMany64(h, dim, nn, nullptr, 1, 0, nullptr, 1, 0, type, batch, &ws));
+    plans[key] = h;
+    work_bytes = std::max(work_bytes, ws);
+  } else {
+    h = it->second;
+  }
+  size_t ws = 0;
+  EFGP_CUFFT(cufftGetSize(h, &ws));
+  EFGP_CUFFT(cufftSetWorkArea(h, work.get(std::max<size_t>(ws, 256))));
+  EFGP_CUFFT(cufftSetStream(h, st));
+  return h;
+}
+FftCache::~FftCache() {
+  for (auto& kv : plans) cufftDestroy(kv.second);
+}
+
+// ------------------------------------------------------------------ mode bookkeeping
+struct ModeGeom {
+  int dim;
+  int n[kMaxDim];       // modes per axis
+  int nf[kMaxDim];      // fine grid per axis
+  int nh;               // nf[last]/2+1
+  int modeord;
+  int flip;             // 1: look up / place at -k
+  int64_t M;            // prod n
+};
+
+__device__ __forceinline__ int signed_mode(int idx, int n, int modeord) {
+  if (modeord) return idx <= (n - 1) / 2 ? idx : idx - n;
+  return idx - n / 2;
+}
+__device__ __forceinline__ int mode_index(int k, int n, int modeord) {  // inverse of signed_mode, -1 if absent
+  if (k < -(n / 2) || k > (n - 1) / 2) return -1;
+  if (modeord) return k >= 0 ? k : k + n;
+  return k + n / 2;
+}
+
+// out[b, idx] = (spec_re[b] (+ i spec_im[b]))[k mod nf] / prod_a psihat_a(k_a) * scale[idx]
+template <typename T>
+__global__ void __launch_bounds__(256)
+deconv_kernel(const typename cplx_of<T>::type* __restrict__ spec, int ncomp, int batch, ModeGeom g,
+              const T* __restrict__ dinv0, const T* __restrict__ dinv1, const T* __restrict__ dinv2,
+              const T* __restrict__ scale, typename cplx_of<T>::type* __restrict__ out) {
+  using C = typename cplx_of<T>::type;
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= g.M * batch) return;
+  int64_t idx = t % g.M;
+  int b = (int)(t / g.M);
+  int id[kMaxDim] = {0, 0, 0};
+  {
+    int64_t r = idx;
+    for (int a = g.dim - 1; a >= 0; --a) {
+      id[a] = (int)(r % g.n[a]);
+      r /= g.n[a];
+    }
+  }
+  const T* dinv[kMaxDim] = {dinv0, dinv1, dinv2};
+  int q[kMaxDim] = {0, 0, 0};
+  T f = T(1);
+  for (int a = 0; a < g.dim; ++a) {
+    int k = signed_mode(id[a], g.n[a], g.modeord);
+    f *= dinv[a][k < 0 ? -k : k];
+    if (g.flip) k = -k;
+    q[a] = k < 0 ? k + g.nf[a] : k;
+  }
+  if (scale) f *= scale[idx];
+  const int last = g.dim - 1;
+  bool conj = q[last] >= g.nh;
+  if (conj)
+    for (int a = 0; a < g.dim; ++a) q[a] = q[a] == 0 ? 0 : g.nf[a] - q[a];
+  int64_t off = 0;
+  int64_t slab = 1;
+  for (int a = 0; a < g.dim; ++a) {
+    int ext = a == last ? g.nh : g.nf[a];
+    off = off * ext + q[a];
+    slab *= ext;
+  }
+  C v = spec[(int64_t)(b * ncomp) * slab + off];
+  T re = v.x, im = conj ? -v.y : v.y;
+  if (ncomp == 2) {
+    C w = spec[(int64_t)(b * ncomp + 1) * slab + off];
+    T wr = w.x, wi = conj ? -w.y : w.y;
+    re -= wi;  // (vr + i vi) + i (wr + i wi)
+    im += wr;
+  }
+  C o;
+  o.x = re * f;
+  o.y = im * f;
+  out[t] = o;
+}
+
+// Half-spectrum of the fine grid for a real-output type-2: comp 0 -> Hermitian part of the scaled,
+// pre-corrected modes; comp 1 -> (f[k] - conj f[-k]) / (2i).  Writes every entry (zero padding).
+template <typename T>
+__global__ void __launch_bounds__(256)
+precorrect_kernel(const typename cplx_of<T>::type* __restrict__ modes, int ncomp, int batch, ModeGeom g,
+                  const T* __restrict__ dinv0, const T* __restrict__ dinv1, const T* __restrict__ dinv2,
+                  const T* __restrict__ scale, typename cplx_of<T>::type* __restrict__ spec) {
+  using C = typename cplx_of<T>::type;
+  int64_t slab = 1;
+  const int last = g.dim - 1;
+  for (int a = 0; a < g.dim; ++a) slab *= (a == last ? g.nh : g.nf[a]);
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= slab * batch * ncomp) return;
+  int64_t off = t % slab;
+  int bc = (int)(t / slab);
+  int b = bc / ncomp, comp = bc % ncomp;
+  int q[kMaxDim] = {0, 0, 0};
+  {
+    int64_t r = off;
+    for (int a = g.dim - 1; a >= 0; --a) {
+      int ext = a == last ? g.nh : g.nf[a];
+      q[a] = (int)(r % ext);
+      r /= ext;
+    }
+  }
+  const T* dinv[kMaxDim] = {dinv0, dinv1, dinv2};
+  T f = T(1);
+  int64_t ip = 0, im = 0;  // flat indices of +k and -k in the mode array
+  bool has_p = true, has_m = true;
+  bool in_range = true;
+  for (int a = 0; a < g.dim; ++a) {
+    int k = q[a] <= g.nf[a] / 2 ? q[a] : q[a] - g.nf[a];
+    if (2 * q[a] == g.nf[a] && g.n[a] > 0) {
+      // Nyquist bin of the fine grid: only reachable if n == nf, which never happens (nf >= 2n)
+    }
+    if (g.flip) k = -k;
+    int ka = k < 0 ? -k : k;
+    if (ka > g.n[a] / 2) {
+      in_range = false;
+      break;
+    }
+    f *= dinv[a][ka];
+    int jp = mode_index(k, g.n[a], g.modeord);
+    int jm = mode_index(-k, g.n[a], g.modeord);
+    if (jp < 0) has_p = false;
+    if (jm < 0) has_m = false;
+    ip = ip * g.n[a] + (jp < 0 ? 0 : jp);
+    im = im * g.n[a] + (jm < 0 ? 0 : jm);
+  }
+  C o;
+  o.x = 0;
+  o.y = 0;
+  if (in_range && (has_p || has_m)) {
+    T pr = 0, pi = 0, mr = 0, mi = 0;
+    if (has_p) {
+      C v = modes[(int64_t)b * g.M + ip];
+      T s = scale ? scale[ip] : T(1);
+      pr = v.x * s;
+      pi = v.y * s;
+    }
+    if (has_m) {
+      C v = modes[(int64_t)b * g.M + im];
+      T s = scale ? scale[im] : T(1);
+      mr = v.x * s;
+      mi = v.y * s;
+    }
+    if (comp == 0) {  // (p + conj m)/2
+      o.x = T(0.5) * (pr + mr) * f;
+      o.y = T(0.5) * (pi - mi) * f;
+    } else {  // (p - conj m)/(2i) = ((pi + mi) - i (pr - mr))/2
+      o.x = T(0.5) * (pi + mi) * f;
+      o.y = -T(0.5) * (pr - mr) * f;
+    }
+  }
+  spec[t] = o;
+}
+
+// ------------------------------------------------------------------ plan selection
+struct GridChoice {
+  int64_t nf[kMaxDim];
+  ESKernel ker;
+  SortedPoints* sp;
+};
+
+static void upload_dinv(Nufft& nu, const ESKernel& ker, const int64_t* nf, const int64_t* n, int dim, int dtype,
+                        void* dptr[kMaxDim], cudaStream_t st) {
+  // dinv_a[k] = 1/psihat(k/nf_a), k = 0..n_a/2 ; all axes packed into nu.dec
+  size_t esz = dtype == 0 ? 4 : 8;
+  size_t total = 0;
+  for (int a = 0; a < dim; ++a) total += (size_t)(n[a] / 2 + 1);
+  char* base = (char*)nu.dec.get(total * esz);
+  std::vector<double> host;
+  std::vector<float> hostf;
+  size_t pos = 0;
+  std::vector<double> all(total);
+  for (int a = 0; a < dim; ++a) {
+    es_fourier_series(ker, nf[a], n[a] / 2, host);
+    for (size_t k = 0; k < host.size(); ++k) all[pos + k] = 1.0 / host[k];
+    dptr[a] = base + pos * esz;
+    pos += host.size();
+  }
+  for (int a = dim; a < kMaxDim; ++a) dptr[a] = base;
+  if (dtype == 0) {
+    hostf.assign(all.begin(), all.end());
+    EFGP_CUDA(cudaMemcpyAsync(base, hostf.data(), total * 4, cudaMemcpyHostToDevice, st));
+  } else {
+    EFGP_CUDA(cudaMemcpyAsync(base, all.data(), total * 8, cudaMemcpyHostToDevice, st));
+  }
+  EFGP_CUDA(cudaStreamSynchronize(st));  // host vectors go out of scope
+}
+
+static SortedPoints* get_sorted(Nufft& nu, const int64_t* nf, int odd, cudaStream_t st) {
+  for (auto& sp : nu.sorted) {
+    bool same = sp->odd == odd;
+    for (int a = 0; a < nu.dim; ++a) same = same && sp->nf[a] == nf[a];
+    if (same) {
+      sp->last_use = ++nu.clock;
+      return sp.get();
+    }
+  }
+  if (nu.sorted.size() >= 3) {  // evict least recently used
+    size_t j = 0;
+    for (size_t i = 1; i < nu.sorted.size(); ++i)
+      if (nu.sorted[i]->last_use < nu.sorted[j]->last_use) j = i;
+    nu.sorted.erase(nu.sorted.begin() + j);
+  }
+  std::unique_ptr<SortedPoints> sp(new SortedPoints());
+  build_sorted_points(*sp, nu.x, nu.N, nu.dim, nu.dtype, nu.h, nu.xcen, nf, odd, st);
+  sp->last_use = ++nu.clock;
+  nu.sorted.push_back(std::move(sp));
+  return nu.sorted.back().get();
+}
+
+// Pick the fine grid, kernel and sorted point set for `n` modes at tolerance eps.  An existing
+// sorted set on a finer grid is reused when possible (larger effective upsampling -> narrower
+// kernel, and no second sort): this is how the F*y transform shares the Toeplitz-vector grid.
+static GridChoice choose_grid(Nufft& nu, const int64_t* n, double eps, cudaStream_t st) {
+  GridChoice gc;
+  const int max_w = kMaxW;
+  if (nu.dtype == 0 && eps < 1e-7) eps = 1e-7;  // single precision floor
+  int w0 = es_width_for(eps, 2.0, max_w);
+  int64_t own[kMaxDim] = {1, 1, 1};
+  double own_cells = 1;
+  for (int a = 0; a < nu.dim; ++a) {
+    own[a] = next_smooth_even(std::max<int64_t>(2 * n[a], 2 * w0));
+    own_cells *= (double)own[a];
+  }
+  SortedPoints* best = nullptr;
+  for (auto& sp : nu.sorted) {
+    bool ok = true;
+    double cells = 1;
+    for (int a = 0; a < nu.dim; ++a) {
+      ok = ok && sp->nf[a] >= own[a];
+      cells *= (double)sp->nf[a];
+    }
+    if (!ok) continue;
+    if (cells > std::max(16.0 * own_cells, (double)nu.N)) continue;
+    if (!best) best = sp.get();
+  }
+  if (best) {
+    double sigma = 1e30;
+    for (int a = 0; a < nu.dim; ++a) sigma = std::min(sigma, (double)best->nf[a] / (double)n[a]);
+    int w = es_width_for(eps, std::min(sigma, 4.0), max_w);
+    if ((w & 1) != best->odd) ++w;
+    bool fits = w <= max_w;
+    for (int a = 0; a < nu.dim; ++a) fits = fits && best->nf[a] >= 2 * w;
+    if (fits) {
+      for (int a = 0; a < kMaxDim; ++a) gc.nf[a] = best->nf[a];
+      es_build(gc.ker, w, std::min(sigma, 4.0), 0);
+      best->last_use = ++nu.clock;
+      gc.sp = best;
+      return gc;
+    }
+  }
+  double sigma = 1e30;
+  for (int a = 0; a < nu.dim; ++a) sigma = std::min(sigma, (double)own[a] / (double)n[a]);
+  int w = es_width_for(eps, std::min(sigma, 4.0), max_w);
+  for (int a = 0; a < kMaxDim; ++a) gc.nf[a] = own[a];
+  es_build(gc.ker, w, std::min(sigma, 4.0), 0);
+  gc.sp = get_sorted(nu, gc.nf, w & 1, st);
+  return gc;
+}
+
+static ModeGeom make_geom(int dim, const int64_t* n, const int64_t* nf, int modeord, int flip) {
+  ModeGeom g;
+  g.dim = dim;
+  g.M = 1;
+  for (int a = 0; a < kMaxDim; ++a) {
+    g.n[a] = a < dim ? (int)n[a] : 1;
+    g.nf[a] = a < dim ? (int)nf[a] : 1;
+    if (a < dim) g.M *= n[a];
+  }
+  g.nh = g.nf[dim - 1] / 2 + 1;
+  g.modeord = modeord;
+  g.flip = flip;
+  return g;
+}
+
+template <typename T>
+static void type1_t(Nufft& nu, const void* strengths, int is_complex, int batch, const int64_t* n, double eps,
+                    int isign, int modeord, const void* scale, void* out, cudaStream_t st) {
+  using C = typename cplx_of<T>::type;
+  const int dim = nu.dim;
+  GridChoice gc = choose_grid(nu, n, eps, st);
+  ModeGeom g = make_geom(dim, n, gc.nf, modeord, isign > 0 ? 1 : 0);
+  void* dinv[kMaxDim];
+  upload_dinv(nu, gc.ker, gc.nf, n, dim, nu.dtype, dinv, st);
+  int64_t cells = 1, slab = 1;
+  for (int a = 0; a < dim; ++a) {
+    cells *= gc.nf[a];
+    slab *= (a == dim - 1 ? gc.nf[a] / 2 + 1 : gc.nf[a]);
+  }
+  const int ncomp = is_complex ? 2 : 1;
+  // chunk the batch so the fine grids stay under ~8 GB
+  int64_t per = (int64_t)ncomp * (cells * sizeof(T) + slab * sizeof(C));
+  int chunk = (int)std::max<int64_t>(1, std::min<int64_t>(batch, (8ll << 30) / std::max<int64_t>(per, 1)));
+  T* fine = (T*)nu.fine.get((size_t)chunk * ncomp * cells * sizeof(T));
+  C* spec = (C*)nu.spec.get((size_t)chunk * ncomp * slab * sizeof(C));
+  for (int b0 = 0; b0 < batch; b0 += chunk) {
+    int nb = std::min(chunk, batch - b0);
+    EFGP_CUDA(cudaMemsetAsync(fine, 0, (size_t)nb * ncomp * cells * sizeof(T), st));
+    for (int b = 0; b < nb; ++b) {
+      for (int comp = 0; comp < ncomp; ++comp) {
+        const T* c = nullptr;
+        if (strengths) c = (const T*)strengths + (int64_t)(b0 + b) * nu.N * ncomp + comp;
+        launch_spread(*gc.sp, gc.ker, c, ncomp, fine + (int64_t)(b * ncomp + comp) * cells, st);
+      }
+    }
+    cufftHandle plan = nu.fft.get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_R2C : CUFFT_D2Z, nb * ncomp, st);
+    if (sizeof(T) == 4)
+      EFGP_CUFFT(cufftExecR2C(plan, (cufftReal*)fine, (cufftComplex*)spec));
+    else
+      EFGP_CUFFT(cufftExecD2Z(plan, (cufftDoubleReal*)fine, (cufftDoubleComplex*)spec));
+    int64_t tot = g.M * nb;
+    deconv_kernel<T><<<div_up(tot, 256), 256, 0, st>>>(spec, ncomp, nb, g, (const T*)dinv[0], (const T*)dinv[1],
+                                                       (const T*)dinv[2], (const T*)scale,
+                                                       (C*)out + (int64_t)b0 * g.M);
+    EFGP_CUDA(cudaGetLastError());
+  }
+}
+
+template <typename T>
+static void type2_t(Nufft& nu, const void* modes, int batch, const int64_t* n, double eps, int isign,
+                    int modeord, const void* scale, int real_out, void* out, cudaStream_t st) {
+  using C = typename cplx_of<T>::type;
+  const int dim = nu.dim;
+  GridChoice gc = choose_grid(nu, n, eps, st);
+  // cuFFT's inverse is e^{+i}: isign > 0 places mode k at +k, isign < 0 at -k
+  ModeGeom g = make_geom(dim, n, gc.nf, modeord, isign > 0 ? 0 : 1);
+  void* dinv[kMaxDim];
+  upload_dinv(nu, gc.ker, gc.nf, n, dim, nu.dtype, dinv, st);
+  int64_t cells = 1, slab = 1;
+  for (int a = 0; a < dim; ++a) {
+    cells *= gc.nf[a];
+    slab *= (a == dim - 1 ? gc.nf[a] / 2 + 1 : gc.nf[a]);
+  }
+  const int ncomp = real_out ? 1 : 2;
+  int64_t per = (int64_t)ncomp * (cells * sizeof(T) + slab * sizeof(C));
+  int chunk = (int)std::max<int64_t>(1, std::min<int64_t>(batch, (8ll << 30) / std::max<int64_t>(per, 1)));
+  T* fine = (T*)nu.fine.get((size_t)chunk * ncomp * cells * sizeof(T));
+  C* spec = (C*)nu.spec.get((size_t)chunk * ncomp * slab * sizeof(C));
+  for (int b0 = 0; b0 < batch; b0 += chunk) {
+    int nb = std::min(chunk, batch - b0);
+    int64_t tot = slab * nb * ncomp;
+    precorrect_kernel<T><<<div_up(tot, 256), 256, 0, st>>>((const C*)modes + (int64_t)b0 * g.M, ncomp, nb, g,
+                                                           (const T*)dinv[0], (const T*)dinv[1],
+                                                           (const T*)dinv[2], (const T*)scale, spec);
+    EFGP_CUDA(cudaGetLastError());
+    cufftHandle plan = nu.fft.get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_C2R : CUFFT_Z2D, nb * ncomp, st);
+    if (sizeof(T) == 4)
+      EFGP_CUFFT(cufftExecC2R(plan, (cufftComplex*)spec, (cufftReal*)fine));
+    else
+      EFGP_CUFFT(cufftExecZ2D(plan, (cufftDoubleComplex*)spec, (cufftDoubleReal*)fine));
+    for (int b = 0; b < nb; ++b)
+      for (int comp = 0; comp < ncomp; ++comp)
+        launch_interp(*gc.sp, gc.ker, fine + (int64_t)(b * ncomp + comp) * cells,
+                      (T*)out + (int64_t)(b0 + b) * nu.N * ncomp + comp, ncomp, st);
+  }
+}
+
+void nufft_type1(Nufft& nu, const void* strengths, int is_complex, int batch, const int64_t* n, double eps,
+                 int isign, int modeord, const void* scale, void* out, cudaStream_t st) {
+  EFGP_CHECK(batch >= 1, "batch must be >= 1");
+  for (int a = 0; a < nu.dim; ++a) EFGP_CHECK(n[a] >= 1, "mode counts must be >= 1");
+  if (nu.dtype == 0)
+    type1_t<float>(nu, strengths, is_complex, batch, n, eps, isign, modeord, scale, out, st);
+  else
+    type1_t<double>(nu, strengths, is_complex, batch, n, eps, isign, modeord, scale, out, st);
+}
+
+void nufft_type2(Nufft& nu, const void* modes, int batch, const int64_t* n, double eps, int isign, int modeord,
+                 const void* scale, int real_out, void* out, cudaStream_t st) {
+  EFGP_CHECK(batch >= 1, "batch must be >= 1");
+  for (int a = 0; a < nu.dim; ++a) EFGP_CHECK(n[a] >= 1, "mode counts must be >= 1");
+  if (nu.N == 0) return;
+  if (nu.dtype == 0)
+    type2_t<float>(nu, modes, batch, n, eps, isign, modeord, scale, real_out, out, st);
+  else
+    type2_t<double>(nu, modes, batch, n, eps, isign, modeord, scale, real_out, out, st);
+}
+
+}  // namespace efgp

@@ -1,0 +1,285 @@
+// Type-1 spreading: real strengths at bin-sorted nonuniform points -> real fine grid.
+//
+// This is the arithmetic FINUFFT performs inside pff.finufft_type1 (reference call site
+// efgpnd.py:1496-1499); the algorithm here is this library's own.
+//
+// Design (B200): points are sorted by fine-grid cell, so long runs of consecutive points share
+// one W^d footprint.  Each thread walks a contiguous slice of the sorted points and keeps the
+// footprint's partial sums in REGISTERS (W*W doubles for d=2), so a point costs only the
+// piecewise-polynomial kernel evaluation plus W^d FMAs -- no shared-memory or global atomics in
+// the inner loop (sm_100a has no native shared fp atomics: ATOMS.CAST.SPIN loops).  Only when the
+// cell changes (or the slice ends) is the footprint flushed with native REDG.ADD.F64/F32 into
+// the L2-resident fine grid.  EFGP grids are tiny next to N (e.g. 282^2 cells for 1e8 points),
+// so flushes are ~1/100 of the FMA work at the headline size and degrade gracefully to one
+// flush per point for sparse cases.
+#include "nufft.cuh"
+
+namespace efgp {
+
+template <typename T, int W>
+__device__ __forceinline__ void es_eval(const ESDev<T>& es, T s, T* __restrict__ k) {
+  constexpr int DEG = W + 2;
+  constexpr int NE = DEG / 2 + 1;    // even coefficients 0,2,..
+  constexpr int NO = (DEG + 1) / 2;  // odd coefficients 1,3,..
+  const T v = s * s;
+#pragma unroll
+  for (int i = 0; i < W / 2; ++i) {
+    T e = es.c[i][2 * (NE - 1)];
+#pragma unroll
+    for (int j = NE - 2; j >= 0; --j) e = fma(e, v, es.c[i][2 * j]);
+    T o = es.c[i][2 * NO - 1];
+#pragma unroll
+    for (int j = NO - 2; j >= 0; --j) o = fma(o, v, es.c[i][2 * j + 1]);
+    o *= s;
+    k[i] = e + o;
+    k[W - 1 - i] = e - o;
+  }
+  if (W & 1) {
+    constexpr int i = W / 2;
+    T e = es.c[i][2 * (NE - 1)];
+#pragma unroll
+    for (int j = NE - 2; j >= 0; --j) e = fma(e, v, es.c[i][2 * j]);
+    k[i] = e;
+  }
+}
+
+__device__ __forceinline__ int wrap_idx(int i, int n) {
+  if (i < 0) i += n;
+  if (i >= n) i -= n;
+  return i;
+}
+
+// ------------------------------------------------------------------ 1-D
+template <typename T, int W, bool HAS_C>
+__global__ void __launch_bounds__(256)
+spread1d_kernel(const T* __restrict__ xs0, const uint32_t* __restrict__ perm, const T* __restrict__ c,
+                int64_t cstride, int64_t N, int P, int nf0, T* __restrict__ grid,
+                const __grid_constant__ ESDev<T> es) {
+  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t s = tid * P, e = s + P < N ? s + P : N;
+  if (s >= N) return;
+  T acc[W];
+#pragma unroll
+  for (int i = 0; i < W; ++i) acc[i] = 0;
+  int cur = -1;
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  for (int64_t n = s; n < e; ++n) {
+    T X = xs0[n];
+    T cv = HAS_C ? c[(int64_t)perm[n] * cstride] : T(1);
+    int c0 = (int)X;
+    if (c0 != cur) {
+      if (cur >= 0) {
+#pragma unroll
+        for (int i = 0; i < W; ++i) atomicAdd(&grid[wrap_idx(cur - OFF + i, nf0)], acc[i]);
+      }
+#pragma unroll
+      for (int i = 0; i < W; ++i) acc[i] = 0;
+      cur = c0;
+    }
+    T k0[W];
+    es_eval<T, W>(es, T(2) * (X - (T)c0) - T(1), k0);
+#pragma unroll
+    for (int i = 0; i < W; ++i) acc[i] = fma(cv, k0[i], acc[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < W; ++i) atomicAdd(&grid[wrap_idx(cur - OFF + i, nf0)], acc[i]);
+}
+
+// ------------------------------------------------------------------ 2-D, register footprint
+template <typename T, int W>
+__device__ __forceinline__ void flush2d(T (&acc)[W][W], int c0, int c1, int nf0, int nf1, T* __restrict__ grid) {
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  int cols[W];
+#pragma unroll
+  for (int j = 0; j < W; ++j) cols[j] = wrap_idx(c1 - OFF + j, nf1);
+#pragma unroll
+  for (int i = 0; i < W; ++i) {
+    T* row = grid + (int64_t)wrap_idx(c0 - OFF + i, nf0) * nf1;
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+      atomicAdd(row + cols[j], acc[i][j]);
+      acc[i][j] = 0;
+    }
+  }
+}
+
+template <typename T, int W, bool HAS_C>
+__global__ void __launch_bounds__(256, 1)
+spread2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const uint32_t* __restrict__ perm,
+                const T* __restrict__ c, int64_t cstride, int64_t N, int P, int nf0, int nf1,
+                T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
+  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t s = tid * P, e = s + P < N ? s + P : N;
+  if (s >= N) return;
+  T acc[W][W];
+#pragma unroll
+  for (int i = 0; i < W; ++i)
+#pragma unroll
+    for (int j = 0; j < W; ++j) acc[i][j] = 0;
+  int cur0 = -1, cur1 = -1;
+  // software prefetch of the next point
+  T X0 = xs0[s], X1 = xs1[s];
+  T cv = HAS_C ? c[(int64_t)perm[s] * cstride] : T(1);
+  for (int64_t n = s; n < e; ++n) {
+    T nX0 = X0, nX1 = X1, ncv = cv;
+    if (n + 1 < e) {
+      nX0 = xs0[n + 1];
+      nX1 = xs1[n + 1];
+      if (HAS_C) ncv = c[(int64_t)perm[n + 1] * cstride];
+    }
+    int c0 = (int)X0, c1 = (int)X1;
+    if (c0 != cur0 || c1 != cur1) {
+      if (cur0 >= 0) flush2d<T, W>(acc, cur0, cur1, nf0, nf1, grid);
+      cur0 = c0;
+      cur1 = c1;
+    }
+    T k0[W], k1[W];
+    es_eval<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
+    es_eval<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
+#pragma unroll
+    for (int i = 0; i < W; ++i) {
+      T a = cv * k0[i];
+#pragma unroll
+      for (int j = 0; j < W; ++j) acc[i][j] = fma(a, k1[j], acc[i][j]);
+    }
+    X0 = nX0;
+    X1 = nX1;
+    cv = ncv;
+  }
+  flush2d<T, W>(acc, cur0, cur1, nf0, nf1, grid);
+}
+
+// ------------------------------------------------------------------ generic d (2-D wide kernels, 3-D): per-point REDs
+// Points are still cell-sorted, so the reductions of neighbouring threads land in the same L2 lines.
+template <typename T, int W, int D, bool HAS_C>
+__global__ void __launch_bounds__(256)
+spread_direct_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* __restrict__ xs2,
+                     const uint32_t* __restrict__ perm, const T* __restrict__ c, int64_t cstride, int64_t N,
+                     int nf0, int nf1, int nf2, T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
+  int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  T cv = HAS_C ? c[(int64_t)perm[n] * cstride] : T(1);
+  T k0[W], k1[W], k2[W];
+  T X0 = xs0[n];
+  int c0 = (int)X0;
+  es_eval<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
+  T X1 = xs1[n];
+  int c1 = (int)X1;
+  es_eval<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
+  int c2 = 0;
+  if (D == 3) {
+    T X2 = xs2[n];
+    c2 = (int)X2;
+    es_eval<T, W>(es, T(2) * (X2 - (T)c2) - T(1), k2);
+  }
+  if (D == 2) {
+#pragma unroll
+    for (int i = 0; i < W; ++i) {
+      T* row = grid + (int64_t)wrap_idx(c0 - OFF + i, nf0) * nf1;
+      T a = cv * k0[i];
+#pragma unroll
+      for (int j = 0; j < W; ++j) atomicAdd(row + wrap_idx(c1 - OFF + j, nf1), a * k1[j]);
+    }
+  } else {
+    int cols[W];
+#pragma unroll
+    for (int l = 0; l < W; ++l) cols[l] = wrap_idx(c2 - OFF + l, nf2);
+#pragma unroll 1
+    for (int i = 0; i < W; ++i) {
+      int64_t r0 = (int64_t)wrap_idx(c0 - OFF + i, nf0) * nf1;
+      T a = cv * k0[i];
+#pragma unroll 1
+      for (int j = 0; j < W; ++j) {
+        T* row = grid + (r0 + wrap_idx(c1 - OFF + j, nf1)) * nf2;
+        T b = a * k1[j];
+#pragma unroll
+        for (int l = 0; l < W; ++l) atomicAdd(row + cols[l], b * k2[l]);
+      }
+    }
+  }
+}
+
+static int pick_points_per_thread(int64_t N) {
+  // aim for >= 2 full waves of 148 SMs x 256 threads, and long register runs when N is large
+  int64_t P = N / (148 * 256 * 4);
+  if (P < 1) P = 1;
+  if (P > 64) P = 64;
+  return (int)P;
+}
+
+template <typename T, int W>
+static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* c, int64_t cstride, T* grid,
+                     cudaStream_t st) {
+  ESDev<T> es;
+  es_to_dev<T>(k, es);
+  const int64_t N = sp.N;
+  const T* x0 = (const T*)sp.xs[0];
+  const T* x1 = (const T*)sp.xs[1];
+  const T* x2 = (const T*)sp.xs[2];
+  constexpr int kRegMaxW = sizeof(T) == 8 ? 9 : 10;
+  if (sp.dim == 1) {
+    int P = pick_points_per_thread(N);
+    int nb = div_up(div_up(N, P), 256);
+    if (c)
+      spread1d_kernel<T, W, true><<<nb, 256, 0, st>>>(x0, sp.perm, c, cstride, N, P, (int)sp.nf[0], grid, es);
+    else
+      spread1d_kernel<T, W, false><<<nb, 256, 0, st>>>(x0, sp.perm, c, cstride, N, P, (int)sp.nf[0], grid, es);
+  } else if (sp.dim == 2) {
+    if constexpr (W <= kRegMaxW) {
+      int P = pick_points_per_thread(N);
+      int nb = div_up(div_up(N, P), 256);
+      if (c)
+        spread2d_kernel<T, W, true>
+            <<<nb, 256, 0, st>>>(x0, x1, sp.perm, c, cstride, N, P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
+      else
+        spread2d_kernel<T, W, false>
+            <<<nb, 256, 0, st>>>(x0, x1, sp.perm, c, cstride, N, P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
+    } else {
+      int nb = div_up(N, 256);
+      if (c)
+        spread_direct_kernel<T, W, 2, true><<<nb, 256, 0, st>>>(x0, x1, x2, sp.perm, c, cstride, N, (int)sp.nf[0],
+                                                                (int)sp.nf[1], 1, grid, es);
+      else
+        spread_direct_kernel<T, W, 2, false><<<nb, 256, 0, st>>>(x0, x1, x2, sp.perm, c, cstride, N,
+                                                                 (int)sp.nf[0], (int)sp.nf[1], 1, grid, es);
+    }
+  } else {
+    int nb = div_up(N, 256);
+    if (c)
+      spread_direct_kernel<T, W, 3, true><<<nb, 256, 0, st>>>(x0, x1, x2, sp.perm, c, cstride, N, (int)sp.nf[0],
+                                                              (int)sp.nf[1], (int)sp.nf[2], grid, es);
+    else
+      spread_direct_kernel<T, W, 3, false><<<nb, 256, 0, st>>>(x0, x1, x2, sp.perm, c, cstride, N, (int)sp.nf[0],
+                                                               (int)sp.nf[1], (int)sp.nf[2], grid, es);
+  }
+  EFGP_CUDA(cudaGetLastError());
+}
+
+template <typename T>
+static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* c, int64_t cstride, T* grid,
+                     cudaStream_t st) {
+  switch (k.W) {
+#define EFGP_CASE(w) \
+  case w:            \
+    launch_w<T, w>(sp, k, c, cstride, grid, st); \
+    break;
+    EFGP_CASE(2) EFGP_CASE(3) EFGP_CASE(4) EFGP_CASE(5) EFGP_CASE(6) EFGP_CASE(7) EFGP_CASE(8) EFGP_CASE(9)
+    EFGP_CASE(10) EFGP_CASE(11) EFGP_CASE(12) EFGP_CASE(13) EFGP_CASE(14) EFGP_CASE(15) EFGP_CASE(16)
+#undef EFGP_CASE
+    default:
+      throw Error(1, "unsupported spreading width");
+  }
+}
+
+void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* c, int64_t cstride, void* grid,
+                   cudaStream_t st) {
+  if (sp.N == 0) return;
+  EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
+  if (sp.dtype == 0)
+    launch_t<float>(sp, k, (const float*)c, cstride, (float*)grid, st);
+  else
+    launch_t<double>(sp, k, (const double*)c, cstride, (double*)grid, st);
+}
+
+}  // namespace efgp

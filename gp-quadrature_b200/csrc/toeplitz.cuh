@@ -1,0 +1,32 @@
+// Toeplitz (F^H F) operator and lockstep batched CG -- internal declarations.
+#pragma once
+#include "nufft.cuh"
+
+namespace efgp {
+
+struct Toeplitz {
+  int dim = 0;
+  int dtype = 1;
+  int64_t L[kMaxDim] = {1, 1, 1};   // generator extents (4m+1)
+  int64_t n[kMaxDim] = {1, 1, 1};   // block extents (L+1)/2
+  int64_t F[kMaxDim] = {1, 1, 1};   // FFT extents
+  int64_t M = 1, Ftot = 1;
+  void* vhat = nullptr;             // FFT of the zero-padded generator, pre-scaled by 1/Ftot
+  FftCache fft;
+  DevBuf P, Q;                      // padded input (zeros persist), spectrum / output
+  int64_t P_rows = 0;               // rows of P known to be zero outside the block
+  DevBuf cg_vec, cg_scal;
+  ~Toeplitz();
+};
+
+enum ApplyMode { kModeT = 0, kModeGv = 1, kModeAmean = 2, kModeAvar = 3 };
+
+void toeplitz_create(Toeplitz& t, const void* v, int dim, const int64_t* Ls, int dtype, int force_pow2,
+                     cudaStream_t st);
+void toeplitz_apply(Toeplitz& t, const void* x, int batch, const void* ws, double sigmasq, int mode, void* y,
+                    cudaStream_t st);
+void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void* minv, const void* b, void* x,
+              int batch, double tol, int max_iter, int early_stopping, int batched_semantics,
+              int* iters_completed, cudaStream_t st);
+
+}  // namespace efgp

@@ -1,0 +1,76 @@
+"""ctypes binding of libefgp_b200.so (the C ABI in include/efgp_b200.h).
+
+There is no CPU fallback: if the shared library is missing or a tensor is not on a CUDA device
+the call raises.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libefgp_b200.so")
+
+_lib = None
+
+c_i64p = ctypes.POINTER(ctypes.c_int64)
+c_dblp = ctypes.POINTER(ctypes.c_double)
+c_intp = ctypes.POINTER(ctypes.c_int)
+vp = ctypes.c_void_p
+
+_SIGNATURES = {
+    "efgp_version": (ctypes.c_int, []),
+    "efgp_last_error": (ctypes.c_char_p, []),
+    "efgp_nufft_create": (ctypes.c_int, [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_int]),
+    "efgp_nufft_set_points": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_double, c_dblp, vp]),
+    "efgp_nufft_destroy": (None, [vp]),
+    "efgp_nufft_type1": (ctypes.c_int, [vp, vp, ctypes.c_int, ctypes.c_int, c_i64p, ctypes.c_double,
+                                        ctypes.c_int, ctypes.c_int, vp, vp, vp]),
+    "efgp_nufft_type2": (ctypes.c_int, [vp, vp, ctypes.c_int, c_i64p, ctypes.c_double, ctypes.c_int,
+                                        ctypes.c_int, vp, ctypes.c_int, vp, vp]),
+    "efgp_nufft_plan_info": (ctypes.c_int, [vp, c_i64p, ctypes.c_double, c_i64p, c_intp]),
+    "efgp_toeplitz_create": (ctypes.c_int, [ctypes.POINTER(vp), vp, ctypes.c_int, c_i64p, ctypes.c_int,
+                                            ctypes.c_int, vp]),
+    "efgp_toeplitz_destroy": (None, [vp]),
+    "efgp_toeplitz_fft_shape": (ctypes.c_int, [vp, c_i64p]),
+    "efgp_toeplitz_apply": (ctypes.c_int, [vp, vp, ctypes.c_int, vp, ctypes.c_double, ctypes.c_int, vp, vp]),
+    "efgp_cg_solve": (ctypes.c_int, [vp, vp, ctypes.c_double, ctypes.c_int, vp, vp, vp, ctypes.c_int,
+                                     ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_intp, vp]),
+}
+
+EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+
+
+class EfgpError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load (once) and return the shared library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise EfgpError(
+                f"{LIB_PATH} not found: build it with `python gp-quadrature_b200/build.py` "
+                "(there is no CPU or PyTorch fallback for the EFGP hot path)")
+        l = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def check(code):
+    if code != 0:
+        msg = lib().efgp_last_error()
+        raise EfgpError(f"libefgp_b200 error {code}: {msg.decode() if msg else '?'}")
+
+
+def i64_array(vals):
+    vals = [int(v) for v in vals]
+    return (ctypes.c_int64 * len(vals))(*vals)
+
+
+def dbl_array(vals):
+    vals = [float(v) for v in vals]
+    return (ctypes.c_double * len(vals))(*vals)

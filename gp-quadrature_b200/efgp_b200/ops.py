@@ -1,0 +1,204 @@
+"""Torch-facing wrappers over the C ABI: device tensors in, device tensors out.
+
+PyTorch is used only for device memory and streams; all arithmetic on the O(N) and O(M log M)
+paths happens in libefgp_b200.so.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import check, i64_array, dbl_array
+
+MODE_T, MODE_GV, MODE_A_MEAN, MODE_A_VAR = 0, 1, 2, 3
+
+
+def _dtype_code(real_dtype):
+    if real_dtype == torch.float32:
+        return 0
+    if real_dtype == torch.float64:
+        return 1
+    raise TypeError(f"unsupported dtype {real_dtype}; EFGP runs in float32 or float64")
+
+
+def cmplx_of(real_dtype):
+    return torch.complex64 if real_dtype == torch.float32 else torch.complex128
+
+
+def real_of(dtype):
+    if dtype in (torch.complex64, torch.float32):
+        return torch.float32
+    return torch.float64
+
+
+def _require_cuda(t, what):
+    if not t.is_cuda:
+        raise _lib.EfgpError(f"{what} must be a CUDA tensor: the EFGP hot path has no CPU fallback")
+
+
+def _stream(dev):
+    return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+class NufftPlan:
+    """Bin-sorted point set + fine-grid plans for x (N, d) scaled by h (phi = 2 pi h (x - xcen))."""
+
+    def __init__(self, x, h, xcen=None):
+        _require_cuda(x, "x")
+        if x.ndim == 1:
+            x = x[:, None]
+        self.x = x.contiguous()
+        self.N, self.d = self.x.shape
+        self.rdtype = self.x.dtype
+        self.cdtype = cmplx_of(self.rdtype)
+        self.device = self.x.device
+        self.h = float(h)
+        xc = [0.0] * self.d if xcen is None else [float(v) for v in xcen]
+        self._h = ctypes.c_void_p()
+        check(_lib.lib().efgp_nufft_create(ctypes.byref(self._h), int(self.d), _dtype_code(self.rdtype)))
+        with torch.cuda.device(self.device):
+            check(_lib.lib().efgp_nufft_set_points(self._h, _ptr(self.x), int(self.N), self.h, dbl_array(xc),
+                                                   _stream(self.device)))
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().efgp_nufft_destroy(h)
+            except Exception:
+                pass
+
+    def _scale(self, scale, M):
+        if scale is None:
+            return None
+        if scale.is_complex():
+            scale = scale.real
+        scale = scale.to(device=self.device, dtype=self.rdtype).reshape(-1).contiguous()
+        if scale.numel() != M:
+            raise ValueError(f"scale has {scale.numel()} entries, expected {M}")
+        return scale
+
+    def type1(self, vals, out_shape, eps, isign=-1, modeord=False, scale=None):
+        """vals (N,) or (B, N), real or complex, or None for all-ones -> (…, *out_shape) complex."""
+        out_shape = tuple(int(s) for s in out_shape)
+        if len(out_shape) != self.d:
+            raise ValueError(f"out_shape {out_shape} does not match dimension {self.d}")
+        M = 1
+        for s in out_shape:
+            M *= s
+        batched = vals is not None and vals.ndim > 1
+        if vals is None:
+            B, is_c, v = 1, 0, None
+        else:
+            _require_cuda(vals, "vals")
+            if vals.shape[-1] != self.N:
+                raise ValueError(f"vals has trailing size {vals.shape[-1]}, expected {self.N}")
+            is_c = 1 if vals.is_complex() else 0
+            v = vals.to(self.cdtype if is_c else self.rdtype).reshape(-1, self.N).contiguous()
+            B = v.shape[0]
+        sc = self._scale(scale, M)
+        out = torch.empty((B,) + out_shape, dtype=self.cdtype, device=self.device)
+        with torch.cuda.device(self.device):
+            check(_lib.lib().efgp_nufft_type1(self._h, _ptr(v), is_c, B, i64_array(out_shape), float(eps),
+                                              int(isign), int(bool(modeord)), _ptr(sc), _ptr(out),
+                                              _stream(self.device)))
+        if batched:
+            return out.reshape(tuple(vals.shape[:-1]) + out_shape)
+        return out.reshape(out_shape)
+
+    def type2(self, fk, shape, eps, isign=+1, modeord=False, scale=None, real_out=False):
+        """fk (*shape) / (M,) or batched (B, …) complex -> (N,) or (B, N), real if real_out."""
+        shape = tuple(int(s) for s in shape)
+        if len(shape) != self.d:
+            raise ValueError(f"shape {shape} does not match dimension {self.d}")
+        M = 1
+        for s in shape:
+            M *= s
+        _require_cuda(fk, "fk")
+        f = fk.to(self.cdtype)
+        if f.numel() % M != 0:
+            raise ValueError(f"mode array of {f.numel()} elements is not a multiple of {M}")
+        B = f.numel() // M
+        batched = not (tuple(f.shape) == shape or tuple(f.shape) == (M,))
+        f = f.reshape(B, M).contiguous()
+        sc = self._scale(scale, M)
+        out = torch.empty((B, self.N), dtype=self.rdtype if real_out else self.cdtype, device=self.device)
+        with torch.cuda.device(self.device):
+            check(_lib.lib().efgp_nufft_type2(self._h, _ptr(f), B, i64_array(shape), float(eps), int(isign),
+                                              int(bool(modeord)), _ptr(sc), 1 if real_out else 0, _ptr(out),
+                                              _stream(self.device)))
+        return out if batched else out.reshape(self.N)
+
+
+class ToeplitzPlan:
+    """Cached spectrum of the zero-padded F^H F generator v ((4m+1)^d complex)."""
+
+    def __init__(self, v, force_pow2=True):
+        _require_cuda(v, "v")
+        if not v.is_complex():
+            v = v.to(cmplx_of(v.dtype))
+        self.v = v.contiguous()
+        self.cdtype = self.v.dtype
+        self.rdtype = real_of(self.cdtype)
+        self.device = v.device
+        self.Ls = list(self.v.shape)
+        self.d = len(self.Ls)
+        self.ns = [(L + 1) // 2 for L in self.Ls]
+        self.size = 1
+        for n in self.ns:
+            self.size *= n
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            check(_lib.lib().efgp_toeplitz_create(ctypes.byref(self._h), _ptr(self.v), self.d, i64_array(self.Ls),
+                                                  _dtype_code(self.rdtype), 1 if force_pow2 else 0,
+                                                  _stream(self.device)))
+        shp = (ctypes.c_int64 * self.d)()
+        check(_lib.lib().efgp_toeplitz_fft_shape(self._h, shp))
+        self.fft_shape = [int(s) for s in shp]
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                _lib.lib().efgp_toeplitz_destroy(h)
+            except Exception:
+                pass
+
+    def _ws(self, ws):
+        if ws is None:
+            return None
+        if ws.is_complex():
+            ws = ws.real
+        return ws.to(device=self.device, dtype=self.rdtype).reshape(-1).contiguous()
+
+    def apply(self, x, mode=MODE_T, ws=None, sigmasq=0.0):
+        """x (…, M) complex -> same shape."""
+        _require_cuda(x, "x")
+        xs = x.to(self.cdtype).reshape(-1, self.size).contiguous()
+        y = torch.empty_like(xs)
+        w = self._ws(ws)
+        with torch.cuda.device(self.device):
+            check(_lib.lib().efgp_toeplitz_apply(self._h, _ptr(xs), xs.shape[0], _ptr(w), float(sigmasq), int(mode),
+                                                 _ptr(y), _stream(self.device)))
+        return y.reshape(x.shape)
+
+    def cg(self, b, x0, mode, ws, sigmasq, tol, max_iter=None, early_stopping=True, minv=None, batched=None):
+        """Solve A x = b for the fused operator `mode`; returns (x, iters_completed)."""
+        _require_cuda(b, "b")
+        if batched is None:
+            batched = b.ndim > 1
+        bs = b.to(self.cdtype).reshape(-1, self.size).contiguous()
+        x = x0.to(self.cdtype).reshape(-1, self.size).clone().contiguous()
+        w = self._ws(ws)
+        mi = self._ws(minv)
+        iters = ctypes.c_int(0)
+        with torch.cuda.device(self.device):
+            check(_lib.lib().efgp_cg_solve(self._h, _ptr(w), float(sigmasq), int(mode), _ptr(mi), _ptr(bs), _ptr(x),
+                                           bs.shape[0], float(tol), -1 if max_iter is None else int(max_iter),
+                                           1 if early_stopping else 0, 1 if batched else 0, ctypes.byref(iters),
+                                           _stream(self.device)))
+        return x.reshape(b.shape), int(iters.value)

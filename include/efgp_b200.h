@@ -1,0 +1,85 @@
+/* libefgp_b200 -- C ABI of the B200-native EFGP hot path.
+ *
+ * The reference (danbider/gp-quadrature) is pure Python and has no FFI layer; its hot path
+ * bottoms out in four external calls.  Each entry point below replaces one
+ * reference interface, cited as file:line relative to the reference tree.  INTEGRATION.md shows
+ * the ctypes binding a reference maintainer would add.
+ *
+ * Conventions
+ *   - every data pointer is a caller-owned DEVICE pointer (e.g. torch.Tensor.data_ptr()); the
+ *     caller keeps the allocation alive for the duration of the call (and, for set_points, for
+ *     the lifetime of the handle);
+ *   - dtype: 0 = float32 / complex64, 1 = float64 / complex128 (interleaved re,im);
+ *   - `stream` is a cudaStream_t passed as void* (0 = default stream); calls enqueue on it and
+ *     do not synchronise unless stated;
+ *   - return value 0 = ok; otherwise efgp_last_error() holds a thread-local message;
+ *   - handles are not thread-safe.
+ */
+#ifndef EFGP_B200_H
+#define EFGP_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct efgp_nufft efgp_nufft;
+typedef struct efgp_toeplitz efgp_toeplitz;
+
+int efgp_version(void);
+const char* efgp_last_error(void);
+
+/* ---- NUFFT: replaces class NUFFT (efgpnd.py:1423-1549) and the pytorch_finufft calls under it */
+
+/* NUFFT.__init__ (efgpnd.py:1432-1452): phi = 2*pi*h*(x - xcen).  x is (N, dim) row-major. */
+int efgp_nufft_create(efgp_nufft** out, int dim, int dtype);
+int efgp_nufft_set_points(efgp_nufft* nu, const void* x, int64_t npts, double h, const double* xcen,
+                          void* stream);
+void efgp_nufft_destroy(efgp_nufft* nu);
+
+/* NUFFT.type1 -> pff.finufft_type1(phi, vals, out_shape, eps, isign=-1, modeord=False)
+ * (efgpnd.py:1454-1508).  strengths: (batch, npts) real (is_complex=0) or complex (1), NULL = all
+ * ones (the Toeplitz generator, efgpnd.py:1395-1421).  out: (batch, *out_shape) complex, C order,
+ * modes -(n/2)..(n-1)/2 per axis (FFT order if modeord != 0).  scale: optional real (prod out_shape,)
+ * diagonal multiplied into the output (the spectral weights ws, efgpnd.py:786). */
+int efgp_nufft_type1(efgp_nufft* nu, const void* strengths, int is_complex, int batch,
+                     const int64_t* out_shape, double eps, int isign, int modeord, const void* scale,
+                     void* out, void* stream);
+
+/* NUFFT.type2 -> pff.finufft_type2(phi, fk, eps, isign=+1, modeord) (efgpnd.py:1510-1549, 1679).
+ * modes: (batch, *shape) complex; scale: optional real diagonal applied to the modes first
+ * (ws * beta, efgpnd.py:922).  out: (batch, npts) complex, or real when real_out != 0 (exactly the
+ * real part of the complex result: every reference caller takes .real). */
+int efgp_nufft_type2(efgp_nufft* nu, const void* modes, int batch, const int64_t* shape, double eps,
+                     int isign, int modeord, const void* scale, int real_out, void* out, void* stream);
+
+/* diagnostics: spreading width / fine grid the plan would use for (shape, eps) */
+int efgp_nufft_plan_info(efgp_nufft* nu, const int64_t* shape, double eps, int64_t* nf_out, int* width_out);
+
+/* ---- Toeplitz: replaces class ToeplitzND (efgpnd.py:1239-1393) */
+int efgp_toeplitz_create(efgp_toeplitz** out, const void* v, int dim, const int64_t* Ls, int dtype,
+                         int force_pow2, void* stream);
+void efgp_toeplitz_destroy(efgp_toeplitz* t);
+int efgp_toeplitz_fft_shape(efgp_toeplitz* t, int64_t* shape_out);
+
+/* mode 0: y = T x                          ToeplitzND.__call__ (efgpnd.py:1331-1393)
+ * mode 1: y = ws * T(ws * x)               create_Gv      (efgpnd.py:1572-1591)
+ * mode 2: y = Gv(x) + sigmasq * x          create_A_mean  (efgpnd.py:1593-1600)
+ * mode 3: y = Gv(x) / sigmasq + x          create_A_var   (efgpnd.py:1602-1609)
+ * x, y: (batch, M) complex; ws: (M,) real. */
+int efgp_toeplitz_apply(efgp_toeplitz* t, const void* x, int batch, const void* ws, double sigmasq,
+                        int mode, void* y, void* stream);
+
+/* ---- CG: replaces ConjugateGradients.solve (cg.py:73-244) for operators of the four modes above.
+ * b: (batch, M) complex; x: (batch, M) complex, holds x0 on entry and the solution on exit;
+ * minv: optional (M,) real Jacobi diagonal M^-1 (create_jacobi_precond, efgpnd.py:1619-1631);
+ * max_iter < 0 means 2*M (cg.py:60-65); batched_semantics selects _solve_batched (1) or
+ * _solve_single (0) stopping rules and iteration counting.  Synchronises the stream. */
+int efgp_cg_solve(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, const void* minv,
+                  const void* b, void* x, int batch, double tol, int max_iter, int early_stopping,
+                  int batched_semantics, int* iters_completed, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EFGP_B200_H */
