@@ -98,8 +98,10 @@ class NufftPlan:
             if vals.shape[-1] != self.N:
                 raise ValueError(f"vals has trailing size {vals.shape[-1]}, expected {self.N}")
             is_c = 1 if vals.is_complex() else 0
-            v = vals.to(self.cdtype if is_c else self.rdtype).reshape(-1, self.N).contiguous()
-            B = v.shape[0]
+            B = 1
+            for sdim in vals.shape[:-1]:
+                B *= int(sdim)
+            v = vals.to(self.cdtype if is_c else self.rdtype).reshape(B, self.N).contiguous()
         sc = self._scale(scale, M)
         out = torch.empty((B,) + out_shape, dtype=self.cdtype, device=self.device)
         with torch.cuda.device(self.device):
