@@ -85,4 +85,11 @@ template <> struct cplx_of<double> { using type = double2; };
 
 inline int div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
+// Process-wide caching pool for large device scratch (sort temporaries, sorted point sets):
+// cudaMalloc/cudaFree of GB-sized blocks costs milliseconds and synchronises the device, and the
+// EFGP loop rebuilds its plans every hyperparameter step.
+void* pool_alloc(size_t bytes);
+void pool_free(void* p);
+void pool_trim();
+
 }  // namespace efgp

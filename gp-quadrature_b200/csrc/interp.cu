@@ -45,18 +45,18 @@ __device__ __forceinline__ int wrap_i(int i, int n) {
 }
 
 template <typename T, int W>
-__global__ void __launch_bounds__(256)
-interp1d_kernel(const T* __restrict__ xs0, const uint32_t* __restrict__ perm, int64_t N, int P, int nf0,
+__global__ void __launch_bounds__(kTileThreads)
+interp1d_kernel(const T* __restrict__ xs0, const uint32_t* __restrict__ perm, int P, int nf0,
                 const T* __restrict__ grid, T* __restrict__ out, int64_t ostride,
                 const __grid_constant__ ESDev<T> es) {
-  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t s = tid * P, e = s + P < N ? s + P : N;
-  if (s >= N) return;
+  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
   T g[W];
   int cur = -1;
-  for (int64_t n = s; n < e; ++n) {
-    T X = xs0[n];
+  for (int j = 0; j < P; ++j) {
+    const int64_t pos = base + (int64_t)j * kTileThreads;
+    T X = xs0[pos];
+    if (X < T(0)) break;
     int c0 = (int)X;
     if (c0 != cur) {
 #pragma unroll
@@ -68,41 +68,48 @@ interp1d_kernel(const T* __restrict__ xs0, const uint32_t* __restrict__ perm, in
     T acc = 0;
 #pragma unroll
     for (int i = 0; i < W; ++i) acc = fma(g[i], k0[i], acc);
-    out[(int64_t)perm[n] * ostride] = acc;
+    out[(int64_t)perm[pos] * ostride] = acc;
   }
 }
 
 template <typename T, int W>
-__global__ void __launch_bounds__(256, 1)
-interp2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const uint32_t* __restrict__ perm,
-                int64_t N, int P, int nf0, int nf1, const T* __restrict__ grid, T* __restrict__ out,
-                int64_t ostride, const __grid_constant__ ESDev<T> es) {
-  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t s = tid * P, e = s + P < N ? s + P : N;
-  if (s >= N) return;
+__global__ void __launch_bounds__(kTileThreads, 1)
+interp2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const uint32_t* __restrict__ perm, int P,
+                int nf0, int nf1, const T* __restrict__ grid, T* __restrict__ out, int64_t ostride,
+                const __grid_constant__ ESDev<T> es) {
+  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
   T g[W][W];
   int cur0 = -1, cur1 = -1;
-  T X0 = xs0[s], X1 = xs1[s];
-  uint32_t pn = perm[s];
-  for (int64_t n = s; n < e; ++n) {
-    T nX0 = X0, nX1 = X1;
-    uint32_t npn = pn;
-    if (n + 1 < e) {
-      nX0 = xs0[n + 1];
-      nX1 = xs1[n + 1];
-      npn = perm[n + 1];
+  T X0 = xs0[base], X1 = xs1[base];
+  uint32_t pn = perm[base];
+  T nX0 = T(-1), nX1 = T(0);
+  uint32_t npn = 0;
+  if (P > 1) {
+    nX0 = xs0[base + kTileThreads];
+    nX1 = xs1[base + kTileThreads];
+    npn = perm[base + kTileThreads];
+  }
+  for (int j = 0; j < P; ++j) {
+    if (X0 < T(0)) break;
+    T fX0 = T(-1), fX1 = T(0);
+    uint32_t fpn = 0;
+    if (j + 2 < P) {
+      const int64_t pos = base + (int64_t)(j + 2) * kTileThreads;
+      fX0 = xs0[pos];
+      fX1 = xs1[pos];
+      fpn = perm[pos];
     }
     int c0 = (int)X0, c1 = (int)X1;
     if (c0 != cur0 || c1 != cur1) {
       int cols[W];
 #pragma unroll
-      for (int j = 0; j < W; ++j) cols[j] = wrap_i(c1 - OFF + j, nf1);
+      for (int jj = 0; jj < W; ++jj) cols[jj] = wrap_i(c1 - OFF + jj, nf1);
 #pragma unroll
       for (int i = 0; i < W; ++i) {
         const T* row = grid + (int64_t)wrap_i(c0 - OFF + i, nf0) * nf1;
 #pragma unroll
-        for (int j = 0; j < W; ++j) g[i][j] = __ldg(row + cols[j]);
+        for (int jj = 0; jj < W; ++jj) g[i][jj] = __ldg(row + cols[jj]);
       }
       cur0 = c0;
       cur1 = c1;
@@ -115,28 +122,32 @@ interp2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const uint
     for (int i = 0; i < W; ++i) {
       T r = 0;
 #pragma unroll
-      for (int j = 0; j < W; ++j) r = fma(g[i][j], k1[j], r);
+      for (int jj = 0; jj < W; ++jj) r = fma(g[i][jj], k1[jj], r);
       acc = fma(r, k0[i], acc);
     }
     out[(int64_t)pn * ostride] = acc;
     X0 = nX0;
     X1 = nX1;
     pn = npn;
+    nX0 = fX0;
+    nX1 = fX1;
+    npn = fpn;
   }
 }
 
-// generic: wide 2-D kernels and 3-D, one point per thread, gathers through L1/L2
+// generic: wide 2-D kernels and 3-D, one slot per thread, gathers through L1/L2
 template <typename T, int W, int D>
 __global__ void __launch_bounds__(256)
 interp_direct_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* __restrict__ xs2,
-                     const uint32_t* __restrict__ perm, int64_t N, int nf0, int nf1, int nf2,
+                     const uint32_t* __restrict__ perm, int64_t npos, int nf0, int nf1, int nf2,
                      const T* __restrict__ grid, T* __restrict__ out, int64_t ostride,
                      const __grid_constant__ ESDev<T> es) {
   int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
+  if (n >= npos) return;
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
   T k0[W], k1[W], k2[W];
   T X0 = xs0[n];
+  if (X0 < T(0)) return;
   int c0 = (int)X0;
   es_eval_i<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
   T X1 = xs1[n];
@@ -180,40 +191,29 @@ interp_direct_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const
   out[(int64_t)perm[n] * ostride] = acc;
 }
 
-static int pick_ppt(int64_t N) {
-  int64_t P = N / (148 * 256 * 4);
-  if (P < 1) P = 1;
-  if (P > 64) P = 64;
-  return (int)P;
-}
-
 template <typename T, int W>
 static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* grid, T* out, int64_t ostride,
                      cudaStream_t st) {
   ESDev<T> es;
   es_to_dev<T>(k, es);
-  const int64_t N = sp.N;
   const T* x0 = (const T*)sp.xs[0];
   const T* x1 = (const T*)sp.xs[1];
   const T* x2 = (const T*)sp.xs[2];
   constexpr int kRegMaxW = sizeof(T) == 8 ? 9 : 10;
+  const int nt = (int)sp.ntiles;
   if (sp.dim == 1) {
-    int P = pick_ppt(N);
-    interp1d_kernel<T, W><<<div_up(div_up(N, P), 256), 256, 0, st>>>(x0, sp.perm, N, P, (int)sp.nf[0], grid, out,
-                                                                     ostride, es);
+    interp1d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(x0, sp.perm, sp.P, (int)sp.nf[0], grid, out, ostride, es);
   } else if (sp.dim == 2) {
     if constexpr (W <= kRegMaxW) {
-      int P = pick_ppt(N);
-      interp2d_kernel<T, W><<<div_up(div_up(N, P), 256), 256, 0, st>>>(x0, x1, sp.perm, N, P, (int)sp.nf[0],
-                                                                       (int)sp.nf[1], grid, out, ostride, es);
+      interp2d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(x0, x1, sp.perm, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
+                                                         out, ostride, es);
     } else {
-      interp_direct_kernel<T, W, 2><<<div_up(N, 256), 256, 0, st>>>(x0, x1, x2, sp.perm, N, (int)sp.nf[0],
-                                                                    (int)sp.nf[1], 1, grid, out, ostride, es);
+      interp_direct_kernel<T, W, 2><<<div_up(sp.npos, 256), 256, 0, st>>>(
+          x0, x1, x2, sp.perm, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, out, ostride, es);
     }
   } else {
-    interp_direct_kernel<T, W, 3><<<div_up(N, 256), 256, 0, st>>>(x0, x1, x2, sp.perm, N, (int)sp.nf[0],
-                                                                  (int)sp.nf[1], (int)sp.nf[2], grid, out, ostride,
-                                                                  es);
+    interp_direct_kernel<T, W, 3><<<div_up(sp.npos, 256), 256, 0, st>>>(
+        x0, x1, x2, sp.perm, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, out, ostride, es);
   }
   EFGP_CUDA(cudaGetLastError());
 }

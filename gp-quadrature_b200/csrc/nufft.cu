@@ -215,7 +215,27 @@ static void upload_dinv(Nufft& nu, const ESKernel& ker, const int64_t* nf, const
   size_t esz = dtype == 0 ? 4 : 8;
   size_t total = 0;
   for (int a = 0; a < dim; ++a) total += (size_t)(n[a] / 2 + 1);
-  char* base = (char*)nu.dec.get(total * esz);
+  // tables are cached per geometry: repeated transforms (probes, CG) skip the host work and the sync
+  char keybuf[160];
+  snprintf(keybuf, sizeof(keybuf), "%d|%.17g|%lld,%lld,%lld|%lld,%lld,%lld", ker.W, ker.beta, (long long)nf[0],
+           (long long)(dim > 1 ? nf[1] : 0), (long long)(dim > 2 ? nf[2] : 0), (long long)n[0],
+           (long long)(dim > 1 ? n[1] : 0), (long long)(dim > 2 ? n[2] : 0));
+  std::string key(keybuf);
+  auto hit = nu.dec_tables.find(key);
+  if (hit != nu.dec_tables.end()) {
+    char* b0 = (char*)hit->second->p;
+    size_t pos0 = 0;
+    for (int a = 0; a < dim; ++a) {
+      dptr[a] = b0 + pos0 * esz;
+      pos0 += (size_t)(n[a] / 2 + 1);
+    }
+    for (int a = dim; a < kMaxDim; ++a) dptr[a] = b0;
+    return;
+  }
+  if (nu.dec_tables.size() > 16) nu.dec_tables.clear();
+  std::unique_ptr<DevBuf> holder(new DevBuf());
+  char* base = (char*)holder->get(total * esz);
+  nu.dec_tables[key] = std::move(holder);
   std::vector<double> host;
   std::vector<float> hostf;
   size_t pos = 0;
@@ -346,11 +366,14 @@ static void type1_t(Nufft& nu, const void* strengths, int is_complex, int batch,
   for (int b0 = 0; b0 < batch; b0 += chunk) {
     int nb = std::min(chunk, batch - b0);
     EFGP_CUDA(cudaMemsetAsync(fine, 0, (size_t)nb * ncomp * cells * sizeof(T), st));
+    T* cs = strengths ? (T*)nu.cperm.get((size_t)gc.sp->npos * sizeof(T)) : nullptr;
     for (int b = 0; b < nb; ++b) {
       for (int comp = 0; comp < ncomp; ++comp) {
-        const T* c = nullptr;
-        if (strengths) c = (const T*)strengths + (int64_t)(b0 + b) * nu.N * ncomp + comp;
-        launch_spread(*gc.sp, gc.ker, c, ncomp, fine + (int64_t)(b * ncomp + comp) * cells, st);
+        if (strengths) {
+          const T* c = (const T*)strengths + (int64_t)(b0 + b) * nu.N * ncomp + comp;
+          permute_strengths(*gc.sp, c, ncomp, cs, st);
+        }
+        launch_spread(*gc.sp, gc.ker, cs, fine + (int64_t)(b * ncomp + comp) * cells, st);
       }
     }
     cufftHandle plan = nu.fft.get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_R2C : CUFFT_D2Z, nb * ncomp, st);

@@ -9,14 +9,23 @@ namespace efgp {
 // Points sorted by fine-grid cell for one fine grid geometry.
 // xs[a][i] = Xc = X + shift (mod nf), X = nf * frac(h (x - xcen)); shift = 1/2 for odd W, 0 for even
 // (so cell = floor(Xc) identifies the W^d footprint for either parity, see spread.cu).
+//
+// Storage is TILE-TRANSPOSED: sorted ranks are cut into tiles of kTileThreads*P consecutive points;
+// inside a tile thread t owns the P consecutive ranks [t*P, (t+1)*P) (one long register run), and
+// its j-th point is stored at  tile*kTileThreads*P + j*kTileThreads + t  so that at every step j a
+// warp reads 32 consecutive words (fully coalesced, prefetchable).  Slots past N hold xs[0] = -1.
+constexpr int kTileThreads = 256;
 struct SortedPoints {
   int dim = 0;
   int dtype = 1;  // 0 f32, 1 f64
   int64_t N = 0;
   int64_t nf[kMaxDim] = {1, 1, 1};
   int odd = 0;
+  int P = 1;            // points per thread
+  int64_t ntiles = 0;
+  int64_t npos = 0;     // ntiles * kTileThreads * P
   void* xs[kMaxDim] = {nullptr, nullptr, nullptr};
-  uint32_t* perm = nullptr;
+  uint32_t* perm = nullptr;   // perm[pos] = original index of the point stored at slot pos
   uint64_t last_use = 0;
   ~SortedPoints();
 };
@@ -60,18 +69,20 @@ struct Nufft {
   uint64_t clock = 0;
   std::vector<std::unique_ptr<SortedPoints>> sorted;  // small LRU cache
   FftCache fft;
-  DevBuf fine, spec, tmp, dec;
-  std::map<std::string, std::vector<double>> dec_cache_host;
+  DevBuf fine, spec, tmp, dec, cperm;
+  std::map<std::string, std::unique_ptr<DevBuf>> dec_tables;  // deconvolution factors per geometry
 };
 
 // ---- points.cu
 void build_sorted_points(SortedPoints& sp, const void* x, int64_t N, int dim, int dtype, double h,
                          const double* xcen, const int64_t* nf, int odd, cudaStream_t st);
 
-// ---- spread.cu : grid (real, nf^d) += sum_n c_n psi(l - X_n).  c == nullptr means all ones.
-// c is indexed in ORIGINAL point order through perm (c[perm[i] * cstride]).
-void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* c, int64_t cstride,
-                   void* grid, cudaStream_t st);
+// ---- points.cu : cs[pos] = c[perm[pos] * cstride]  (strengths into slot order; npos entries)
+void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, void* cs, cudaStream_t st);
+
+// ---- spread.cu : grid (real, nf^d) += sum_n c_n psi(l - X_n).  cs == nullptr means all ones;
+// otherwise cs holds the strengths in SLOT order (permute_strengths).
+void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, void* grid, cudaStream_t st);
 
 // ---- interp.cu : out[perm[i] * ostride] = sum_l grid[l] psi(l - X_i)
 void launch_interp(const SortedPoints& sp, const ESKernel& k, const void* grid, void* out,

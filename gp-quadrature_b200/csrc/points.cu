@@ -11,8 +11,8 @@ namespace efgp {
 
 SortedPoints::~SortedPoints() {
   for (int a = 0; a < kMaxDim; ++a)
-    if (xs[a]) cudaFree(xs[a]);
-  if (perm) cudaFree(perm);
+    if (xs[a]) pool_free(xs[a]);
+  if (perm) pool_free(perm);
 }
 
 void* DevBuf::get(size_t bytes) {
@@ -71,20 +71,63 @@ __global__ void __launch_bounds__(256) key_kernel(const T* __restrict__ x, int64
   idx[i] = (uint32_t)i;
 }
 
+// One thread per SLOT (coalesced writes); the slot's sorted rank follows from the tile-transposed
+// layout described in nufft.cuh.
 template <typename T, int D>
-__global__ void __launch_bounds__(256) gather_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p,
-                                                     const uint32_t* __restrict__ perm, T* __restrict__ o0,
-                                                     T* __restrict__ o1, T* __restrict__ o2) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N) return;
-  int64_t src = perm[i];
+__global__ void __launch_bounds__(256) gather_kernel(const T* __restrict__ x, int64_t N, int P, FoldParams<T> p,
+                                                     const uint32_t* __restrict__ sorted_idx,
+                                                     uint32_t* __restrict__ perm, T* __restrict__ o0,
+                                                     T* __restrict__ o1, T* __restrict__ o2, int64_t npos) {
+  int64_t pos = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pos >= npos) return;
+  const int64_t tile_len = (int64_t)kTileThreads * P;
+  int64_t tile = pos / tile_len;
+  int r = (int)(pos - tile * tile_len);
+  int j = r / kTileThreads, t = r - j * kTileThreads;
+  int64_t rank = tile * tile_len + (int64_t)t * P + j;
   T* outs[3] = {o0, o1, o2};
+  if (rank >= N) {
+    outs[0][pos] = T(-1);
+#pragma unroll
+    for (int a = 1; a < D; ++a) outs[a][pos] = T(0);
+    perm[pos] = 0;
+    return;
+  }
+  int64_t src = sorted_idx[rank];
+  perm[pos] = (uint32_t)src;
 #pragma unroll
   for (int a = 0; a < D; ++a) {
     T X = fold_coord(x[src * D + a], p.h, p.xcen[a], p.nf[a], p.shift);
     if ((int)X >= p.inf[a]) X = T(0);
-    outs[a][i] = X;
+    outs[a][pos] = X;
   }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) permute_kernel(const T* __restrict__ c, int64_t cstride,
+                                                      const uint32_t* __restrict__ perm, int64_t npos,
+                                                      T* __restrict__ cs) {
+  int64_t pos = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pos >= npos) return;
+  cs[pos] = c[(int64_t)perm[pos] * cstride];
+}
+
+void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, void* cs, cudaStream_t st) {
+  if (sp.npos == 0) return;
+  int nb = div_up(sp.npos, 256);
+  if (sp.dtype == 0)
+    permute_kernel<float><<<nb, 256, 0, st>>>((const float*)c, cstride, sp.perm, sp.npos, (float*)cs);
+  else
+    permute_kernel<double><<<nb, 256, 0, st>>>((const double*)c, cstride, sp.perm, sp.npos, (double*)cs);
+  EFGP_CUDA(cudaGetLastError());
+}
+
+static int pick_points_per_thread(int64_t N) {
+  // >= 4 waves of 148 SMs x 256 threads when N allows, and long register runs when N is large
+  int64_t P = N / (148 * 256 * 4);
+  if (P < 1) P = 1;
+  if (P > 64) P = 64;
+  return (int)P;
 }
 
 template <typename T>
@@ -105,36 +148,42 @@ static void build_t(SortedPoints& sp, const T* x, int64_t N, int dim, double h, 
   int bits = 1;
   while ((1ull << bits) < (unsigned long long)cells) ++bits;
 
-  uint32_t *keys_in, *keys_out, *idx_in;
-  EFGP_CUDA(cudaMalloc(&keys_in, sizeof(uint32_t) * (size_t)N));
-  EFGP_CUDA(cudaMalloc(&keys_out, sizeof(uint32_t) * (size_t)N));
-  EFGP_CUDA(cudaMalloc(&idx_in, sizeof(uint32_t) * (size_t)N));
-  EFGP_CUDA(cudaMalloc(&sp.perm, sizeof(uint32_t) * (size_t)N));
+  sp.P = pick_points_per_thread(N);
+  const int64_t tile_len = (int64_t)kTileThreads * sp.P;
+  sp.ntiles = (N + tile_len - 1) / tile_len;
+  sp.npos = sp.ntiles * tile_len;
+
+  uint32_t* keys_in = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
+  uint32_t* keys_out = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
+  uint32_t* idx_in = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
+  uint32_t* idx_out = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
+  sp.perm = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)sp.npos);
   int nb = div_up(N, 256);
   if (dim == 1) key_kernel<T, 1><<<nb, 256, 0, st>>>(x, N, p, keys_in, idx_in);
   if (dim == 2) key_kernel<T, 2><<<nb, 256, 0, st>>>(x, N, p, keys_in, idx_in);
   if (dim == 3) key_kernel<T, 3><<<nb, 256, 0, st>>>(x, N, p, keys_in, idx_in);
   EFGP_CUDA(cudaGetLastError());
   size_t tmp_bytes = 0;
-  EFGP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, idx_in, sp.perm, (int)N, 0,
+  EFGP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, idx_in, idx_out, (int)N, 0,
                                             bits, st));
-  void* tmp = nullptr;
-  EFGP_CUDA(cudaMalloc(&tmp, tmp_bytes));
-  EFGP_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, idx_in, sp.perm, (int)N, 0, bits,
+  void* tmp = pool_alloc(tmp_bytes);
+  EFGP_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, idx_in, idx_out, (int)N, 0, bits,
                                             st));
-  for (int a = 0; a < dim; ++a) EFGP_CUDA(cudaMalloc(&sp.xs[a], sizeof(T) * (size_t)N));
+  for (int a = 0; a < dim; ++a) sp.xs[a] = pool_alloc(sizeof(T) * (size_t)sp.npos);
   T* o0 = (T*)sp.xs[0];
   T* o1 = (T*)sp.xs[1];
   T* o2 = (T*)sp.xs[2];
-  if (dim == 1) gather_kernel<T, 1><<<nb, 256, 0, st>>>(x, N, p, sp.perm, o0, o1, o2);
-  if (dim == 2) gather_kernel<T, 2><<<nb, 256, 0, st>>>(x, N, p, sp.perm, o0, o1, o2);
-  if (dim == 3) gather_kernel<T, 3><<<nb, 256, 0, st>>>(x, N, p, sp.perm, o0, o1, o2);
+  int nbp = div_up(sp.npos, 256);
+  if (dim == 1) gather_kernel<T, 1><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, sp.npos);
+  if (dim == 2) gather_kernel<T, 2><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, sp.npos);
+  if (dim == 3) gather_kernel<T, 3><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, sp.npos);
   EFGP_CUDA(cudaGetLastError());
-  EFGP_CUDA(cudaStreamSynchronize(st));
-  cudaFree(tmp);
-  cudaFree(keys_in);
-  cudaFree(keys_out);
-  cudaFree(idx_in);
+  // scratch goes back to the pool; later users run on the same stream, so ordering is preserved
+  pool_free(tmp);
+  pool_free(keys_in);
+  pool_free(keys_out);
+  pool_free(idx_in);
+  pool_free(idx_out);
 }
 
 void build_sorted_points(SortedPoints& sp, const void* x, int64_t N, int dim, int dtype, double h,

@@ -49,23 +49,24 @@ __device__ __forceinline__ int wrap_idx(int i, int n) {
   return i;
 }
 
+// Slot addressing of the tile-transposed sorted layout (nufft.cuh): thread t of tile `blockIdx.x`
+// reads its j-th point at base + j*kTileThreads.
 // ------------------------------------------------------------------ 1-D
 template <typename T, int W, bool HAS_C>
-__global__ void __launch_bounds__(256)
-spread1d_kernel(const T* __restrict__ xs0, const uint32_t* __restrict__ perm, const T* __restrict__ c,
-                int64_t cstride, int64_t N, int P, int nf0, T* __restrict__ grid,
+__global__ void __launch_bounds__(kTileThreads)
+spread1d_kernel(const T* __restrict__ xs0, const T* __restrict__ cs, int P, int nf0, T* __restrict__ grid,
                 const __grid_constant__ ESDev<T> es) {
-  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t s = tid * P, e = s + P < N ? s + P : N;
-  if (s >= N) return;
+  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
   T acc[W];
 #pragma unroll
   for (int i = 0; i < W; ++i) acc[i] = 0;
   int cur = -1;
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
-  for (int64_t n = s; n < e; ++n) {
-    T X = xs0[n];
-    T cv = HAS_C ? c[(int64_t)perm[n] * cstride] : T(1);
+  for (int j = 0; j < P; ++j) {
+    const int64_t pos = base + (int64_t)j * kTileThreads;
+    T X = xs0[pos];
+    if (X < T(0)) break;
+    T cv = HAS_C ? cs[pos] : T(1);
     int c0 = (int)X;
     if (c0 != cur) {
       if (cur >= 0) {
@@ -81,8 +82,10 @@ spread1d_kernel(const T* __restrict__ xs0, const uint32_t* __restrict__ perm, co
 #pragma unroll
     for (int i = 0; i < W; ++i) acc[i] = fma(cv, k0[i], acc[i]);
   }
+  if (cur >= 0) {
 #pragma unroll
-  for (int i = 0; i < W; ++i) atomicAdd(&grid[wrap_idx(cur - OFF + i, nf0)], acc[i]);
+    for (int i = 0; i < W; ++i) atomicAdd(&grid[wrap_idx(cur - OFF + i, nf0)], acc[i]);
+  }
 }
 
 // ------------------------------------------------------------------ 2-D, register footprint
@@ -104,28 +107,33 @@ __device__ __forceinline__ void flush2d(T (&acc)[W][W], int c0, int c1, int nf0,
 }
 
 template <typename T, int W, bool HAS_C>
-__global__ void __launch_bounds__(256, 1)
-spread2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const uint32_t* __restrict__ perm,
-                const T* __restrict__ c, int64_t cstride, int64_t N, int P, int nf0, int nf1,
-                T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
-  int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t s = tid * P, e = s + P < N ? s + P : N;
-  if (s >= N) return;
+__global__ void __launch_bounds__(kTileThreads, 1)
+spread2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* __restrict__ cs, int P, int nf0,
+                int nf1, T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
+  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
   T acc[W][W];
 #pragma unroll
   for (int i = 0; i < W; ++i)
 #pragma unroll
     for (int j = 0; j < W; ++j) acc[i][j] = 0;
   int cur0 = -1, cur1 = -1;
-  // software prefetch of the next point
-  T X0 = xs0[s], X1 = xs1[s];
-  T cv = HAS_C ? c[(int64_t)perm[s] * cstride] : T(1);
-  for (int64_t n = s; n < e; ++n) {
-    T nX0 = X0, nX1 = X1, ncv = cv;
-    if (n + 1 < e) {
-      nX0 = xs0[n + 1];
-      nX1 = xs1[n + 1];
-      if (HAS_C) ncv = c[(int64_t)perm[n + 1] * cstride];
+  // two-deep software prefetch of the (coalesced) point stream
+  T X0 = xs0[base], X1 = xs1[base];
+  T cv = HAS_C ? cs[base] : T(1);
+  T nX0 = T(-1), nX1 = T(0), ncv = T(1);
+  if (P > 1) {
+    nX0 = xs0[base + kTileThreads];
+    nX1 = xs1[base + kTileThreads];
+    if (HAS_C) ncv = cs[base + kTileThreads];
+  }
+  for (int j = 0; j < P; ++j) {
+    if (X0 < T(0)) break;
+    T fX0 = T(-1), fX1 = T(0), fcv = T(1);
+    if (j + 2 < P) {
+      const int64_t pos = base + (int64_t)(j + 2) * kTileThreads;
+      fX0 = xs0[pos];
+      fX1 = xs1[pos];
+      if (HAS_C) fcv = cs[pos];
     }
     int c0 = (int)X0, c1 = (int)X1;
     if (c0 != cur0 || c1 != cur1) {
@@ -140,28 +148,32 @@ spread2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const uint
     for (int i = 0; i < W; ++i) {
       T a = cv * k0[i];
 #pragma unroll
-      for (int j = 0; j < W; ++j) acc[i][j] = fma(a, k1[j], acc[i][j]);
+      for (int jj = 0; jj < W; ++jj) acc[i][jj] = fma(a, k1[jj], acc[i][jj]);
     }
     X0 = nX0;
     X1 = nX1;
     cv = ncv;
+    nX0 = fX0;
+    nX1 = fX1;
+    ncv = fcv;
   }
-  flush2d<T, W>(acc, cur0, cur1, nf0, nf1, grid);
+  if (cur0 >= 0) flush2d<T, W>(acc, cur0, cur1, nf0, nf1, grid);
 }
 
 // ------------------------------------------------------------------ generic d (2-D wide kernels, 3-D): per-point REDs
-// Points are still cell-sorted, so the reductions of neighbouring threads land in the same L2 lines.
+// Points are still cell-sorted, so the reductions of neighbouring slots land in the same L2 lines.
 template <typename T, int W, int D, bool HAS_C>
 __global__ void __launch_bounds__(256)
 spread_direct_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* __restrict__ xs2,
-                     const uint32_t* __restrict__ perm, const T* __restrict__ c, int64_t cstride, int64_t N,
-                     int nf0, int nf1, int nf2, T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
+                     const T* __restrict__ cs, int64_t npos, int nf0, int nf1, int nf2, T* __restrict__ grid,
+                     const __grid_constant__ ESDev<T> es) {
   int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
+  if (n >= npos) return;
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
-  T cv = HAS_C ? c[(int64_t)perm[n] * cstride] : T(1);
-  T k0[W], k1[W], k2[W];
   T X0 = xs0[n];
+  if (X0 < T(0)) return;
+  T cv = HAS_C ? cs[n] : T(1);
+  T k0[W], k1[W], k2[W];
   int c0 = (int)X0;
   es_eval<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
   T X1 = xs1[n];
@@ -200,69 +212,55 @@ spread_direct_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const
   }
 }
 
-static int pick_points_per_thread(int64_t N) {
-  // aim for >= 2 full waves of 148 SMs x 256 threads, and long register runs when N is large
-  int64_t P = N / (148 * 256 * 4);
-  if (P < 1) P = 1;
-  if (P > 64) P = 64;
-  return (int)P;
-}
-
 template <typename T, int W>
-static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* c, int64_t cstride, T* grid,
-                     cudaStream_t st) {
+static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st) {
   ESDev<T> es;
   es_to_dev<T>(k, es);
-  const int64_t N = sp.N;
   const T* x0 = (const T*)sp.xs[0];
   const T* x1 = (const T*)sp.xs[1];
   const T* x2 = (const T*)sp.xs[2];
   constexpr int kRegMaxW = sizeof(T) == 8 ? 9 : 10;
+  const int nt = (int)sp.ntiles;
   if (sp.dim == 1) {
-    int P = pick_points_per_thread(N);
-    int nb = div_up(div_up(N, P), 256);
-    if (c)
-      spread1d_kernel<T, W, true><<<nb, 256, 0, st>>>(x0, sp.perm, c, cstride, N, P, (int)sp.nf[0], grid, es);
+    if (cs)
+      spread1d_kernel<T, W, true><<<nt, kTileThreads, 0, st>>>(x0, cs, sp.P, (int)sp.nf[0], grid, es);
     else
-      spread1d_kernel<T, W, false><<<nb, 256, 0, st>>>(x0, sp.perm, c, cstride, N, P, (int)sp.nf[0], grid, es);
+      spread1d_kernel<T, W, false><<<nt, kTileThreads, 0, st>>>(x0, cs, sp.P, (int)sp.nf[0], grid, es);
   } else if (sp.dim == 2) {
     if constexpr (W <= kRegMaxW) {
-      int P = pick_points_per_thread(N);
-      int nb = div_up(div_up(N, P), 256);
-      if (c)
+      if (cs)
         spread2d_kernel<T, W, true>
-            <<<nb, 256, 0, st>>>(x0, x1, sp.perm, c, cstride, N, P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
+            <<<nt, kTileThreads, 0, st>>>(x0, x1, cs, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
       else
         spread2d_kernel<T, W, false>
-            <<<nb, 256, 0, st>>>(x0, x1, sp.perm, c, cstride, N, P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
+            <<<nt, kTileThreads, 0, st>>>(x0, x1, cs, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
     } else {
-      int nb = div_up(N, 256);
-      if (c)
-        spread_direct_kernel<T, W, 2, true><<<nb, 256, 0, st>>>(x0, x1, x2, sp.perm, c, cstride, N, (int)sp.nf[0],
-                                                                (int)sp.nf[1], 1, grid, es);
+      int nb = div_up(sp.npos, 256);
+      if (cs)
+        spread_direct_kernel<T, W, 2, true>
+            <<<nb, 256, 0, st>>>(x0, x1, x2, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, es);
       else
-        spread_direct_kernel<T, W, 2, false><<<nb, 256, 0, st>>>(x0, x1, x2, sp.perm, c, cstride, N,
-                                                                 (int)sp.nf[0], (int)sp.nf[1], 1, grid, es);
+        spread_direct_kernel<T, W, 2, false>
+            <<<nb, 256, 0, st>>>(x0, x1, x2, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, es);
     }
   } else {
-    int nb = div_up(N, 256);
-    if (c)
-      spread_direct_kernel<T, W, 3, true><<<nb, 256, 0, st>>>(x0, x1, x2, sp.perm, c, cstride, N, (int)sp.nf[0],
-                                                              (int)sp.nf[1], (int)sp.nf[2], grid, es);
+    int nb = div_up(sp.npos, 256);
+    if (cs)
+      spread_direct_kernel<T, W, 3, true>
+          <<<nb, 256, 0, st>>>(x0, x1, x2, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, es);
     else
-      spread_direct_kernel<T, W, 3, false><<<nb, 256, 0, st>>>(x0, x1, x2, sp.perm, c, cstride, N, (int)sp.nf[0],
-                                                               (int)sp.nf[1], (int)sp.nf[2], grid, es);
+      spread_direct_kernel<T, W, 3, false>
+          <<<nb, 256, 0, st>>>(x0, x1, x2, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, es);
   }
   EFGP_CUDA(cudaGetLastError());
 }
 
 template <typename T>
-static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* c, int64_t cstride, T* grid,
-                     cudaStream_t st) {
+static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st) {
   switch (k.W) {
 #define EFGP_CASE(w) \
   case w:            \
-    launch_w<T, w>(sp, k, c, cstride, grid, st); \
+    launch_w<T, w>(sp, k, cs, grid, st); \
     break;
     EFGP_CASE(2) EFGP_CASE(3) EFGP_CASE(4) EFGP_CASE(5) EFGP_CASE(6) EFGP_CASE(7) EFGP_CASE(8) EFGP_CASE(9)
     EFGP_CASE(10) EFGP_CASE(11) EFGP_CASE(12) EFGP_CASE(13) EFGP_CASE(14) EFGP_CASE(15) EFGP_CASE(16)
@@ -272,14 +270,13 @@ static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* c, int6
   }
 }
 
-void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* c, int64_t cstride, void* grid,
-                   cudaStream_t st) {
+void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, void* grid, cudaStream_t st) {
   if (sp.N == 0) return;
   EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
   if (sp.dtype == 0)
-    launch_t<float>(sp, k, (const float*)c, cstride, (float*)grid, st);
+    launch_t<float>(sp, k, (const float*)cs, (float*)grid, st);
   else
-    launch_t<double>(sp, k, (const double*)c, cstride, (double*)grid, st);
+    launch_t<double>(sp, k, (const double*)cs, (double*)grid, st);
 }
 
 }  // namespace efgp
