@@ -12,7 +12,7 @@ LIB = os.path.join(OUT_DIR, "libefgp_b200.so")
 OBJ_DIR = os.path.join(HERE, "build")
 
 SOURCES = ["es_kernel.cpp", "pool.cpp", "points.cu", "spread.cu", "interp.cu", "nufft.cu", "toeplitz.cu", "cg.cu", "capi.cu"]
-HEADERS = ["common.cuh", "nufft.cuh", "toeplitz.cuh", os.path.join("..", "..", "include", "efgp_b200.h")]
+HEADERS = ["common.cuh", "nufft.cuh", "toeplitz.cuh", "stream_ring.cuh", os.path.join("..", "..", "include", "efgp_b200.h")]
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

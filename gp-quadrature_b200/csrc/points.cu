@@ -126,8 +126,10 @@ static int pick_points_per_thread(int64_t N) {
   // >= 4 waves of 148 SMs x 256 threads when N allows, and long register runs when N is large
   int64_t P = N / (148 * 256 * 4);
   if (P < 1) P = 1;
-  if (P > 64) P = 64;
-  return (int)P;
+  if (P > 128) P = 128;
+  int p2 = 1;
+  while (p2 * 2 <= P) p2 *= 2;   // power of two: the gather kernel reads the sort output in 8-wide chunks
+  return p2;
 }
 
 template <typename T>
@@ -148,7 +150,7 @@ static void build_t(SortedPoints& sp, const T* x, int64_t N, int dim, double h, 
   int bits = 1;
   while ((1ull << bits) < (unsigned long long)cells) ++bits;
 
-  sp.P = pick_points_per_thread(N);
+  sp.P = dim == 3 ? 1 : pick_points_per_thread(N);  // 3-D uses the per-point kernels: keep rank order
   const int64_t tile_len = (int64_t)kTileThreads * sp.P;
   sp.ntiles = (N + tile_len - 1) / tile_len;
   sp.npos = sp.ntiles * tile_len;

@@ -13,6 +13,7 @@
 // so flushes are ~1/100 of the FMA work at the headline size and degrade gracefully to one
 // flush per point for sparse cases.
 #include "nufft.cuh"
+#include "stream_ring.cuh"
 
 namespace efgp {
 
@@ -110,31 +111,37 @@ template <typename T, int W, bool HAS_C>
 __global__ void __launch_bounds__(kTileThreads, 1)
 spread2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* __restrict__ cs, int P, int nf0,
                 int nf1, T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
-  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
+  constexpr int NA = HAS_C ? 3 : 2;
+  constexpr int S = kRingStages;
+  __shared__ T ring[S][NA][kTileThreads];
+  const int t = threadIdx.x;
+  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + t;
+  auto issue = [&](int j) {
+    if (j < P) {
+      const int64_t pos = base + (int64_t)j * kTileThreads;
+      const int s = j % S;
+      cp_async_word<sizeof(T)>(&ring[s][0][t], xs0 + pos);
+      cp_async_word<sizeof(T)>(&ring[s][1][t], xs1 + pos);
+      if (HAS_C) cp_async_word<sizeof(T)>(&ring[s][NA - 1][t], cs + pos);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int j = 0; j < S - 1; ++j) issue(j);
   T acc[W][W];
 #pragma unroll
   for (int i = 0; i < W; ++i)
 #pragma unroll
     for (int j = 0; j < W; ++j) acc[i][j] = 0;
   int cur0 = -1, cur1 = -1;
-  // two-deep software prefetch of the (coalesced) point stream
-  T X0 = xs0[base], X1 = xs1[base];
-  T cv = HAS_C ? cs[base] : T(1);
-  T nX0 = T(-1), nX1 = T(0), ncv = T(1);
-  if (P > 1) {
-    nX0 = xs0[base + kTileThreads];
-    nX1 = xs1[base + kTileThreads];
-    if (HAS_C) ncv = cs[base + kTileThreads];
-  }
   for (int j = 0; j < P; ++j) {
+    issue(j + S - 1);
+    cp_async_wait<S - 1>();
+    const int s = j % S;
+    const T X0 = ring[s][0][t];
     if (X0 < T(0)) break;
-    T fX0 = T(-1), fX1 = T(0), fcv = T(1);
-    if (j + 2 < P) {
-      const int64_t pos = base + (int64_t)(j + 2) * kTileThreads;
-      fX0 = xs0[pos];
-      fX1 = xs1[pos];
-      if (HAS_C) fcv = cs[pos];
-    }
+    const T X1 = ring[s][1][t];
+    const T cv = HAS_C ? ring[s][NA - 1][t] : T(1);
     int c0 = (int)X0, c1 = (int)X1;
     if (c0 != cur0 || c1 != cur1) {
       if (cur0 >= 0) flush2d<T, W>(acc, cur0, cur1, nf0, nf1, grid);
@@ -150,13 +157,8 @@ spread2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* _
 #pragma unroll
       for (int jj = 0; jj < W; ++jj) acc[i][jj] = fma(a, k1[jj], acc[i][jj]);
     }
-    X0 = nX0;
-    X1 = nX1;
-    cv = ncv;
-    nX0 = fX0;
-    nX1 = fX1;
-    ncv = fcv;
   }
+  cp_async_wait<0>();
   if (cur0 >= 0) flush2d<T, W>(acc, cur0, cur1, nf0, nf1, grid);
 }
 
