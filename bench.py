@@ -1,0 +1,343 @@
+#!/usr/bin/env python
+"""Headline benchmark: 2-D squared-exponential EFGP posterior-mean solve on N = 1e8 synthetic points
+(BASELINE.json configs[2]), eps = 1e-4, fp64.
+
+One step = the whole hot path on one batch of points: bin-sort of x, the F^*1 Toeplitz generator
+(type-1 at eps 6e-8), ws * F^* y (type-1), Toeplitz spectrum, Jacobi-preconditioned CG for beta, and
+the posterior mean Re F(ws beta) at the N training points (type-2)  --  exactly
+EFGPND(x, y, ...).predict(x, return_variance=False) of the reference (efgpnd.py:710-822, 918-922).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--npts N]
+
+Multi-GPU (torchrun, one rank per GPU): the N points are sharded over the ranks ("strong" scaling:
+total N fixed), each rank spreads its shard, ONE NCCL all-reduce sums the two mode grids, every
+rank solves the same M x M system and interpolates at its own points.
+
+`--impl reference` times the reference's CPU path (the oracle's restatement of efgpnd.py with the
+C/OpenMP NUFFT of oracle/cnufft.c standing in for FINUFFT, which is not installable here) on a
+bounded sample of the same workload, on all host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "gp-quadrature_b200")
+for _p in (PKG, ROOT):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "efgp_posterior_mean_solve_throughput"
+UNIT = "Mpts/s"
+ELL, VAR, SIG2, EPS, NUFFT_EPS, CG_TOL = 0.05, 1.0, 0.1, 1e-4, 1e-4, 1e-4
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--npts", type=float, default=1e8, help="total number of points (all ranks)")
+    ap.add_argument("--cpu-sample", type=float, default=4e6, help="points in the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def synth(n, d, seed, device, dtype):
+    """x ~ U[-1,1]^d, y = analytic field + N(0, 0.2^2)  (test_timing_profiling.py:25-44 recipe)."""
+    import torch
+    g = torch.Generator(device=device).manual_seed(seed)
+    x = torch.rand(n, d, dtype=dtype, device=device, generator=g) * 2 - 1
+    r2 = (x * x).sum(1)
+    y = (torch.sin(3 * x[:, 0]) * torch.cos(4 * x[:, 1])
+         + 0.5 * torch.exp(-((x[:, 0] - 0.3) ** 2 + (x[:, 1] + 0.3) ** 2) / 0.3)
+         + 0.7 * torch.sin(2 * torch.pi * r2))
+    y = y + 0.2 * torch.randn(n, dtype=dtype, device=device, generator=g)
+    return x, y
+
+
+# ----------------------------------------------------------------------------- CPU reference arm
+def cpu_solve_step(x, y):
+    """One posterior-mean solve with the oracle's restatement of the reference + the fast CPU NUFFT."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import efgp_oracle as O
+    import fast_nufft as F
+    kern = O.OracleKernel("se", 2, ELL, VAR)
+    f = O.fit(x, y, kern, SIG2, EPS, NUFFT_EPS, cg_tol=CG_TOL, backend=F)
+    mean = O.predict_mean(f, x, NUFFT_EPS, backend=F)
+    return f, mean
+
+
+def cpu_baseline(n_sample, reps):
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import fast_nufft as F
+    x, y = synth(int(n_sample), 2, 1234, "cpu", torch.float64)
+    cpu_solve_step(x[:20000], y[:20000])  # warm the libraries
+    best = float("inf")
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        f, _ = cpu_solve_step(x, y)
+        best = min(best, time.perf_counter() - t0)
+    cores = max(F.num_threads(), torch.get_num_threads())
+    return {"value": n_sample / best / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{int(n_sample)} of the workload's points, full solve (2 type-1, CG {f.iters} its, 1 type-2), "
+                      f"best of {reps}; oracle restatement of efgpnd.py + C/OpenMP ES-kernel NUFFT (FINUFFT absent)",
+            "seconds": best, "os_cpu_count": os.cpu_count()}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    reps = max(1, args.steps)
+    n_s = args.cpu_sample
+    import torch
+    x, y = synth(int(n_s), 2, 1234, "cpu", torch.float64)
+    for _ in range(min(args.warmup, 1)):
+        cpu_solve_step(x[:200000], y[:200000])
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        f, _ = cpu_solve_step(x, y)
+    dt = (time.perf_counter() - t0) / reps
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import fast_nufft as F
+    v = n_s / dt / 1e6
+    cores = max(F.num_threads(), torch.get_num_threads())
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": reps,
+            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, 1, f.mtot),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"{int(n_s)} points per step (bounded sample of the N={int(args.npts)} workload)",
+                             "os_cpu_count": os.cpu_count()},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, world, mtot=None):
+    return {"workload": "BASELINE.json configs[2]: 2-D squared-exponential EFGP posterior-mean solve "
+                        "(sort + F^*1 @6e-8 + F^*y + Toeplitz + PCG + mean at the N training points)",
+            "N_total": int(args.npts), "d": 2, "lengthscale": ELL, "variance": VAR, "sigmasq": SIG2, "eps": EPS,
+            "nufft_eps": NUFFT_EPS, "cg_tolerance": CG_TOL, "mtot": mtot,
+            "parallelism": f"points sharded over {world} GPU(s), NCCL all-reduce of the mode grids" if world > 1
+            else "single GPU",
+            "l2_policy": "inputs (>= 2.4 GB per step) are larger than the 126 MB L2; the sort is redone every step"}
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons, pw = [], [], set(), []
+        for line in self.f.read().splitlines():
+            c = [t.strip() for t in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1]))
+                mx.append(float(c[2]))
+                pw.append(float(c[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        hi = sorted(sm)[len(sm) // 2:]            # samples under load = the upper half
+        return {"sm_mhz": sorted(hi)[len(hi) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(pw)}
+
+
+# ----------------------------------------------------------------------------- algorithmic bytes
+def algorithmic_bytes(stage, n, d=2, word=8):
+    """Bytes one launch of `stage` must move for n points."""
+    if stage.startswith("spread"):
+        return n * word * (d + (0 if stage.endswith("_ones") else 1))      # coordinates (+ real strength)
+    if stage.startswith("interp"):
+        return n * (word * d + 4 + word)                                    # coordinates + perm + real output
+    if stage == "sort.key_kernel":
+        return n * (word * d + 8)                                           # x -> key + index
+    if stage == "sort.gather_kernel":
+        return n * (4 + word * d + word * d + 4)                            # rank -> x gather -> sorted coords + perm
+    if stage == "permute_strengths":
+        return n * (4 + word + word)
+    return None
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback for the product path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import efgpnd
+    from efgp_b200 import _lib
+    from kernels.squared_exponential import SquaredExponential
+
+    n_total = int(args.npts)
+    n_loc = n_total // world + (1 if rank < n_total % world else 0)
+    x, y = synth(n_loc, 2, 1000 + rank, dev, torch.float64)
+    opts = {"cg_tolerance": CG_TOL, "shard_points": world > 1}
+    stats = {}
+
+    def solve(xd, yd):
+        efgpnd._PLAN_CACHE.clear()                 # a step starts from raw points: sort included
+        kern = SquaredExponential(dimension=2, init_lengthscale=ELL, init_variance=VAR)
+        model = efgpnd.EFGPND(xd, yd, kern, sigmasq=SIG2, eps=EPS, nufft_eps=NUFFT_EPS, opts=opts,
+                              estimate_params=False)
+        mean, _ = model.predict(xd, return_variance=False)
+        stats.update(model.last_fit_stats)
+        return mean
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        mean = solve(x, y)
+    barrier()
+
+    # ---- device-resident timing (value) with per-stage timing inside the library
+    sampler = ClockSampler(local) if rank == 0 else None
+    _lib.timing_enable(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        mean = solve(x, y)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    stages = _lib.timing_report()
+    _lib.timing_enable(False)
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    check = float(mean.double().square().mean().sqrt().item())
+
+    # ---- end to end: pinned host buffers -> device -> solve -> result back on the host, every step
+    e2e = None
+    if not args.no_e2e:
+        xh = torch.empty((n_loc, 2), dtype=torch.float64, pin_memory=True)
+        yh = torch.empty((n_loc,), dtype=torch.float64, pin_memory=True)
+        mh = torch.empty((n_loc,), dtype=torch.float64, pin_memory=True)
+        xh.copy_(x)
+        yh.copy_(y)
+        xd, yd = torch.empty_like(x), torch.empty_like(y)
+
+        def e2e_step():
+            xd.copy_(xh, non_blocking=True)
+            yd.copy_(yh, non_blocking=True)
+            m = solve(xd, yd)
+            mh.copy_(m, non_blocking=True)
+
+        e2e_step()
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            e2e_step()
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1) / args.steps], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e2e = float(t.item())
+        e2e = {"value": n_total / ms_e2e / 1e3, "unit": UNIT, "ms_per_step": ms_e2e,
+               "h2d_bytes_per_step": (xh.numel() + yh.numel()) * 8 * world,
+               "d2h_bytes_per_step": mh.numel() * 8 * world,
+               "api": "EFGPND(x, y, SquaredExponential, ...).predict(x, return_variance=False) on buffers copied "
+                      "from pinned host memory; posterior mean copied back"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant hand-written kernel (live CUDA-event durations from the library)
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    own = {k: v for k, v in stages.items() if algorithmic_bytes(k, n_loc) is not None and v["launches"] > 0}
+    per_stage = {}
+    for k, v in stages.items():
+        ent = {"ms_per_step": v["ms"] / args.steps, "launches_per_step": v["launches"] / args.steps}
+        ab = algorithmic_bytes(k, n_loc)
+        if ab is not None and v["launches"] > 0:
+            dur = v["ms"] / v["launches"]
+            ent["achieved_gbs"] = ab / dur / 1e6
+            ent["hbm_frac"] = ent["achieved_gbs"] / peak
+        per_stage[k] = ent
+    roofline = None
+    if own:
+        top = max(own, key=lambda k: own[k]["ms"])
+        dur = own[top]["ms"] / own[top]["launches"]
+        ach = algorithmic_bytes(top, n_loc) / dur / 1e6
+        roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "traffic": None, "peak_source": peak_src, "avg_launch_ms": dur,
+                    "algorithmic_bytes_per_launch": algorithmic_bytes(top, n_loc)}
+    launches = sum(v["launches"] for v in stages.values())
+
+    line = {"metric": METRIC, "value": n_total / ms / 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, world, stats.get("mtot")),
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+            "stages": per_stage, "mean_cg_iters": stats.get("mean_cg_iters"), "result_rms": check}
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args.cpu_sample, 2)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

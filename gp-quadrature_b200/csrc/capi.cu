@@ -32,6 +32,24 @@ int efgp_version(void) { return 100; }
 
 const char* efgp_last_error(void) { return efgp::g_last_error.c_str(); }
 
+/* per-stage device timing (bench / diagnostics) */
+int efgp_timing_enable(int on) {
+  EFGP_TRY({ efgp::timing_enable(on); })
+}
+
+int efgp_timing_report(char* buf, int64_t cap) {
+  EFGP_TRY({
+    EFGP_CHECK(buf != nullptr && cap > 0, "null report buffer");
+    std::string r = efgp::timing_report();
+    if ((int64_t)r.size() + 1 > cap) r.resize((size_t)cap - 1);
+    memcpy(buf, r.c_str(), r.size() + 1);
+  })
+}
+
+int efgp_pool_trim(void) {
+  EFGP_TRY({ efgp::pool_trim(); })
+}
+
 int efgp_nufft_create(efgp_nufft** out, int dim, int dtype) {
   EFGP_TRY({
     EFGP_CHECK(out != nullptr, "null output handle");

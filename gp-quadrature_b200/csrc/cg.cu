@@ -351,8 +351,11 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   // Ap = A x0  (generic apply writes through P/Q as well)
   toeplitz_apply(t, x, B, ws, sigmasq, mode, Ap, st);
   dim3 grid(s.NC, B), gf(div_up(t.Ftot, 256), B);
-  cg_init_kernel<T><<<grid, 256, 0, st>>>(b, Ap, minv, r, p, M, s);
-  cg_init_scal_kernel<<<div_up(B, 128), 128, 0, st>>>(s);
+  {
+    ScopedStage stg_init("cg.init", st, 2);
+    cg_init_kernel<T><<<grid, 256, 0, st>>>(b, Ap, minv, r, p, M, s);
+    cg_init_scal_kernel<<<div_up(B, 128), 128, 0, st>>>(s);
+  }
   EFGP_CUDA(cudaGetLastError());
 
   int* h_counters = nullptr;
@@ -361,8 +364,10 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   h_counters[1] = -1;
   int it = 0;
   int check = 4;
+  ScopedStage stg("cg.iterations", st, 0);
   while (it < max_iter) {
     int until = std::min(max_iter, it + check);
+    stg.add_launches(4 * (until - it));
     for (; it < until; ++it) {
       cg_A_kernel<T><<<grid, 256, 0, st>>>(p, r, minv, w, g, it, tol, early, batched, P, s);
       fft_pair_begin<T>(t, B, P, Q, st);

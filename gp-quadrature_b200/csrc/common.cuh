@@ -88,6 +88,19 @@ inline int div_up(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 // Process-wide caching pool for large device scratch (sort temporaries, sorted point sets):
 // cudaMalloc/cudaFree of GB-sized blocks costs milliseconds and synchronises the device, and the
 // EFGP loop rebuilds its plans every hyperparameter step.
+// Optional per-stage device timing (timing.cpp): a ScopedStage records CUDA events on `st` around the
+// launches issued during its lifetime when timing is enabled, and costs one branch otherwise.
+bool timing_on();
+void timing_enable(int on);
+std::string timing_report();
+struct ScopedStage {
+  ScopedStage(const char* name, cudaStream_t st, int launches = 1);
+  ~ScopedStage();
+  void add_launches(int n);
+  cudaStream_t st_;
+  long long idx_;
+};
+
 void* pool_alloc(size_t bytes);
 void pool_free(void* p);
 void pool_trim();

@@ -365,7 +365,10 @@ static void type1_t(Nufft& nu, const void* strengths, int is_complex, int batch,
   C* spec = (C*)nu.spec.get((size_t)chunk * ncomp * slab * sizeof(C));
   for (int b0 = 0; b0 < batch; b0 += chunk) {
     int nb = std::min(chunk, batch - b0);
-    EFGP_CUDA(cudaMemsetAsync(fine, 0, (size_t)nb * ncomp * cells * sizeof(T), st));
+    {
+      ScopedStage stg("type1.memset_fine", st, 0);
+      EFGP_CUDA(cudaMemsetAsync(fine, 0, (size_t)nb * ncomp * cells * sizeof(T), st));
+    }
     T* cs = strengths ? (T*)nu.cperm.get((size_t)gc.sp->npos * sizeof(T)) : nullptr;
     for (int b = 0; b < nb; ++b) {
       for (int comp = 0; comp < ncomp; ++comp) {
@@ -377,11 +380,15 @@ static void type1_t(Nufft& nu, const void* strengths, int is_complex, int batch,
       }
     }
     cufftHandle plan = nu.fft.get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_R2C : CUFFT_D2Z, nb * ncomp, st);
-    if (sizeof(T) == 4)
-      EFGP_CUFFT(cufftExecR2C(plan, (cufftReal*)fine, (cufftComplex*)spec));
-    else
-      EFGP_CUFFT(cufftExecD2Z(plan, (cufftDoubleReal*)fine, (cufftDoubleComplex*)spec));
+    {
+      ScopedStage stg("type1.cufft_r2c", st, 0);
+      if (sizeof(T) == 4)
+        EFGP_CUFFT(cufftExecR2C(plan, (cufftReal*)fine, (cufftComplex*)spec));
+      else
+        EFGP_CUFFT(cufftExecD2Z(plan, (cufftDoubleReal*)fine, (cufftDoubleComplex*)spec));
+    }
     int64_t tot = g.M * nb;
+    ScopedStage stg("type1.deconv_kernel", st);
     deconv_kernel<T><<<div_up(tot, 256), 256, 0, st>>>(spec, ncomp, nb, g, (const T*)dinv[0], (const T*)dinv[1],
                                                        (const T*)dinv[2], (const T*)scale,
                                                        (C*)out + (int64_t)b0 * g.M);
@@ -412,15 +419,21 @@ static void type2_t(Nufft& nu, const void* modes, int batch, const int64_t* n, d
   for (int b0 = 0; b0 < batch; b0 += chunk) {
     int nb = std::min(chunk, batch - b0);
     int64_t tot = slab * nb * ncomp;
+    {
+    ScopedStage stg("type2.precorrect_kernel", st);
     precorrect_kernel<T><<<div_up(tot, 256), 256, 0, st>>>((const C*)modes + (int64_t)b0 * g.M, ncomp, nb, g,
                                                            (const T*)dinv[0], (const T*)dinv[1],
                                                            (const T*)dinv[2], (const T*)scale, spec);
+    }
     EFGP_CUDA(cudaGetLastError());
     cufftHandle plan = nu.fft.get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_C2R : CUFFT_Z2D, nb * ncomp, st);
-    if (sizeof(T) == 4)
-      EFGP_CUFFT(cufftExecC2R(plan, (cufftComplex*)spec, (cufftReal*)fine));
-    else
-      EFGP_CUFFT(cufftExecZ2D(plan, (cufftDoubleComplex*)spec, (cufftDoubleReal*)fine));
+    {
+      ScopedStage stg("type2.cufft_c2r", st, 0);
+      if (sizeof(T) == 4)
+        EFGP_CUFFT(cufftExecC2R(plan, (cufftComplex*)spec, (cufftReal*)fine));
+      else
+        EFGP_CUFFT(cufftExecZ2D(plan, (cufftDoubleComplex*)spec, (cufftDoubleReal*)fine));
+    }
     for (int b = 0; b < nb; ++b)
       for (int comp = 0; comp < ncomp; ++comp)
         launch_interp(*gc.sp, gc.ker, fine + (int64_t)(b * ncomp + comp) * cells,

@@ -115,6 +115,7 @@ __global__ void __launch_bounds__(256) permute_kernel(const T* __restrict__ c, i
 void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, void* cs, cudaStream_t st) {
   if (sp.npos == 0) return;
   int nb = div_up(sp.npos, 256);
+  ScopedStage stg("permute_strengths", st);
   if (sp.dtype == 0)
     permute_kernel<float><<<nb, 256, 0, st>>>((const float*)c, cstride, sp.perm, sp.npos, (float*)cs);
   else
@@ -161,24 +162,33 @@ static void build_t(SortedPoints& sp, const T* x, int64_t N, int dim, double h, 
   uint32_t* idx_out = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
   sp.perm = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)sp.npos);
   int nb = div_up(N, 256);
+  {
+  ScopedStage stg("sort.key_kernel", st);
   if (dim == 1) key_kernel<T, 1><<<nb, 256, 0, st>>>(x, N, p, keys_in, idx_in);
   if (dim == 2) key_kernel<T, 2><<<nb, 256, 0, st>>>(x, N, p, keys_in, idx_in);
   if (dim == 3) key_kernel<T, 3><<<nb, 256, 0, st>>>(x, N, p, keys_in, idx_in);
+  }
   EFGP_CUDA(cudaGetLastError());
   size_t tmp_bytes = 0;
   EFGP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, idx_in, idx_out, (int)N, 0,
                                             bits, st));
   void* tmp = pool_alloc(tmp_bytes);
-  EFGP_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, idx_in, idx_out, (int)N, 0, bits,
-                                            st));
+  {
+    ScopedStage stg("sort.cub_radix_sort_pairs", st, 0);
+    EFGP_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, idx_in, idx_out, (int)N, 0, bits,
+                                              st));
+  }
   for (int a = 0; a < dim; ++a) sp.xs[a] = pool_alloc(sizeof(T) * (size_t)sp.npos);
   T* o0 = (T*)sp.xs[0];
   T* o1 = (T*)sp.xs[1];
   T* o2 = (T*)sp.xs[2];
   int nbp = div_up(sp.npos, 256);
+  {
+  ScopedStage stg("sort.gather_kernel", st);
   if (dim == 1) gather_kernel<T, 1><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, sp.npos);
   if (dim == 2) gather_kernel<T, 2><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, sp.npos);
   if (dim == 3) gather_kernel<T, 3><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, sp.npos);
+  }
   EFGP_CUDA(cudaGetLastError());
   // scratch goes back to the pool; later users run on the same stream, so ordering is preserved
   pool_free(tmp);

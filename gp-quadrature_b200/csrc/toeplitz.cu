@@ -152,6 +152,7 @@ static void create_t(Toeplitz& t, const void* v, cudaStream_t st) {
   EFGP_CUDA(cudaMalloc(&t.vhat, sizeof(C) * (size_t)t.Ftot));
   TzGeom g = make_tz_geom(t);
   for (int a = 0; a < kMaxDim; ++a) g.n[a] = (int)t.L[a];
+  ScopedStage stg("toeplitz.create", st, 2);
   tz_pad_v_kernel<C><<<div_up(t.Ftot, 256), 256, 0, st>>>((const C*)v, g, (C*)t.vhat);
   EFGP_CUDA(cudaGetLastError());
   cufftHandle plan = t.fft.get(t.dim, t.F, sizeof(T) == 4 ? CUFFT_C2C : CUFFT_Z2Z, 1, st);
@@ -247,6 +248,7 @@ static void apply_t(Toeplitz& t, const void* x, int batch, const void* ws, doubl
     const C* xb = (const C*)x + (int64_t)b0 * t.M;
     C* yb = (C*)y + (int64_t)b0 * t.M;
     dim3 gm(div_up(t.M, 256), nb), gf(div_up(t.Ftot, 256), nb);
+    ScopedStage stg("toeplitz.apply", st, 3);
     tz_pad_x_kernel<T><<<gm, 256, 0, st>>>(xb, w, g, nb, nullptr, P);
     fft_pair_begin<T>(t, nb, P, Q, st);
     tz_mul_kernel<T><<<gf, 256, 0, st>>>(Q, (const C*)t.vhat, t.Ftot, nullptr);

@@ -19,6 +19,9 @@ vp = ctypes.c_void_p
 _SIGNATURES = {
     "efgp_version": (ctypes.c_int, []),
     "efgp_last_error": (ctypes.c_char_p, []),
+    "efgp_timing_enable": (ctypes.c_int, [ctypes.c_int]),
+    "efgp_timing_report": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_int64]),
+    "efgp_pool_trim": (ctypes.c_int, []),
     "efgp_nufft_create": (ctypes.c_int, [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_int]),
     "efgp_nufft_set_points": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_double, c_dblp, vp]),
     "efgp_nufft_destroy": (None, [vp]),
@@ -74,3 +77,19 @@ def i64_array(vals):
 def dbl_array(vals):
     vals = [float(v) for v in vals]
     return (ctypes.c_double * len(vals))(*vals)
+
+
+def timing_enable(on=True):
+    """Start (and reset) / stop per-stage device timing inside the library."""
+    check(lib().efgp_timing_enable(1 if on else 0))
+
+
+def timing_report():
+    """{stage: {"scopes": n, "launches": n, "ms": total}} since timing_enable(True); synchronises."""
+    buf = ctypes.create_string_buffer(1 << 16)
+    check(lib().efgp_timing_report(buf, len(buf)))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, scopes, launches, ms = line.rsplit(",", 3)
+        out[name] = {"scopes": int(scopes), "launches": int(launches), "ms": float(ms)}
+    return out

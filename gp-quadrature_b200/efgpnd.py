@@ -44,6 +44,20 @@ def _as_float(v):
     return float(v)
 
 
+def _point_shard_group(opts):
+    """Process group over which the training points are sharded, or None.  opts["shard_points"] is
+    True (default group) or a torch.distributed group; with it every rank passes ITS shard of (x, y)
+    and the type-1 results are summed over ranks (linearity in the points)."""
+    g = opts.get("shard_points", None) if opts else None
+    if not g:
+        return None
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        raise EfgpError("opts['shard_points'] needs an initialised torch.distributed process group")
+    group = dist.group.WORLD if g is True else g
+    return group if dist.get_world_size(group) > 1 else None
+
+
 # ----------------------------------------------------------------------------- NUFFT
 _PLAN_CACHE: "OrderedDict[tuple, _ops.NufftPlan]" = OrderedDict()
 _PLAN_CACHE_SIZE = 3
@@ -727,7 +741,14 @@ class EFGPND(nn.Module):
         if x.ndim == 1:
             x = x[:, None]
         N, d = x.shape
-        L = float(torch.max(torch.max(x, dim=0).values - torch.min(x, dim=0).values).item())
+        group = _point_shard_group(self.opts)
+        if group is None:
+            L = float(torch.max(torch.max(x, dim=0).values - torch.min(x, dim=0).values).item())
+        else:
+            # points are sharded over the ranks: the box is the union of the shards' boxes
+            ext = torch.cat([torch.max(x, dim=0).values, -torch.min(x, dim=0).values])
+            torch.distributed.all_reduce(ext, op=torch.distributed.ReduceOp.MAX, group=group)
+            L = float(torch.max(ext[:d] + ext[d:]).item())
         if L <= 1e-9:
             L = 1.0
         xis_1d, h_float, mtot = get_xis(kernel_obj=self.kernel, eps=self.eps, L=L, use_integral=True,
@@ -745,6 +766,13 @@ class EFGPND(nn.Module):
         v_kernel = compute_convolution_vector_vectorized_dD(m_conv, x, h_float).to(dtype=cdtype)
         nufft_op = NUFFT(x, xcen, h_float, nufft_eps, cdtype=cdtype, device=device)
         rhs = nufft_op.type1(y, OUT, scale=ws_r).reshape(-1)                     # ws * F^* y, fused
+        if group is not None:
+            # F^*1 and F^*y are sums over points: one NCCL all-reduce of the two (cropped, deconvolved)
+            # mode grids replaces the fine-grid exchange; every rank then solves the same M-sized system.
+            packed = torch.cat([v_kernel.reshape(-1), rhs])
+            torch.distributed.all_reduce(torch.view_as_real(packed), op=torch.distributed.ReduceOp.SUM, group=group)
+            v_kernel = packed[: v_kernel.numel()].reshape(v_kernel.shape)
+            rhs = packed[v_kernel.numel():]
         toeplitz = ToeplitzND(v_kernel, force_pow2=True)
         A_mean = create_A_mean(ws, toeplitz, s2, cdtype)
         center = tuple((s - 1) // 2 for s in v_kernel.shape)

@@ -29,6 +29,14 @@ typedef struct efgp_toeplitz efgp_toeplitz;
 int efgp_version(void);
 const char* efgp_last_error(void);
 
+/* ---- diagnostics (no reference counterpart; the reference's torch.profiler ranges, efgpnd.py:46-59).
+ * efgp_timing_enable(1) starts recording CUDA events around every launch group the library issues;
+ * efgp_timing_report writes "stage,scopes,launches,total_ms\n" lines (synchronises the device).
+ * efgp_pool_trim releases the cached device scratch blocks. */
+int efgp_timing_enable(int on);
+int efgp_timing_report(char* buf, int64_t cap);
+int efgp_pool_trim(void);
+
 /* ---- NUFFT: replaces class NUFFT (efgpnd.py:1423-1549) and the pytorch_finufft calls under it */
 
 /* NUFFT.__init__ (efgpnd.py:1432-1452): phi = 2*pi*h*(x - xcen).  x is (N, dim) row-major. */

@@ -100,3 +100,38 @@ def test_model_matches_reference(case):
     if f64:
         assert abs(st["mean_cg_iters"] - int(g["grad_T4_iters"][0])) <= 1
         assert abs(st["trace_cg_iters"] - int(g["grad_T4_iters"][1])) <= 1
+
+
+FAST_CASES = [(1, 3000, 35, 1e-4), (2, 5000, 17, 1e-4), (2, 5000, 16, 6e-8), (3, 2000, 9, 1e-6), (2, 3000, 21, 1e-12)]
+
+
+@pytest.mark.parametrize("d,N,n,eps", FAST_CASES)
+def test_fast_cpu_nufft_matches_exact_nudft(d, N, n, eps):
+    """oracle/fast_nufft.py (C spreader + numpy FFT: the timed CPU baseline) against the exact NUDFT,
+    within the same 10*eps relative l2 the GPU path is held to."""
+    import fast_nufft as F
+    from pytorch_finufft import functional as E
+    g = torch.Generator().manual_seed(5)
+    x = (torch.rand(d, N, dtype=torch.float64, generator=g) * 2 - 1) * 2.5
+    c = torch.randn(N, dtype=torch.complex128, generator=g)
+    f = torch.randn((2,) + (n,) * d, dtype=torch.complex128, generator=g)
+    for modeord in (False, True):
+        a = F.finufft_type1(x, c, (n,) * d, eps=eps, isign=-1, modeord=modeord)
+        b = E.finufft_type1(x, c, (n,) * d, isign=-1, modeord=modeord)
+        assert rel(a, b) < 10 * eps
+        a2 = F.finufft_type2(x, f, eps=eps, isign=+1, modeord=modeord)
+        b2 = E.finufft_type2(x, f, isign=+1, modeord=modeord)
+        assert a2.shape == b2.shape and rel(a2, b2) < 10 * eps
+
+
+def test_oracle_fit_with_fast_backend_matches_exact_backend():
+    """The CPU-baseline configuration (reference algebra + fast CPU NUFFT) reproduces the exact-NUDFT fit."""
+    import fast_nufft as F
+    g = torch.Generator().manual_seed(11)
+    x = torch.rand(3000, 2, dtype=torch.float64, generator=g) * 2 - 1
+    y = torch.sin(3 * x[:, 0]) * torch.cos(4 * x[:, 1]) + 0.1 * torch.randn(3000, dtype=torch.float64, generator=g)
+    k = O.OracleKernel("se", 2, 0.3, 1.0)
+    fe = O.fit(x, y, k, 0.05, 1e-4, 1e-12, cg_tol=1e-10)
+    ff = O.fit(x, y, k, 0.05, 1e-4, 1e-12, cg_tol=1e-10, backend=F)
+    assert rel(ff.beta, fe.beta) < 1e-6
+    assert rel(O.predict_mean(ff, x[:200], 1e-12, backend=F), O.predict_mean(fe, x[:200], 1e-12)) < 1e-7
