@@ -185,7 +185,7 @@ class ClockSampler:
 
 # ----------------------------------------------------------------------------- algorithmic bytes
 def algorithmic_bytes(stage, n, d=2, word=8):
-    """Bytes one launch of `stage` must move for n points."""
+    """Bytes `stage` must move to process n points."""
     if stage.startswith("spread"):
         return n * word * (d + (0 if stage.endswith("_ones") else 1))      # coordinates (+ real strength)
     if stage.startswith("interp"):
@@ -306,24 +306,24 @@ def main():
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    own = {k: v for k, v in stages.items() if algorithmic_bytes(k, n_loc) is not None and v["launches"] > 0}
+    own = {k: v for k, v in stages.items() if algorithmic_bytes(k, 1) is not None and v["launches"] > 0}
     per_stage = {}
     for k, v in stages.items():
         ent = {"ms_per_step": v["ms"] / args.steps, "launches_per_step": v["launches"] / args.steps}
-        ab = algorithmic_bytes(k, n_loc)
-        if ab is not None and v["launches"] > 0:
-            dur = v["ms"] / v["launches"]
-            ent["achieved_gbs"] = ab / dur / 1e6
+        if k in own and v["ms"] > 0:
+            # algorithmic bytes of all the points the stage processed / the CUDA-event time of its launches
+            ent["achieved_gbs"] = algorithmic_bytes(k, v["units"]) / v["ms"] / 1e6
             ent["hbm_frac"] = ent["achieved_gbs"] / peak
         per_stage[k] = ent
     roofline = None
     if own:
         top = max(own, key=lambda k: own[k]["ms"])
-        dur = own[top]["ms"] / own[top]["launches"]
-        ach = algorithmic_bytes(top, n_loc) / dur / 1e6
+        v = own[top]
+        ach = algorithmic_bytes(top, v["units"]) / v["ms"] / 1e6
         roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                    "traffic": None, "peak_source": peak_src, "avg_launch_ms": dur,
-                    "algorithmic_bytes_per_launch": algorithmic_bytes(top, n_loc)}
+                    "traffic": None, "peak_source": peak_src, "avg_launch_ms": v["ms"] / v["launches"],
+                    "algorithmic_bytes_per_launch": algorithmic_bytes(top, v["units"]) / v["launches"],
+                    "points_per_launch": v["units"] / v["launches"]}
     launches = sum(v["launches"] for v in stages.values())
 
     line = {"metric": METRIC, "value": n_total / ms / 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -94,7 +94,7 @@ bool timing_on();
 void timing_enable(int on);
 std::string timing_report();
 struct ScopedStage {
-  ScopedStage(const char* name, cudaStream_t st, int launches = 1);
+  ScopedStage(const char* name, cudaStream_t st, int launches = 1, long long units = 0);
   ~ScopedStage();
   void add_launches(int n);
   cudaStream_t st_;

@@ -203,7 +203,7 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* grid, T
   const int nt = (int)sp.ntiles;
   char nm[48];
   snprintf(nm, sizeof(nm), "interp%dd_w%d_%s", sp.dim, W, sizeof(T) == 8 ? "f64" : "f32");
-  ScopedStage stg(nm, st);
+  ScopedStage stg(nm, st, 1, sp.N);
   if (sp.dim == 1) {
     interp1d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(x0, sp.perm, sp.P, (int)sp.nf[0], grid, out, ostride, es);
   } else if (sp.dim == 2) {

@@ -47,7 +47,15 @@ cufftHandle FftCache::get(int dim, const int64_t* n, cufftType type, int batch, 
   return h;
 }
 FftCache::~FftCache() {
-  for (auto& kv : plans) cufftDestroy(kv.second);
+  // process teardown: the CUDA context may already be gone, leave the plans to the driver
+}
+FftCache& global_fft() {
+  static FftCache* g = new FftCache();   // intentionally leaked (see ~FftCache)
+  return *g;
+}
+static std::map<std::string, std::unique_ptr<DevBuf>>& global_dec_tables() {
+  static auto* g = new std::map<std::string, std::unique_ptr<DevBuf>>();
+  return *g;
 }
 
 // ------------------------------------------------------------------ mode bookkeeping
@@ -217,12 +225,14 @@ static void upload_dinv(Nufft& nu, const ESKernel& ker, const int64_t* nf, const
   for (int a = 0; a < dim; ++a) total += (size_t)(n[a] / 2 + 1);
   // tables are cached per geometry: repeated transforms (probes, CG) skip the host work and the sync
   char keybuf[160];
-  snprintf(keybuf, sizeof(keybuf), "%d|%.17g|%lld,%lld,%lld|%lld,%lld,%lld", ker.W, ker.beta, (long long)nf[0],
+  snprintf(keybuf, sizeof(keybuf), "%d|%d|%.17g|%lld,%lld,%lld|%lld,%lld,%lld", dtype, ker.W, ker.beta, (long long)nf[0],
            (long long)(dim > 1 ? nf[1] : 0), (long long)(dim > 2 ? nf[2] : 0), (long long)n[0],
            (long long)(dim > 1 ? n[1] : 0), (long long)(dim > 2 ? n[2] : 0));
   std::string key(keybuf);
-  auto hit = nu.dec_tables.find(key);
-  if (hit != nu.dec_tables.end()) {
+  auto& tables = global_dec_tables();
+  (void)nu;
+  auto hit = tables.find(key);
+  if (hit != tables.end()) {
     char* b0 = (char*)hit->second->p;
     size_t pos0 = 0;
     for (int a = 0; a < dim; ++a) {
@@ -232,10 +242,10 @@ static void upload_dinv(Nufft& nu, const ESKernel& ker, const int64_t* nf, const
     for (int a = dim; a < kMaxDim; ++a) dptr[a] = b0;
     return;
   }
-  if (nu.dec_tables.size() > 16) nu.dec_tables.clear();
+  if (tables.size() > 64) tables.clear();
   std::unique_ptr<DevBuf> holder(new DevBuf());
   char* base = (char*)holder->get(total * esz);
-  nu.dec_tables[key] = std::move(holder);
+  tables[key] = std::move(holder);
   std::vector<double> host;
   std::vector<float> hostf;
   size_t pos = 0;
@@ -253,7 +263,7 @@ static void upload_dinv(Nufft& nu, const ESKernel& ker, const int64_t* nf, const
   } else {
     EFGP_CUDA(cudaMemcpyAsync(base, all.data(), total * 8, cudaMemcpyHostToDevice, st));
   }
-  EFGP_CUDA(cudaStreamSynchronize(st));  // host vectors go out of scope
+  // (pageable-memory cudaMemcpyAsync stages the host buffer before returning: no sync needed)
 }
 
 static SortedPoints* get_sorted(Nufft& nu, const int64_t* nf, int odd, cudaStream_t st) {
@@ -379,7 +389,7 @@ static void type1_t(Nufft& nu, const void* strengths, int is_complex, int batch,
         launch_spread(*gc.sp, gc.ker, cs, fine + (int64_t)(b * ncomp + comp) * cells, st);
       }
     }
-    cufftHandle plan = nu.fft.get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_R2C : CUFFT_D2Z, nb * ncomp, st);
+    cufftHandle plan = global_fft().get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_R2C : CUFFT_D2Z, nb * ncomp, st);
     {
       ScopedStage stg("type1.cufft_r2c", st, 0);
       if (sizeof(T) == 4)
@@ -426,7 +436,7 @@ static void type2_t(Nufft& nu, const void* modes, int batch, const int64_t* n, d
                                                            (const T*)dinv[2], (const T*)scale, spec);
     }
     EFGP_CUDA(cudaGetLastError());
-    cufftHandle plan = nu.fft.get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_C2R : CUFFT_Z2D, nb * ncomp, st);
+    cufftHandle plan = global_fft().get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_C2R : CUFFT_Z2D, nb * ncomp, st);
     {
       ScopedStage stg("type2.cufft_c2r", st, 0);
       if (sizeof(T) == 4)

@@ -24,6 +24,7 @@ struct SortedPoints {
   int P = 1;            // points per thread
   int64_t ntiles = 0;
   int64_t npos = 0;     // ntiles * kTileThreads * P
+  int64_t chunk = 0;    // slots per independently sorted chunk (a multiple of the tile length)
   void* xs[kMaxDim] = {nullptr, nullptr, nullptr};
   uint32_t* perm = nullptr;   // perm[pos] = original index of the point stored at slot pos
   uint64_t last_use = 0;
@@ -51,6 +52,9 @@ struct DevBuf {
   ~DevBuf();
 };
 
+// cuFFT plans are cached process-wide (one process drives one GPU): the EFGP loop rebuilds its NUFFT
+// and Toeplitz handles at every hyperparameter step, and plan creation costs far more than the
+// transforms on these small grids.  All plans share one work area (calls are stream-ordered).
 struct FftCache {
   std::map<FftPlanKey, cufftHandle> plans;
   DevBuf work;
@@ -58,6 +62,7 @@ struct FftCache {
   cufftHandle get(int dim, const int64_t* n, cufftType type, int batch, cudaStream_t st);
   ~FftCache();
 };
+FftCache& global_fft();
 
 struct Nufft {
   int dim = 0;
@@ -68,9 +73,7 @@ struct Nufft {
   double xcen[kMaxDim] = {0, 0, 0};
   uint64_t clock = 0;
   std::vector<std::unique_ptr<SortedPoints>> sorted;  // small LRU cache
-  FftCache fft;
   DevBuf fine, spec, tmp, dec, cperm;
-  std::map<std::string, std::unique_ptr<DevBuf>> dec_tables;  // deconvolution factors per geometry
 };
 
 // ---- points.cu

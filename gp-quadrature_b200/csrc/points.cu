@@ -15,23 +15,20 @@ SortedPoints::~SortedPoints() {
   if (perm) pool_free(perm);
 }
 
+// Scratch comes from the caching pool (pool.cpp): handles are rebuilt every hyperparameter step and a
+// cudaMalloc/cudaFree pair per buffer would synchronise the device each time.
 void* DevBuf::get(size_t bytes) {
   if (bytes > cap) {
-    if (p) cudaFree(p);
+    if (p) pool_free(p);
     p = nullptr;
     cap = 0;
-    size_t want = bytes + bytes / 8 + 256;
-    cudaError_t e = cudaMalloc(&p, want);
-    if (e != cudaSuccess) {
-      p = nullptr;
-      throw Error(2, std::string("cudaMalloc(") + std::to_string(want) + "): " + cudaGetErrorString(e));
-    }
-    cap = want;
+    p = pool_alloc(bytes);
+    cap = bytes;
   }
   return p;
 }
 DevBuf::~DevBuf() {
-  if (p) cudaFree(p);
+  if (p) pool_free(p);
 }
 
 template <typename T>
@@ -73,13 +70,16 @@ __global__ void __launch_bounds__(256) key_kernel(const T* __restrict__ x, int64
 
 // One thread per SLOT (coalesced writes); the slot's sorted rank follows from the tile-transposed
 // layout described in nufft.cuh.
+// Slots [pos0, pos1) belong to the chunk whose points are the original indices [lo, lo + n): ranks are
+// chunk-local sort positions, `sorted_idx` holds chunk-local indices.
 template <typename T, int D>
 __global__ void __launch_bounds__(256) gather_kernel(const T* __restrict__ x, int64_t N, int P, FoldParams<T> p,
                                                      const uint32_t* __restrict__ sorted_idx,
                                                      uint32_t* __restrict__ perm, T* __restrict__ o0,
-                                                     T* __restrict__ o1, T* __restrict__ o2, int64_t npos) {
-  int64_t pos = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (pos >= npos) return;
+                                                     T* __restrict__ o1, T* __restrict__ o2, int64_t pos0,
+                                                     int64_t pos1, int64_t lo) {
+  int64_t pos = pos0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pos >= pos1) return;
   const int64_t tile_len = (int64_t)kTileThreads * P;
   int64_t tile = pos / tile_len;
   int r = (int)(pos - tile * tile_len);
@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(256) gather_kernel(const T* __restrict__ x, in
     perm[pos] = 0;
     return;
   }
-  int64_t src = sorted_idx[rank];
+  int64_t src = lo + sorted_idx[rank - pos0];
   perm[pos] = (uint32_t)src;
 #pragma unroll
   for (int a = 0; a < D; ++a) {
@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(256) permute_kernel(const T* __restrict__ c, i
 void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, void* cs, cudaStream_t st) {
   if (sp.npos == 0) return;
   int nb = div_up(sp.npos, 256);
-  ScopedStage stg("permute_strengths", st);
+  ScopedStage stg("permute_strengths", st, 1, sp.N);
   if (sp.dtype == 0)
     permute_kernel<float><<<nb, 256, 0, st>>>((const float*)c, cstride, sp.perm, sp.npos, (float*)cs);
   else
@@ -131,6 +131,21 @@ static int pick_points_per_thread(int64_t N) {
   int p2 = 1;
   while (p2 * 2 <= P) p2 *= 2;   // power of two: the gather kernel reads the sort output in 8-wide chunks
   return p2;
+}
+
+// Points per sort chunk: a whole number of tiles, sized so that one chunk's coordinates plus the sort's
+// key/index ping-pong buffers (d*word + 16 bytes per point) fit comfortably in L2.  EFGP_SORT_CHUNK
+// (points) overrides it; 0 or a value >= N gives one global sort.
+static int64_t pick_sort_chunk(int64_t N, int64_t tile_len, int dim, size_t word) {
+  int64_t target = (int64_t)((48ull << 20) / (dim * word + 16));   // ~48 MB working set
+  if (const char* e = getenv("EFGP_SORT_CHUNK")) {
+    long long v = atoll(e);
+    target = v <= 0 ? N : (int64_t)v;
+  }
+  int64_t ntile_total = (N + tile_len - 1) / tile_len;
+  int64_t tiles = std::max<int64_t>(1, target / tile_len);
+  if (tiles * 3 >= ntile_total * 2) tiles = ntile_total;            // not worth splitting
+  return tiles * tile_len;
 }
 
 template <typename T>
@@ -156,40 +171,52 @@ static void build_t(SortedPoints& sp, const T* x, int64_t N, int dim, double h, 
   sp.ntiles = (N + tile_len - 1) / tile_len;
   sp.npos = sp.ntiles * tile_len;
 
-  uint32_t* keys_in = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
-  uint32_t* keys_out = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
-  uint32_t* idx_in = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
-  uint32_t* idx_out = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
+  // Chunked sort.  The points are cut into chunks of consecutive ORIGINAL indices (a whole number of
+  // tiles each) and every chunk is cell-sorted on its own: key -> radix sort -> gather run back to back
+  // per chunk, so the chunk's coordinates, keys and indices stay resident in the 126 MB L2 between the
+  // three kernels, and -- because a chunk's slots only ever reference original indices of the same chunk --
+  // the strength gathers (permute_strengths) and the type-2 result scatters (interp) of later transforms
+  // hit an L2-sized window instead of issuing one 32-byte DRAM sector per 8-byte element.
+  const int64_t chunk = pick_sort_chunk(N, tile_len, dim, sizeof(T));
+  sp.chunk = chunk;
+  uint32_t* keys_in = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)chunk);
+  uint32_t* keys_out = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)chunk);
+  uint32_t* idx_in = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)chunk);
+  uint32_t* idx_out = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)chunk);
   sp.perm = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)sp.npos);
-  int nb = div_up(N, 256);
-  {
-  ScopedStage stg("sort.key_kernel", st);
-  if (dim == 1) key_kernel<T, 1><<<nb, 256, 0, st>>>(x, N, p, keys_in, idx_in);
-  if (dim == 2) key_kernel<T, 2><<<nb, 256, 0, st>>>(x, N, p, keys_in, idx_in);
-  if (dim == 3) key_kernel<T, 3><<<nb, 256, 0, st>>>(x, N, p, keys_in, idx_in);
-  }
-  EFGP_CUDA(cudaGetLastError());
-  size_t tmp_bytes = 0;
-  EFGP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, idx_in, idx_out, (int)N, 0,
-                                            bits, st));
-  void* tmp = pool_alloc(tmp_bytes);
-  {
-    ScopedStage stg("sort.cub_radix_sort_pairs", st, 0);
-    EFGP_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, idx_in, idx_out, (int)N, 0, bits,
-                                              st));
-  }
   for (int a = 0; a < dim; ++a) sp.xs[a] = pool_alloc(sizeof(T) * (size_t)sp.npos);
   T* o0 = (T*)sp.xs[0];
   T* o1 = (T*)sp.xs[1];
   T* o2 = (T*)sp.xs[2];
-  int nbp = div_up(sp.npos, 256);
-  {
-  ScopedStage stg("sort.gather_kernel", st);
-  if (dim == 1) gather_kernel<T, 1><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, sp.npos);
-  if (dim == 2) gather_kernel<T, 2><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, sp.npos);
-  if (dim == 3) gather_kernel<T, 3><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, sp.npos);
+  size_t tmp_bytes = 0;
+  EFGP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, idx_in, idx_out,
+                                            (int)std::min<int64_t>(chunk, N), 0, bits, st));
+  void* tmp = pool_alloc(tmp_bytes);
+  for (int64_t lo = 0; lo < sp.npos; lo += chunk) {
+    const int64_t n = std::min(chunk, N - lo);          // points of this chunk (> 0: npos - N < tile_len)
+    const int64_t pos1 = std::min(lo + chunk, sp.npos);
+    const T* xc = x + lo * dim;
+    int nb = div_up(n, 256);
+    {
+      ScopedStage stg("sort.key_kernel", st, 1, n);
+      if (dim == 1) key_kernel<T, 1><<<nb, 256, 0, st>>>(xc, n, p, keys_in, idx_in);
+      if (dim == 2) key_kernel<T, 2><<<nb, 256, 0, st>>>(xc, n, p, keys_in, idx_in);
+      if (dim == 3) key_kernel<T, 3><<<nb, 256, 0, st>>>(xc, n, p, keys_in, idx_in);
+    }
+    {
+      ScopedStage stg("sort.cub_radix_sort_pairs", st, 0, n);
+      size_t tb = tmp_bytes;
+      EFGP_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, keys_in, keys_out, idx_in, idx_out, (int)n, 0, bits, st));
+    }
+    int nbp = div_up(pos1 - lo, 256);
+    {
+      ScopedStage stg("sort.gather_kernel", st, 1, n);
+      if (dim == 1) gather_kernel<T, 1><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, lo, pos1, lo);
+      if (dim == 2) gather_kernel<T, 2><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, lo, pos1, lo);
+      if (dim == 3) gather_kernel<T, 3><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, lo, pos1, lo);
+    }
+    EFGP_CUDA(cudaGetLastError());
   }
-  EFGP_CUDA(cudaGetLastError());
   // scratch goes back to the pool; later users run on the same stream, so ordering is preserved
   pool_free(tmp);
   pool_free(keys_in);

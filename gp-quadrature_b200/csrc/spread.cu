@@ -225,7 +225,7 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
   const int nt = (int)sp.ntiles;
   char nm[48];
   snprintf(nm, sizeof(nm), "spread%dd_w%d_%s%s", sp.dim, W, sizeof(T) == 8 ? "f64" : "f32", cs ? "" : "_ones");
-  ScopedStage stg(nm, st);
+  ScopedStage stg(nm, st, 1, sp.N);
   if (sp.dim == 1) {
     if (cs)
       spread1d_kernel<T, W, true><<<nt, kTileThreads, 0, st>>>(x0, cs, sp.P, (int)sp.nf[0], grid, es);

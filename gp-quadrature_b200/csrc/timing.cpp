@@ -13,6 +13,7 @@ struct Rec {
   std::string name;
   cudaEvent_t a, b;
   int launches;
+  long long units;   // points (or grid entries) the scope processed: the roofline's unit count
 };
 std::mutex g_tmu;
 bool g_on = false;
@@ -45,7 +46,7 @@ void timing_enable(int on) {
   g_on = on != 0;
 }
 
-ScopedStage::ScopedStage(const char* name, cudaStream_t st, int launches) : st_(st), idx_(-1) {
+ScopedStage::ScopedStage(const char* name, cudaStream_t st, int launches, long long units) : st_(st), idx_(-1) {
   if (!g_on) return;
   std::lock_guard<std::mutex> lk(g_tmu);
   Rec r;
@@ -53,6 +54,7 @@ ScopedStage::ScopedStage(const char* name, cudaStream_t st, int launches) : st_(
   r.a = get_event();
   r.b = get_event();
   r.launches = launches;
+  r.units = units;
   cudaEventRecord(r.a, st);
   g_recs.push_back(r);
   idx_ = (long long)g_recs.size() - 1;
@@ -70,13 +72,14 @@ void ScopedStage::add_launches(int n) {
   if (idx_ < (long long)g_recs.size()) g_recs[idx_].launches += n;
 }
 
-// "name,scopes,launches,total_ms\n" per stage, in first-seen order.  Synchronises the device.
+// "name,scopes,launches,units,total_ms\n" per stage, in first-seen order.  Synchronises the device.
 std::string timing_report() {
   std::lock_guard<std::mutex> lk(g_tmu);
   cudaDeviceSynchronize();
   std::vector<std::string> order;
   std::map<std::string, double> ms;
   std::map<std::string, std::pair<long long, long long>> cnt;
+  std::map<std::string, long long> units;
   for (auto& r : g_recs) {
     float t = 0;
     if (cudaEventElapsedTime(&t, r.a, r.b) != cudaSuccess) {
@@ -87,11 +90,12 @@ std::string timing_report() {
     ms[r.name] += t;
     cnt[r.name].first += 1;
     cnt[r.name].second += r.launches;
+    units[r.name] += r.units;
   }
   std::string out;
   char buf[256];
   for (auto& n : order) {
-    snprintf(buf, sizeof(buf), "%s,%lld,%lld,%.6f\n", n.c_str(), cnt[n].first, cnt[n].second, ms[n]);
+    snprintf(buf, sizeof(buf), "%s,%lld,%lld,%lld,%.6f\n", n.c_str(), cnt[n].first, cnt[n].second, units[n], ms[n]);
     out += buf;
   }
   return out;

@@ -15,7 +15,7 @@
 namespace efgp {
 
 Toeplitz::~Toeplitz() {
-  if (vhat) cudaFree(vhat);
+  if (vhat) pool_free(vhat);
 }
 
 struct TzGeom {
@@ -149,13 +149,13 @@ static TzGeom make_tz_geom(const Toeplitz& t) {
 template <typename T>
 static void create_t(Toeplitz& t, const void* v, cudaStream_t st) {
   using C = typename cplx_of<T>::type;
-  EFGP_CUDA(cudaMalloc(&t.vhat, sizeof(C) * (size_t)t.Ftot));
+  t.vhat = pool_alloc(sizeof(C) * (size_t)t.Ftot);
   TzGeom g = make_tz_geom(t);
   for (int a = 0; a < kMaxDim; ++a) g.n[a] = (int)t.L[a];
   ScopedStage stg("toeplitz.create", st, 2);
   tz_pad_v_kernel<C><<<div_up(t.Ftot, 256), 256, 0, st>>>((const C*)v, g, (C*)t.vhat);
   EFGP_CUDA(cudaGetLastError());
-  cufftHandle plan = t.fft.get(t.dim, t.F, sizeof(T) == 4 ? CUFFT_C2C : CUFFT_Z2Z, 1, st);
+  cufftHandle plan = global_fft().get(t.dim, t.F, sizeof(T) == 4 ? CUFFT_C2C : CUFFT_Z2Z, 1, st);
   if (sizeof(T) == 4)
     EFGP_CUFFT(cufftExecC2C(plan, (cufftComplex*)t.vhat, (cufftComplex*)t.vhat, CUFFT_FORWARD));
   else
@@ -202,7 +202,7 @@ static typename cplx_of<T>::type* ensure_P(Toeplitz& t, int rows, cudaStream_t s
 template <typename T>
 void fft_pair_begin(Toeplitz& t, int rows, typename cplx_of<T>::type* P, typename cplx_of<T>::type* Q,
                     cudaStream_t st) {
-  cufftHandle plan = t.fft.get(t.dim, t.F, sizeof(T) == 4 ? CUFFT_C2C : CUFFT_Z2Z, rows, st);
+  cufftHandle plan = global_fft().get(t.dim, t.F, sizeof(T) == 4 ? CUFFT_C2C : CUFFT_Z2Z, rows, st);
   if (sizeof(T) == 4)
     EFGP_CUFFT(cufftExecC2C(plan, (cufftComplex*)P, (cufftComplex*)Q, CUFFT_FORWARD));
   else
@@ -210,7 +210,7 @@ void fft_pair_begin(Toeplitz& t, int rows, typename cplx_of<T>::type* P, typenam
 }
 template <typename T>
 void fft_pair_end(Toeplitz& t, int rows, typename cplx_of<T>::type* Q, cudaStream_t st) {
-  cufftHandle plan = t.fft.get(t.dim, t.F, sizeof(T) == 4 ? CUFFT_C2C : CUFFT_Z2Z, rows, st);
+  cufftHandle plan = global_fft().get(t.dim, t.F, sizeof(T) == 4 ? CUFFT_C2C : CUFFT_Z2Z, rows, st);
   if (sizeof(T) == 4)
     EFGP_CUFFT(cufftExecC2C(plan, (cufftComplex*)Q, (cufftComplex*)Q, CUFFT_INVERSE));
   else

@@ -12,7 +12,6 @@ struct Toeplitz {
   int64_t F[kMaxDim] = {1, 1, 1};   // FFT extents
   int64_t M = 1, Ftot = 1;
   void* vhat = nullptr;             // FFT of the zero-padded generator, pre-scaled by 1/Ftot
-  FftCache fft;
   DevBuf P, Q;                      // padded input (zeros persist), spectrum / output
   int64_t P_rows = 0;               // rows of P known to be zero outside the block
   DevBuf cg_vec, cg_scal;

@@ -85,11 +85,11 @@ def timing_enable(on=True):
 
 
 def timing_report():
-    """{stage: {"scopes": n, "launches": n, "ms": total}} since timing_enable(True); synchronises."""
+    """{stage: {"scopes": n, "launches": n, "units": points processed, "ms": total}} since timing_enable(True); synchronises."""
     buf = ctypes.create_string_buffer(1 << 16)
     check(lib().efgp_timing_report(buf, len(buf)))
     out = {}
     for line in buf.value.decode().splitlines():
-        name, scopes, launches, ms = line.rsplit(",", 3)
-        out[name] = {"scopes": int(scopes), "launches": int(launches), "ms": float(ms)}
+        name, scopes, launches, units, ms = line.rsplit(",", 4)
+        out[name] = {"scopes": int(scopes), "launches": int(launches), "units": int(units), "ms": float(ms)}
     return out

@@ -743,10 +743,12 @@ class EFGPND(nn.Module):
         N, d = x.shape
         group = _point_shard_group(self.opts)
         if group is None:
-            L = float(torch.max(torch.max(x, dim=0).values - torch.min(x, dim=0).values).item())
+            lo_x, hi_x = torch.aminmax(x, dim=0)            # one pass over x
+            L = float(torch.max(hi_x - lo_x).item())
         else:
             # points are sharded over the ranks: the box is the union of the shards' boxes
-            ext = torch.cat([torch.max(x, dim=0).values, -torch.min(x, dim=0).values])
+            lo_x, hi_x = torch.aminmax(x, dim=0)
+            ext = torch.cat([hi_x, -lo_x])
             torch.distributed.all_reduce(ext, op=torch.distributed.ReduceOp.MAX, group=group)
             L = float(torch.max(ext[:d] + ext[d:]).item())
         if L <= 1e-9:

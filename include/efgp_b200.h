@@ -31,7 +31,7 @@ const char* efgp_last_error(void);
 
 /* ---- diagnostics (no reference counterpart; the reference's torch.profiler ranges, efgpnd.py:46-59).
  * efgp_timing_enable(1) starts recording CUDA events around every launch group the library issues;
- * efgp_timing_report writes "stage,scopes,launches,total_ms\n" lines (synchronises the device).
+ * efgp_timing_report writes "stage,scopes,launches,units,total_ms\n" lines (synchronises the device).
  * efgp_pool_trim releases the cached device scratch blocks. */
 int efgp_timing_enable(int on);
 int efgp_timing_report(char* buf, int64_t cap);
