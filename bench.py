@@ -189,13 +189,18 @@ def algorithmic_bytes(stage, n, d=2, word=8):
     if stage.startswith("spread"):
         return n * word * (d + (0 if stage.endswith("_ones") else 1))      # coordinates (+ real strength)
     if stage.startswith("interp"):
-        return n * (word * d + 4 + word)                                    # coordinates + perm + real output
-    if stage == "sort.key_kernel":
-        return n * (word * d + 8)                                           # x -> key + index
-    if stage == "sort.gather_kernel":
-        return n * (4 + word * d + word * d + 4)                            # rank -> x gather -> sorted coords + perm
-    if stage == "permute_strengths":
-        return n * (4 + word + word)
+        return n * (word * d + 4 + word)                                    # coordinates + Binv + real result
+    per_point = {
+        "sort.bucket_hist_kernel": word * d,                                # read x
+        "sort.bucket_scatter_kernel": word * d + word * d + 2 + 4,          # read x; write folded coords, bin, A
+        "sort.bin_hist_kernel": 2,                                          # read level-2 bins
+        "sort.bin_scatter_kernel": word * d + 2 + word * d + 4,             # read coords, bin; write slots, Binv
+        "permute.to_bucket_order": word + 4 + word,                         # read c, A; write tmp
+        "permute.to_slot_order": 4 + word + word,                           # read Binv, tmp; write cs
+        "unpermute.from_bucket_order": 4 + word + word,                     # read A, tmp; write out
+    }
+    if stage in per_point:
+        return n * per_point[stage]
     return None
 
 

@@ -79,6 +79,17 @@ inline void es_to_dev(const ESKernel& k, ESDev<T>& d) {
     for (int j = 0; j <= kMaxDeg; ++j) d.c[i][j] = (T)k.coef[i][j];
 }
 
+// sm_100a 256-bit global accesses (SASS LDG.E.ENL2.256 / STG.E.ENL2.256): a 32-byte point record moves
+// as ONE L2 request covering one full sector.
+#ifdef __CUDACC__
+__device__ __forceinline__ void ld_global_nc_256(const double* p, double& a, double& b, double& c, double& d) {
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(a), "=d"(b), "=d"(c), "=d"(d) : "l"(p));
+}
+__device__ __forceinline__ void st_global_256(double* p, double a, double b, double c, double d) {
+  asm volatile("st.global.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+}
+#endif
+
 template <typename T> struct cplx_of;
 template <> struct cplx_of<float> { using type = float2; };
 template <> struct cplx_of<double> { using type = double2; };

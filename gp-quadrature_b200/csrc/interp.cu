@@ -38,6 +38,25 @@ __device__ __forceinline__ void es_eval_i(const ESDev<T>& es, T s, T* __restrict
   }
 }
 
+template <typename T>
+__device__ __forceinline__ void load_record4i(const T* __restrict__ p, T* w) {
+  if constexpr (sizeof(T) == 8) {
+    ld_global_nc_256(reinterpret_cast<const double*>(p), w[0], w[1], w[2], w[3]);
+  } else {
+    float4 a = __ldg(reinterpret_cast<const float4*>(p));
+    w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
+  }
+}
+// 2-D record: (X0, X1, binv, pad)
+template <typename T>
+__device__ __forceinline__ void load_point2(const T* __restrict__ p, T& X0, T& X1, uint32_t& binv) {
+  T w[4];
+  load_record4i<T>(p, w);
+  X0 = w[0];
+  X1 = w[1];
+  binv = *reinterpret_cast<const uint32_t*>(&w[2]);
+}
+
 __device__ __forceinline__ int wrap_i(int i, int n) {
   if (i < 0) i += n;
   if (i >= n) i -= n;
@@ -46,7 +65,7 @@ __device__ __forceinline__ int wrap_i(int i, int n) {
 
 template <typename T, int W>
 __global__ void __launch_bounds__(kTileThreads)
-interp1d_kernel(const T* __restrict__ xs0, const uint32_t* __restrict__ perm, int P, int nf0,
+interp1d_kernel(const T* __restrict__ rec, int P, int nf0,
                 const T* __restrict__ grid, T* __restrict__ out, int64_t ostride,
                 const __grid_constant__ ESDev<T> es) {
   const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
@@ -55,8 +74,9 @@ interp1d_kernel(const T* __restrict__ xs0, const uint32_t* __restrict__ perm, in
   int cur = -1;
   for (int j = 0; j < P; ++j) {
     const int64_t pos = base + (int64_t)j * kTileThreads;
-    T X = xs0[pos];
+    T X = rec[pos * 2];
     if (X < T(0)) break;
+    const uint32_t bi = *reinterpret_cast<const uint32_t*>(rec + pos * 2 + 1);
     int c0 = (int)X;
     if (c0 != cur) {
 #pragma unroll
@@ -68,37 +88,30 @@ interp1d_kernel(const T* __restrict__ xs0, const uint32_t* __restrict__ perm, in
     T acc = 0;
 #pragma unroll
     for (int i = 0; i < W; ++i) acc = fma(g[i], k0[i], acc);
-    out[(int64_t)perm[pos] * ostride] = acc;
+    out[bi] = acc;
   }
 }
 
 template <typename T, int W>
 __global__ void __launch_bounds__(kTileThreads, 1)
-interp2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const uint32_t* __restrict__ perm, int P,
+interp2d_kernel(const T* __restrict__ rec, int P,
                 int nf0, int nf1, const T* __restrict__ grid, T* __restrict__ out, int64_t ostride,
                 const __grid_constant__ ESDev<T> es) {
   const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
   T g[W][W];
   int cur0 = -1, cur1 = -1;
-  T X0 = xs0[base], X1 = xs1[base];
-  uint32_t pn = perm[base];
-  T nX0 = T(-1), nX1 = T(0);
-  uint32_t npn = 0;
-  if (P > 1) {
-    nX0 = xs0[base + kTileThreads];
-    nX1 = xs1[base + kTileThreads];
-    npn = perm[base + kTileThreads];
-  }
+  T X0, X1, nX0 = T(-1), nX1 = T(0);
+  uint32_t pn, npn = 0;
+  load_point2<T>(rec + base * 4, X0, X1, pn);
+  if (P > 1) load_point2<T>(rec + (base + kTileThreads) * 4, nX0, nX1, npn);
   for (int j = 0; j < P; ++j) {
     if (X0 < T(0)) break;
     T fX0 = T(-1), fX1 = T(0);
     uint32_t fpn = 0;
     if (j + 2 < P) {
       const int64_t pos = base + (int64_t)(j + 2) * kTileThreads;
-      fX0 = xs0[pos];
-      fX1 = xs1[pos];
-      fpn = perm[pos];
+      load_point2<T>(rec + pos * 4, fX0, fX1, fpn);
     }
     int c0 = (int)X0, c1 = (int)X1;
     if (c0 != cur0 || c1 != cur1) {
@@ -125,7 +138,7 @@ interp2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const uint
       for (int jj = 0; jj < W; ++jj) r = fma(g[i][jj], k1[jj], r);
       acc = fma(r, k0[i], acc);
     }
-    out[(int64_t)pn * ostride] = acc;
+    out[pn] = acc;
     X0 = nX0;
     X1 = nX1;
     pn = npn;
@@ -138,24 +151,26 @@ interp2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const uint
 // generic: wide 2-D kernels and 3-D, one slot per thread, gathers through L1/L2
 template <typename T, int W, int D>
 __global__ void __launch_bounds__(256)
-interp_direct_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* __restrict__ xs2,
-                     const uint32_t* __restrict__ perm, int64_t npos, int nf0, int nf1, int nf2,
+interp_direct_kernel(const T* __restrict__ rec, int64_t npos, int nf0, int nf1, int nf2,
                      const T* __restrict__ grid, T* __restrict__ out, int64_t ostride,
                      const __grid_constant__ ESDev<T> es) {
   int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= npos) return;
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
   T k0[W], k1[W], k2[W];
-  T X0 = xs0[n];
+  T Xr[4];
+  load_record4i<T>(rec + n * 4, Xr);
+  T X0 = Xr[0];
   if (X0 < T(0)) return;
+  const uint32_t bi = *reinterpret_cast<const uint32_t*>(&Xr[D]);
   int c0 = (int)X0;
   es_eval_i<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
-  T X1 = xs1[n];
+  T X1 = Xr[1];
   int c1 = (int)X1;
   es_eval_i<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
   int c2 = 0;
   if (D == 3) {
-    T X2 = xs2[n];
+    T X2 = Xr[2];
     c2 = (int)X2;
     es_eval_i<T, W>(es, T(2) * (X2 - (T)c2) - T(1), k2);
   }
@@ -188,7 +203,7 @@ interp_direct_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const
       acc = fma(ri, k0[i], acc);
     }
   }
-  out[(int64_t)perm[n] * ostride] = acc;
+  out[bi] = acc;
 }
 
 template <typename T, int W>
@@ -196,27 +211,25 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* grid, T
                      cudaStream_t st) {
   ESDev<T> es;
   es_to_dev<T>(k, es);
-  const T* x0 = (const T*)sp.xs[0];
-  const T* x1 = (const T*)sp.xs[1];
-  const T* x2 = (const T*)sp.xs[2];
+  const T* rec = (const T*)sp.rec;
   constexpr int kRegMaxW = sizeof(T) == 8 ? 9 : 10;
   const int nt = (int)sp.ntiles;
   char nm[48];
   snprintf(nm, sizeof(nm), "interp%dd_w%d_%s", sp.dim, W, sizeof(T) == 8 ? "f64" : "f32");
   ScopedStage stg(nm, st, 1, sp.N);
   if (sp.dim == 1) {
-    interp1d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(x0, sp.perm, sp.P, (int)sp.nf[0], grid, out, ostride, es);
+    interp1d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], grid, out, ostride, es);
   } else if (sp.dim == 2) {
     if constexpr (W <= kRegMaxW) {
-      interp2d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(x0, x1, sp.perm, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
+      interp2d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
                                                          out, ostride, es);
     } else {
       interp_direct_kernel<T, W, 2><<<div_up(sp.npos, 256), 256, 0, st>>>(
-          x0, x1, x2, sp.perm, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, out, ostride, es);
+          rec, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, out, ostride, es);
     }
   } else {
     interp_direct_kernel<T, W, 3><<<div_up(sp.npos, 256), 256, 0, st>>>(
-        x0, x1, x2, sp.perm, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, out, ostride, es);
+        rec, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, out, ostride, es);
   }
   EFGP_CUDA(cudaGetLastError());
 }
@@ -241,10 +254,16 @@ void launch_interp(const SortedPoints& sp, const ESKernel& k, const void* grid, 
                    cudaStream_t st) {
   if (sp.N == 0) return;
   EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
+  // the kernels write bucket-order results tmp[Binv[slot]] (scatter inside an L2-sized window);
+  // unpermute_output then streams them back to original order through A
+  const size_t esz = sp.dtype == 0 ? 4 : 8;
+  void* tmp = pool_alloc(esz * (size_t)sp.N);
   if (sp.dtype == 0)
-    launch_t<float>(sp, k, (const float*)grid, (float*)out, ostride, st);
+    launch_t<float>(sp, k, (const float*)grid, (float*)tmp, 1, st);
   else
-    launch_t<double>(sp, k, (const double*)grid, (double*)out, ostride, st);
+    launch_t<double>(sp, k, (const double*)grid, (double*)tmp, 1, st);
+  unpermute_output(sp, tmp, out, ostride, st);
+  pool_free(tmp);  // stream-ordered reuse
 }
 
 }  // namespace efgp

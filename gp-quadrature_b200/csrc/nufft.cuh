@@ -7,13 +7,17 @@
 namespace efgp {
 
 // Points sorted by fine-grid cell for one fine grid geometry.
-// xs[a][i] = Xc = X + shift (mod nf), X = nf * frac(h (x - xcen)); shift = 1/2 for odd W, 0 for even
+// Per point a RECORD of RW words of T is stored:  X[0..dim)  then the 32-bit level-1 position `binv`
+// (raw bits in word `dim`), padded to RW = 2 words (dim 1) or 4 words (dim 2, 3) so that a record is
+// one aligned 8/16/32-byte unit: the counting sort places a point with ONE full-sector store, and a
+// spread / interp thread fetches it with one 8- or 16-byte cp.async / vector load.
+// X[a] = Xc = X + shift (mod nf), X = nf * frac(h (x - xcen)); shift = 1/2 for odd W, 0 for even
 // (so cell = floor(Xc) identifies the W^d footprint for either parity, see spread.cu).
 //
-// Storage is TILE-TRANSPOSED: sorted ranks are cut into tiles of kTileThreads*P consecutive points;
-// inside a tile thread t owns the P consecutive ranks [t*P, (t+1)*P) (one long register run), and
-// its j-th point is stored at  tile*kTileThreads*P + j*kTileThreads + t  so that at every step j a
-// warp reads 32 consecutive words (fully coalesced, prefetchable).  Slots past N hold xs[0] = -1.
+// Storage is TILE-TRANSPOSED at record granularity: sorted ranks are cut into tiles of kTileThreads*P
+// consecutive points; inside a tile thread t owns the P consecutive ranks [t*P, (t+1)*P) (one long register
+// run), and its j-th point is stored at slot  tile*kTileThreads*P + j*kTileThreads + t  so that at every
+// step j a warp reads 32 consecutive records (fully coalesced, prefetchable).  Slots past N hold X[0] = -1.
 constexpr int kTileThreads = 256;
 struct SortedPoints {
   int dim = 0;
@@ -22,14 +26,17 @@ struct SortedPoints {
   int64_t nf[kMaxDim] = {1, 1, 1};
   int odd = 0;
   int P = 1;            // points per thread
+  int RW = 2;           // words of T per record
   int64_t ntiles = 0;
   int64_t npos = 0;     // ntiles * kTileThreads * P
-  int64_t chunk = 0;    // slots per independently sorted chunk (a multiple of the tile length)
-  void* xs[kMaxDim] = {nullptr, nullptr, nullptr};
-  uint32_t* perm = nullptr;   // perm[pos] = original index of the point stored at slot pos
+  void* rec = nullptr;        // npos records
+  uint32_t* A = nullptr;      // A[i] = level-1 (bucket-order) position of original point i      (N entries)
+  uint32_t* tileStart = nullptr;  // [nb1][ntiles1]: first level-1 position of (bucket, 2048-point tile)
+  int ntiles1 = 0, nb1 = 0;
   uint64_t last_use = 0;
   ~SortedPoints();
 };
+__host__ __device__ constexpr int rec_words(int dim) { return dim == 1 ? 2 : 4; }
 
 struct FftPlanKey {
   int dim, type, batch;
@@ -80,14 +87,17 @@ struct Nufft {
 void build_sorted_points(SortedPoints& sp, const void* x, int64_t N, int dim, int dtype, double h,
                          const double* xcen, const int64_t* nf, int odd, cudaStream_t st);
 
-// ---- points.cu : cs[pos] = c[perm[pos] * cstride]  (strengths into slot order; npos entries)
+// ---- points.cu : cs[slot] = c[i * cstride] for the point i stored in that slot (npos entries), in two
+// sector-efficient stages (original -> bucket order -> slot order)
 void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, void* cs, cudaStream_t st);
+// out[i * ostride] = tmp[A[i]]: bucket-order results (written by interp through Binv) back to original order
+void unpermute_output(const SortedPoints& sp, const void* tmp, void* out, int64_t ostride, cudaStream_t st);
 
 // ---- spread.cu : grid (real, nf^d) += sum_n c_n psi(l - X_n).  cs == nullptr means all ones;
 // otherwise cs holds the strengths in SLOT order (permute_strengths).
 void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, void* grid, cudaStream_t st);
 
-// ---- interp.cu : out[perm[i] * ostride] = sum_l grid[l] psi(l - X_i)
+// ---- interp.cu : out[i * ostride] = sum_l grid[l] psi(l - X_i)  (i = original point index)
 void launch_interp(const SortedPoints& sp, const ESKernel& k, const void* grid, void* out,
                    int64_t ostride, cudaStream_t st);
 

@@ -1,18 +1,34 @@
-// Bin-sorting of nonuniform points by fine-grid cell.
+// Bin-sorting of nonuniform points by fine-grid cell: a two-level counting sort written for B200.
 //
 // Replaces the point handling FINUFFT does inside every pff.finufft_type1/type2 call
 // (reference call sites efgpnd.py:1496-1499, 1533-1549; phi = 2*pi*h*(x - xcen), efgpnd.py:1451).
-// Points are folded to one period, scaled to fine-grid units, keyed by cell and radix-sorted
-// once per (point set, fine grid); every later spread/interp streams them in cell order.
+// Points are folded to one period, scaled to fine-grid units and ordered by cell once per
+// (point set, fine grid); every later spread / interp streams them in cell order.
+//
+// Why not a library radix sort + gather: moving an 8- or 16-byte payload through a RANDOM permutation
+// of 1e8 elements costs one 32-byte DRAM sector per element (measured: 2.0-2.3 ms per payload array,
+// 4.2 ms for the scattered type-2 result), and an LSD radix sort on (key, index) needs three more passes.
+// Here the permutation is factored into two stages that are each sector-efficient:
+//
+//   level 1  original order -> <= 256 coarse buckets (contiguous cell ranges = bands of grid rows).
+//            One CTA bucket-sorts a tile of 2048 points in shared memory and writes each bucket's
+//            run contiguously, so DRAM sees full sectors.  A[i] = level-1 position of point i.
+//   level 2  inside a bucket (N/256 points: a few MB, L2 resident) a counting sort by cell places the
+//            points in their final slots.  Binv[slot] = level-1 position of the point in that slot.
+//
+// Later transforms move per-point data through the same two stages: strengths c[i] -> tmp[A[i]]
+// (coalesced reads, bucket runs) -> cs[slot] = tmp[Binv[slot]] (gather inside an L2-sized window);
+// type-2 results go back the other way (interp writes tmp[Binv[slot]], then out[i] = tmp[A[i]]).
 #include "nufft.cuh"
-#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <algorithm>
 
 namespace efgp {
 
 SortedPoints::~SortedPoints() {
-  for (int a = 0; a < kMaxDim; ++a)
-    if (xs[a]) pool_free(xs[a]);
-  if (perm) pool_free(perm);
+  if (rec) pool_free(rec);
+  if (A) pool_free(A);
+  if (tileStart) pool_free(tileStart);
 }
 
 // Scratch comes from the caching pool (pool.cpp): handles are rebuilt every hyperparameter step and a
@@ -40,112 +56,535 @@ struct FoldParams {
   T shift;
 };
 
+struct SortGeom {
+  uint32_t cpb;     // cells per level-1 bucket (contiguous range of flattened cell indices)
+  uint32_t g;       // cells per level-2 bin (1 = exact cell sort)
+  int nb1;          // level-1 buckets (<= kMaxBuckets)
+  int nbins2;       // level-2 bins per bucket (<= kMaxBins2)
+  int log2P;        // points per thread of the tile-transposed layout
+};
+
+constexpr int kMaxBuckets = 256;
+constexpr int kMaxBins2 = 8192;
+constexpr int kSortThreads = 256;
+constexpr int kSortPer = 8;
+static_assert(kSortThreads == kMaxBuckets, "the permutation kernels use one thread per bucket");
+constexpr int kSortTile = kSortThreads * kSortPer;  // 2048 points per CTA (43 KB of staging: 5 CTAs per SM)
+
 // fine-grid coordinate of one coordinate value, shifted by 1/2 for odd widths, in [0, nf)
 template <typename T>
-__device__ __forceinline__ T fold_coord(T xv, T h, T xc, T nf, T shift) {
+__device__ __forceinline__ T fold_coord(T xv, T h, T xc, T nf, T shift, int inf) {
   T t = h * (xv - xc);
   t -= floor(t);
   T X = t * nf + shift;
   if (X >= nf) X -= nf;
   if (!(X >= T(0)) || X >= nf) X = T(0);  // rounding at the period edge (and NaN guard)
+  if ((int)X >= inf) X = T(0);
   return X;
 }
 
 template <typename T, int D>
-__global__ void __launch_bounds__(256) key_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p,
-                                                  uint32_t* __restrict__ keys, uint32_t* __restrict__ idx) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= N) return;
+__device__ __forceinline__ uint32_t fold_point(const T* __restrict__ x, int64_t i, const FoldParams<T>& p, T* X) {
   uint32_t key = 0;
 #pragma unroll
   for (int a = 0; a < D; ++a) {
-    T X = fold_coord(x[i * D + a], p.h, p.xcen[a], p.nf[a], p.shift);
-    int c = (int)X;
-    if (c >= p.inf[a]) c = p.inf[a] - 1;
-    key = key * (uint32_t)p.inf[a] + (uint32_t)c;
+    X[a] = fold_coord(x[i * D + a], p.h, p.xcen[a], p.nf[a], p.shift, p.inf[a]);
+    key = key * (uint32_t)p.inf[a] + (uint32_t)(int)X[a];
   }
-  keys[i] = key;
-  idx[i] = (uint32_t)i;
+  return key;
 }
 
-// One thread per SLOT (coalesced writes); the slot's sorted rank follows from the tile-transposed
-// layout described in nufft.cuh.
-// Slots [pos0, pos1) belong to the chunk whose points are the original indices [lo, lo + n): ranks are
-// chunk-local sort positions, `sorted_idx` holds chunk-local indices.
+// slot of sorted rank r in the tile-transposed layout (nufft.cuh)
+__device__ __forceinline__ int64_t slot_of_rank(int64_t r, int log2P) {
+  const int64_t tile_len = (int64_t)kTileThreads << log2P;
+  int64_t tile = r / tile_len;
+  int rr = (int)(r - tile * tile_len);
+  int t = rr >> log2P, j = rr & ((1 << log2P) - 1);
+  return tile * tile_len + (int64_t)j * kTileThreads + t;
+}
+
+// ------------------------------------------------------------------ level 1
 template <typename T, int D>
-__global__ void __launch_bounds__(256) gather_kernel(const T* __restrict__ x, int64_t N, int P, FoldParams<T> p,
-                                                     const uint32_t* __restrict__ sorted_idx,
-                                                     uint32_t* __restrict__ perm, T* __restrict__ o0,
-                                                     T* __restrict__ o1, T* __restrict__ o2, int64_t pos0,
-                                                     int64_t pos1, int64_t lo) {
-  int64_t pos = pos0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (pos >= pos1) return;
-  const int64_t tile_len = (int64_t)kTileThreads * P;
-  int64_t tile = pos / tile_len;
-  int r = (int)(pos - tile * tile_len);
-  int j = r / kTileThreads, t = r - j * kTileThreads;
-  int64_t rank = tile * tile_len + (int64_t)t * P + j;
-  T* outs[3] = {o0, o1, o2};
-  if (rank >= N) {
-    outs[0][pos] = T(-1);
+__global__ void __launch_bounds__(kSortThreads)
+bucket_hist_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortGeom g, int ntiles1,
+                   uint32_t* __restrict__ tileHist) {
+  __shared__ uint32_t cnt[kMaxBuckets];
+  const int tid = threadIdx.x;
+  const int64_t tile = blockIdx.x;
+  if (tid < kMaxBuckets) cnt[tid] = 0;
+  __syncthreads();
 #pragma unroll
-    for (int a = 1; a < D; ++a) outs[a][pos] = T(0);
-    perm[pos] = 0;
-    return;
+  for (int k = 0; k < kSortPer; ++k) {
+    int64_t i = tile * kSortTile + k * kSortThreads + tid;
+    if (i < N) {
+      T X[D];
+      uint32_t key = fold_point<T, D>(x, i, p, X);
+      atomicAdd(&cnt[key / g.cpb], 1u);
+    }
   }
-  int64_t src = lo + sorted_idx[rank - pos0];
-  perm[pos] = (uint32_t)src;
+  __syncthreads();
+  for (int b = tid; b < g.nb1; b += kSortThreads) tileHist[(int64_t)b * ntiles1 + tile] = cnt[b];
+}
+
+// One CTA: bucket-sort its 2048 points in shared memory, then write each bucket's run contiguously.
+template <typename T, int D>
+__global__ void __launch_bounds__(kSortThreads)
+bucket_scatter_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortGeom g, int ntiles1,
+                      const uint32_t* __restrict__ tileStart, T* __restrict__ R0, T* __restrict__ R1,
+                      T* __restrict__ R2, uint16_t* __restrict__ K2, uint32_t* __restrict__ A) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* S = (T*)smem_raw;                                   // [D][kSortTile]
+  uint16_t* SK = (uint16_t*)(S + D * kSortTile);         // level-2 bin
+  uint16_t* SB = SK + kSortTile;                         // level-1 bucket
+  uint32_t* cnt = (uint32_t*)(SB + kSortTile);           // [kMaxBuckets]
+  uint32_t* lstart = cnt + kMaxBuckets;
+  uint32_t* gstart = lstart + kMaxBuckets;
+  const int tid = threadIdx.x;
+  const int64_t tile = blockIdx.x;
+  if (tid < kMaxBuckets) cnt[tid] = 0;
+  __syncthreads();
+  T X[kSortPer][D];
+  uint32_t bk[kSortPer], lr[kSortPer];
+  uint16_t k2[kSortPer];
 #pragma unroll
-  for (int a = 0; a < D; ++a) {
-    T X = fold_coord(x[src * D + a], p.h, p.xcen[a], p.nf[a], p.shift);
-    if ((int)X >= p.inf[a]) X = T(0);
-    outs[a][pos] = X;
+  for (int k = 0; k < kSortPer; ++k) {
+    int64_t i = tile * kSortTile + k * kSortThreads + tid;
+    bk[k] = 0xffffffffu;
+    if (i < N) {
+      uint32_t key = fold_point<T, D>(x, i, p, X[k]);
+      uint32_t b = key / g.cpb;
+      bk[k] = b;
+      k2[k] = (uint16_t)((key - b * g.cpb) / g.g);
+      lr[k] = atomicAdd(&cnt[b], 1u);
+    }
+  }
+  __syncthreads();
+  if (tid < kMaxBuckets) {   // exclusive scan of the 256 bucket counts: warp scans + 8 warp totals
+    const uint32_t c = cnt[tid];
+    uint32_t v = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+      if ((tid & 31) >= o) v += u;
+    }
+    if ((tid & 31) == 31) gstart[tid >> 5] = v;   // gstart doubles as scratch for the warp totals
+    lstart[tid] = v - c;
+  }
+  __syncthreads();
+  uint32_t woff = 0;
+  if (tid < kMaxBuckets)
+    for (int q = 0; q < (tid >> 5); ++q) woff += gstart[q];
+  __syncthreads();
+  if (tid < kMaxBuckets) {
+    lstart[tid] += woff;
+    gstart[tid] = tid < g.nb1 ? tileStart[(int64_t)tid * ntiles1 + tile] : 0u;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < kSortPer; ++k) {
+    if (bk[k] != 0xffffffffu) {
+      int64_t i = tile * kSortTile + k * kSortThreads + tid;
+      uint32_t lp = lstart[bk[k]] + lr[k];
+#pragma unroll
+      for (int a = 0; a < D; ++a) S[a * kSortTile + lp] = X[k][a];
+      SK[lp] = k2[k];
+      SB[lp] = (uint16_t)bk[k];
+      A[i] = gstart[bk[k]] + lr[k];
+    }
+  }
+  __syncthreads();
+  const int64_t rem = N - tile * kSortTile;
+  const int n_tile = rem < kSortTile ? (int)rem : kSortTile;
+  T* R[3] = {R0, R1, R2};
+  for (int lp = tid; lp < n_tile; lp += kSortThreads) {
+    uint32_t b = SB[lp];
+    uint32_t a = gstart[b] + ((uint32_t)lp - lstart[b]);
+#pragma unroll
+    for (int d = 0; d < D; ++d) R[d][a] = S[d * kSortTile + lp];
+    K2[a] = SK[lp];
+  }
+}
+
+// one record = RW words, written with one aligned vector store (a 32-byte record is one 256-bit store)
+template <typename T, int RW>
+__device__ __forceinline__ void store_record(T* dst, const T (&w)[RW]) {
+  if constexpr (sizeof(T) * RW == 32) {
+    const double* wd = reinterpret_cast<const double*>(w);
+    st_global_256(reinterpret_cast<double*>(dst), wd[0], wd[1], wd[2], wd[3]);
+  } else if constexpr (sizeof(T) * RW == 16) {
+    const double* wd = reinterpret_cast<const double*>(w);
+    reinterpret_cast<double2*>(dst)[0] = make_double2(wd[0], wd[1]);
+  } else {
+    reinterpret_cast<double*>(dst)[0] = *reinterpret_cast<const double*>(w);
+  }
+}
+
+// ------------------------------------------------------------------ level 2
+// Level-2 tiles never straddle buckets: bucket b owns tiles [tile2Base[b], tile2Base[b+1]).
+__global__ void __launch_bounds__(kMaxBuckets)
+level2_tiles_kernel(const uint32_t* __restrict__ tileStart, int ntiles1, int nb1, int64_t N,
+                    uint32_t* __restrict__ bucketStart /* nb1+1 */, uint32_t* __restrict__ tile2Base /* nb1+1 */) {
+  __shared__ uint32_t tl[kMaxBuckets + 1];
+  const int b = threadIdx.x;
+  uint32_t s = 0, e = 0;
+  if (b < nb1) {
+    s = tileStart[(int64_t)b * ntiles1];
+    e = b + 1 < nb1 ? tileStart[(int64_t)(b + 1) * ntiles1] : (uint32_t)N;
+    bucketStart[b] = s;
+    if (b == nb1 - 1) bucketStart[nb1] = (uint32_t)N;
+  }
+  tl[b] = b < nb1 ? (e - s + kSortTile - 1) / kSortTile : 0u;
+  __syncthreads();
+  if (b == 0) {
+    uint32_t acc = 0;
+    for (int q = 0; q < nb1; ++q) {
+      uint32_t c = tl[q];
+      tile2Base[q] = acc;
+      acc += c;
+    }
+    tile2Base[nb1] = acc;
+  }
+}
+
+__device__ __forceinline__ bool level2_tile_range(const uint32_t* __restrict__ bucketStart,
+                                                  const uint32_t* __restrict__ tile2Base, int nb1, int& b,
+                                                  uint32_t& s, uint32_t& e) {
+  const uint32_t tile = blockIdx.x;
+  if (tile >= tile2Base[nb1]) return false;
+  int lo = 0, hi = nb1;                 // last b with tile2Base[b] <= tile
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (tile2Base[mid] <= tile) lo = mid; else hi = mid;
+  }
+  b = lo;
+  s = bucketStart[b] + (tile - tile2Base[b]) * kSortTile;
+  uint32_t be = bucketStart[b + 1];
+  e = s + kSortTile < be ? s + kSortTile : be;
+  return true;
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+bin_hist_kernel(const uint16_t* __restrict__ K2, const uint32_t* __restrict__ bucketStart,
+                const uint32_t* __restrict__ tile2Base, SortGeom g, uint32_t* __restrict__ binCount) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint32_t* cnt = (uint32_t*)smem_raw;  // [nbins2]
+  int b;
+  uint32_t s, e;
+  if (!level2_tile_range(bucketStart, tile2Base, g.nb1, b, s, e)) return;
+  for (int q = threadIdx.x; q < g.nbins2; q += kSortThreads) cnt[q] = 0;
+  __syncthreads();
+  for (uint32_t a = s + threadIdx.x; a < e; a += kSortThreads) atomicAdd(&cnt[K2[a]], 1u);
+  __syncthreads();
+  for (int q = threadIdx.x; q < g.nbins2; q += kSortThreads) {
+    uint32_t c = cnt[q];
+    if (c) atomicAdd(&binCount[(int64_t)b * g.nbins2 + q], c);
+  }
+}
+
+template <typename T, int D>
+__global__ void __launch_bounds__(kSortThreads)
+bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* __restrict__ R2,
+                   const uint16_t* __restrict__ K2, const uint32_t* __restrict__ bucketStart,
+                   const uint32_t* __restrict__ tile2Base, SortGeom g, const uint32_t* __restrict__ binStart,
+                   uint32_t* __restrict__ binCursor, T* __restrict__ rec) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint32_t* cnt = (uint32_t*)smem_raw;   // [nbins2] counts, then running ranks
+  uint32_t* base = cnt + g.nbins2;       // [nbins2] first sorted rank of this tile's points in the bin
+  int b;
+  uint32_t s, e;
+  if (!level2_tile_range(bucketStart, tile2Base, g.nb1, b, s, e)) return;
+  for (int q = threadIdx.x; q < g.nbins2; q += kSortThreads) cnt[q] = 0;
+  __syncthreads();
+  for (uint32_t a = s + threadIdx.x; a < e; a += kSortThreads) atomicAdd(&cnt[K2[a]], 1u);
+  __syncthreads();
+  for (int q = threadIdx.x; q < g.nbins2; q += kSortThreads) {
+    uint32_t c = cnt[q];
+    if (c) {
+      int64_t gb = (int64_t)b * g.nbins2 + q;
+      base[q] = binStart[gb] + atomicAdd(&binCursor[gb], c);
+    }
+    cnt[q] = 0;
+  }
+  __syncthreads();
+  const T* R[3] = {R0, R1, R2};
+  constexpr int RW = rec_words(D);
+  for (uint32_t a = s + threadIdx.x; a < e; a += kSortThreads) {
+    uint32_t q = K2[a];
+    uint32_t r = base[q] + atomicAdd(&cnt[q], 1u);
+    int64_t slot = slot_of_rank((int64_t)r, g.log2P);
+    T w[RW];
+#pragma unroll
+    for (int d = 0; d < RW; ++d) w[d] = T(0);
+#pragma unroll
+    for (int d = 0; d < D; ++d) w[d] = R[d][a];
+    *reinterpret_cast<uint32_t*>(&w[D]) = a;
+    store_record<T, RW>(rec + slot * RW, w);
+  }
+}
+
+template <typename T, int D>
+__global__ void __launch_bounds__(256)
+pad_slots_kernel(int64_t N, int64_t npos, int log2P, T* __restrict__ rec) {
+  int64_t r = N + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= npos) return;
+  int64_t slot = slot_of_rank(r, log2P);
+  constexpr int RW = rec_words(D);
+  T w[RW];
+#pragma unroll
+  for (int d = 0; d < RW; ++d) w[d] = T(0);
+  w[0] = T(-1);
+  *reinterpret_cast<uint32_t*>(&w[D]) = 0xffffffffu;
+  store_record<T, RW>(rec + slot * RW, w);
+}
+
+// ------------------------------------------------------------------ per-point data through the two stages
+// Per-tile view of the level-1 permutation, rebuilt from the persistent tileStart table: bucket b's
+// points of this tile sit at global positions [gstart[b], gstart[b] + cnt[b]) and, bucket-major, at
+// tile-local positions [lstart[b], lstart[b] + cnt[b]).  Needs blockDim.x == kMaxBuckets.
+__device__ __forceinline__ void tile_bucket_ranges(const uint32_t* __restrict__ tileStart, int ntiles1, int nb1,
+                                                   int64_t N, int64_t tile, uint32_t* gstart, uint32_t* lstart,
+                                                   uint32_t* wsum) {
+  const int tid = threadIdx.x;
+  uint32_t gs = 0xffffffffu, c = 0;
+  if (tid < nb1) {
+    const int64_t idx = (int64_t)tid * ntiles1 + tile;
+    gs = tileStart[idx];
+    const uint32_t ge = idx + 1 < (int64_t)nb1 * ntiles1 ? tileStart[idx + 1] : (uint32_t)N;
+    c = ge - gs;
+  }
+  uint32_t v = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+    if ((tid & 31) >= o) v += u;
+  }
+  if ((tid & 31) == 31) wsum[tid >> 5] = v;
+  __syncthreads();
+  uint32_t woff = 0;
+  for (int q = 0; q < (tid >> 5); ++q) woff += wsum[q];
+  gstart[tid] = gs;
+  lstart[tid] = woff + v - c;
+  __syncthreads();
+}
+// last b in [0, n) with key[b] <= v (key ascending, key[0] <= v)
+__device__ __forceinline__ int last_le(const uint32_t* key, int n, uint32_t v) {
+  int lo = 0, hi = n;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (key[mid] <= v) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// tmp[A[i]] = c[i]: the tile's values are bucket-ordered in shared memory, then each bucket's run is written
+// contiguously (full sectors, few L2 requests) instead of one scattered 8-byte store per point.
+template <typename T>
+__global__ void __launch_bounds__(kMaxBuckets)
+to_bucket_order_kernel(const T* __restrict__ c, int64_t cstride, const uint32_t* __restrict__ A, int64_t N,
+                       const uint32_t* __restrict__ tileStart, int ntiles1, int nb1, T* __restrict__ tmp) {
+  __shared__ T S[kSortTile];
+  __shared__ uint8_t SB[kSortTile];
+  __shared__ uint32_t gstart[kMaxBuckets], lstart[kMaxBuckets], wsum[8];
+  const int tid = threadIdx.x;
+  const int64_t tile = blockIdx.x;
+  tile_bucket_ranges(tileStart, ntiles1, nb1, N, tile, gstart, lstart, wsum);
+#pragma unroll
+  for (int k = 0; k < kSortPer; ++k) {
+    int64_t i = tile * kSortTile + k * kSortThreads + tid;
+    if (i < N) {
+      uint32_t a = A[i];
+      int b = last_le(gstart, nb1, a);
+      uint32_t lp = lstart[b] + (a - gstart[b]);
+      S[lp] = c[i * cstride];
+      SB[lp] = (uint8_t)b;
+    }
+  }
+  __syncthreads();
+  const int64_t rem = N - tile * kSortTile;
+  const int n_tile = rem < kSortTile ? (int)rem : kSortTile;
+  for (int lp = tid; lp < n_tile; lp += kSortThreads) {
+    int b = SB[lp];
+    tmp[gstart[b] + ((uint32_t)lp - lstart[b])] = S[lp];
+  }
+}
+
+// out[i] = tmp[A[i]]: each bucket's run of this tile is read contiguously into shared memory, then every
+// point picks its value from there.
+template <typename T>
+__global__ void __launch_bounds__(kMaxBuckets)
+from_bucket_order_kernel(const T* __restrict__ tmp, const uint32_t* __restrict__ A, int64_t N,
+                         const uint32_t* __restrict__ tileStart, int ntiles1, int nb1, T* __restrict__ out,
+                         int64_t ostride) {
+  __shared__ T S[kSortTile];
+  __shared__ uint32_t gstart[kMaxBuckets], lstart[kMaxBuckets], wsum[8];
+  const int tid = threadIdx.x;
+  const int64_t tile = blockIdx.x;
+  tile_bucket_ranges(tileStart, ntiles1, nb1, N, tile, gstart, lstart, wsum);
+  const int64_t rem = N - tile * kSortTile;
+  const int n_tile = rem < kSortTile ? (int)rem : kSortTile;
+  for (int lp = tid; lp < n_tile; lp += kSortThreads) {
+    int b = last_le(lstart, nb1, (uint32_t)lp);
+    S[lp] = tmp[gstart[b] + ((uint32_t)lp - lstart[b])];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < kSortPer; ++k) {
+    int64_t i = tile * kSortTile + k * kSortThreads + tid;
+    if (i < N) {
+      uint32_t a = A[i];
+      int b = last_le(gstart, nb1, a);
+      out[i * ostride] = S[lstart[b] + (a - gstart[b])];
+    }
   }
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) permute_kernel(const T* __restrict__ c, int64_t cstride,
-                                                      const uint32_t* __restrict__ perm, int64_t npos,
-                                                      T* __restrict__ cs) {
+__global__ void __launch_bounds__(256)
+to_slot_order_kernel(const T* __restrict__ tmp, const T* __restrict__ rec, int RW, int dim, int64_t npos,
+                     T* __restrict__ cs) {
   int64_t pos = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (pos >= npos) return;
-  cs[pos] = c[(int64_t)perm[pos] * cstride];
+  uint32_t a = *reinterpret_cast<const uint32_t*>(rec + pos * RW + dim);
+  cs[pos] = a == 0xffffffffu ? T(0) : tmp[a];
 }
 
 void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, void* cs, cudaStream_t st) {
   if (sp.npos == 0) return;
-  int nb = div_up(sp.npos, 256);
-  ScopedStage stg("permute_strengths", st, 1, sp.N);
+  const size_t esz = sp.dtype == 0 ? 4 : 8;
+  void* tmp = pool_alloc(esz * (size_t)sp.N);
+  {
+    ScopedStage stg("permute.to_bucket_order", st, 1, sp.N);
+    if (sp.dtype == 0)
+      to_bucket_order_kernel<float><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const float*)c, cstride, sp.A, sp.N,
+                                                                        sp.tileStart, sp.ntiles1, sp.nb1, (float*)tmp);
+    else
+      to_bucket_order_kernel<double><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const double*)c, cstride, sp.A, sp.N,
+                                                                         sp.tileStart, sp.ntiles1, sp.nb1, (double*)tmp);
+  }
+  {
+    ScopedStage stg("permute.to_slot_order", st, 1, sp.N);
+    if (sp.dtype == 0)
+      to_slot_order_kernel<float><<<div_up(sp.npos, 256), 256, 0, st>>>((const float*)tmp, (const float*)sp.rec, sp.RW,
+                                                                        sp.dim, sp.npos, (float*)cs);
+    else
+      to_slot_order_kernel<double><<<div_up(sp.npos, 256), 256, 0, st>>>((const double*)tmp, (const double*)sp.rec,
+                                                                         sp.RW, sp.dim, sp.npos, (double*)cs);
+  }
+  EFGP_CUDA(cudaGetLastError());
+  pool_free(tmp);  // stream-ordered reuse
+}
+
+void unpermute_output(const SortedPoints& sp, const void* tmp, void* out, int64_t ostride, cudaStream_t st) {
+  if (sp.N == 0) return;
+  ScopedStage stg("unpermute.from_bucket_order", st, 1, sp.N);
   if (sp.dtype == 0)
-    permute_kernel<float><<<nb, 256, 0, st>>>((const float*)c, cstride, sp.perm, sp.npos, (float*)cs);
+    from_bucket_order_kernel<float><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const float*)tmp, sp.A, sp.N, sp.tileStart,
+                                                                        sp.ntiles1, sp.nb1, (float*)out, ostride);
   else
-    permute_kernel<double><<<nb, 256, 0, st>>>((const double*)c, cstride, sp.perm, sp.npos, (double*)cs);
+    from_bucket_order_kernel<double><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const double*)tmp, sp.A, sp.N, sp.tileStart,
+                                                                         sp.ntiles1, sp.nb1, (double*)out, ostride);
   EFGP_CUDA(cudaGetLastError());
 }
 
+// ------------------------------------------------------------------ host driver
 static int pick_points_per_thread(int64_t N) {
   // >= 4 waves of 148 SMs x 256 threads when N allows, and long register runs when N is large
   int64_t P = N / (148 * 256 * 4);
   if (P < 1) P = 1;
   if (P > 128) P = 128;
   int p2 = 1;
-  while (p2 * 2 <= P) p2 *= 2;   // power of two: the gather kernel reads the sort output in 8-wide chunks
+  while (p2 * 2 <= P) p2 *= 2;
   return p2;
 }
 
-// Points per sort chunk: a whole number of tiles, sized so that one chunk's coordinates plus the sort's
-// key/index ping-pong buffers (d*word + 16 bytes per point) fit comfortably in L2.  EFGP_SORT_CHUNK
-// (points) overrides it; 0 or a value >= N gives one global sort.
-static int64_t pick_sort_chunk(int64_t N, int64_t tile_len, int dim, size_t word) {
-  int64_t target = (int64_t)((48ull << 20) / (dim * word + 16));   // ~48 MB working set
-  if (const char* e = getenv("EFGP_SORT_CHUNK")) {
-    long long v = atoll(e);
-    target = v <= 0 ? N : (int64_t)v;
+template <typename T, int D>
+static void build_td(SortedPoints& sp, const T* x, int64_t N, const FoldParams<T>& p, const SortGeom& g,
+                     cudaStream_t st) {
+  const int ntiles1 = div_up(N, kSortTile);
+  const int64_t nhist = (int64_t)g.nb1 * ntiles1;
+  const int64_t nbin = (int64_t)g.nb1 * g.nbins2;
+  // scratch (returned to the pool at the end; reuse is stream-ordered)
+  uint32_t* tileHist = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)nhist);
+  uint32_t* tileStart = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)nhist);   // kept: sp.tileStart
+  sp.tileStart = tileStart;
+  sp.ntiles1 = ntiles1;
+  sp.nb1 = g.nb1;
+  uint32_t* meta = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)(2 * (g.nb1 + 1) + 3 * nbin));
+  uint32_t* bucketStart = meta;
+  uint32_t* tile2Base = meta + (g.nb1 + 1);
+  uint32_t* binCount = tile2Base + (g.nb1 + 1);
+  uint32_t* binStart = binCount + nbin;
+  uint32_t* binCursor = binStart + nbin;
+  T* R[3] = {nullptr, nullptr, nullptr};
+  for (int a = 0; a < D; ++a) R[a] = (T*)pool_alloc(sizeof(T) * (size_t)N);
+  uint16_t* K2 = (uint16_t*)pool_alloc(sizeof(uint16_t) * (size_t)N);
+  size_t scan_bytes = 0, sb2 = 0;
+  EFGP_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, tileHist, tileStart, (int)nhist, st));
+  EFGP_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, sb2, binCount, binStart, (int)nbin, st));
+  scan_bytes = std::max(scan_bytes, sb2);
+  void* scan_tmp = pool_alloc(scan_bytes);
+
+  sp.A = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
+  sp.RW = rec_words(D);
+  sp.rec = pool_alloc(sizeof(T) * (size_t)sp.RW * (size_t)sp.npos);
+  T* rec = (T*)sp.rec;
+
+  {
+    ScopedStage stg("sort.bucket_hist_kernel", st, 1, N);
+    bucket_hist_kernel<T, D><<<ntiles1, kSortThreads, 0, st>>>(x, N, p, g, ntiles1, tileHist);
   }
-  int64_t ntile_total = (N + tile_len - 1) / tile_len;
-  int64_t tiles = std::max<int64_t>(1, target / tile_len);
-  if (tiles * 3 >= ntile_total * 2) tiles = ntile_total;            // not worth splitting
-  return tiles * tile_len;
+  {
+    ScopedStage stg("sort.scans", st, 0, 0);
+    size_t tb = scan_bytes;
+    EFGP_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, tb, tileHist, tileStart, (int)nhist, st));
+    EFGP_CUDA(cudaMemsetAsync(binCount, 0, sizeof(uint32_t) * (size_t)nbin, st));
+    EFGP_CUDA(cudaMemsetAsync(binCursor, 0, sizeof(uint32_t) * (size_t)nbin, st));
+  }
+  {
+    ScopedStage stg("sort.bucket_scatter_kernel", st, 1, N);
+    const size_t smem = (size_t)D * kSortTile * sizeof(T) + 2 * kSortTile * sizeof(uint16_t) +
+                        3 * kMaxBuckets * sizeof(uint32_t);
+    static bool attr_set = false;
+    if (!attr_set) {
+      EFGP_CUDA(cudaFuncSetAttribute(bucket_scatter_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(3 * kSortTile * sizeof(double) + 2 * kSortTile * sizeof(uint16_t) +
+                                           3 * kMaxBuckets * sizeof(uint32_t))));
+      attr_set = true;
+    }
+    bucket_scatter_kernel<T, D><<<ntiles1, kSortThreads, smem, st>>>(x, N, p, g, ntiles1, tileStart, R[0], R[1],
+                                                                     R[2], K2, sp.A);
+  }
+  const int ntiles2_max = ntiles1 + g.nb1;
+  {
+    ScopedStage stg("sort.bin_hist_kernel", st, 2, N);
+    level2_tiles_kernel<<<1, kMaxBuckets, 0, st>>>(tileStart, ntiles1, g.nb1, N, bucketStart, tile2Base);
+    bin_hist_kernel<<<ntiles2_max, kSortThreads, g.nbins2 * sizeof(uint32_t), st>>>(K2, bucketStart, tile2Base, g,
+                                                                                    binCount);
+  }
+  {
+    ScopedStage stg("sort.scans", st, 0, 0);
+    size_t tb = scan_bytes;
+    EFGP_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, tb, binCount, binStart, (int)nbin, st));
+  }
+  {
+    ScopedStage stg("sort.bin_scatter_kernel", st, 2, N);
+    static bool attr_set2 = false;
+    if (!attr_set2) {
+      EFGP_CUDA(cudaFuncSetAttribute(bin_scatter_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)(2 * kMaxBins2 * sizeof(uint32_t))));
+      attr_set2 = true;
+    }
+    bin_scatter_kernel<T, D><<<ntiles2_max, kSortThreads, 2 * g.nbins2 * sizeof(uint32_t), st>>>(
+        R[0], R[1], R[2], K2, bucketStart, tile2Base, g, binStart, binCursor, rec);
+    if (sp.npos > N)
+      pad_slots_kernel<T, D><<<div_up(sp.npos - N, 256), 256, 0, st>>>(N, sp.npos, g.log2P, rec);
+  }
+  EFGP_CUDA(cudaGetLastError());
+  pool_free(scan_tmp);
+  pool_free(K2);
+  for (int a = 0; a < D; ++a) pool_free(R[a]);
+  pool_free(meta);
+  pool_free(tileHist);
 }
 
 template <typename T>
@@ -161,68 +600,26 @@ static void build_t(SortedPoints& sp, const T* x, int64_t N, int dim, double h, 
     p.inf[a] = a < dim ? (int)nf[a] : 1;
     if (a < dim) cells *= (double)nf[a];
   }
-  EFGP_CHECK(cells < 4.0e9, "fine grid has too many cells for 32-bit sort keys");
+  EFGP_CHECK(cells < 4.0e9, "fine grid has too many cells for 32-bit cell indices");
   EFGP_CHECK(N < (int64_t)2147483000, "N must be < 2^31");
-  int bits = 1;
-  while ((1ull << bits) < (unsigned long long)cells) ++bits;
+  const uint32_t ncell = (uint32_t)cells;
 
   sp.P = dim == 3 ? 1 : pick_points_per_thread(N);  // 3-D uses the per-point kernels: keep rank order
   const int64_t tile_len = (int64_t)kTileThreads * sp.P;
   sp.ntiles = (N + tile_len - 1) / tile_len;
   sp.npos = sp.ntiles * tile_len;
 
-  // Chunked sort.  The points are cut into chunks of consecutive ORIGINAL indices (a whole number of
-  // tiles each) and every chunk is cell-sorted on its own: key -> radix sort -> gather run back to back
-  // per chunk, so the chunk's coordinates, keys and indices stay resident in the 126 MB L2 between the
-  // three kernels, and -- because a chunk's slots only ever reference original indices of the same chunk --
-  // the strength gathers (permute_strengths) and the type-2 result scatters (interp) of later transforms
-  // hit an L2-sized window instead of issuing one 32-byte DRAM sector per 8-byte element.
-  const int64_t chunk = pick_sort_chunk(N, tile_len, dim, sizeof(T));
-  sp.chunk = chunk;
-  uint32_t* keys_in = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)chunk);
-  uint32_t* keys_out = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)chunk);
-  uint32_t* idx_in = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)chunk);
-  uint32_t* idx_out = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)chunk);
-  sp.perm = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)sp.npos);
-  for (int a = 0; a < dim; ++a) sp.xs[a] = pool_alloc(sizeof(T) * (size_t)sp.npos);
-  T* o0 = (T*)sp.xs[0];
-  T* o1 = (T*)sp.xs[1];
-  T* o2 = (T*)sp.xs[2];
-  size_t tmp_bytes = 0;
-  EFGP_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, idx_in, idx_out,
-                                            (int)std::min<int64_t>(chunk, N), 0, bits, st));
-  void* tmp = pool_alloc(tmp_bytes);
-  for (int64_t lo = 0; lo < sp.npos; lo += chunk) {
-    const int64_t n = std::min(chunk, N - lo);          // points of this chunk (> 0: npos - N < tile_len)
-    const int64_t pos1 = std::min(lo + chunk, sp.npos);
-    const T* xc = x + lo * dim;
-    int nb = div_up(n, 256);
-    {
-      ScopedStage stg("sort.key_kernel", st, 1, n);
-      if (dim == 1) key_kernel<T, 1><<<nb, 256, 0, st>>>(xc, n, p, keys_in, idx_in);
-      if (dim == 2) key_kernel<T, 2><<<nb, 256, 0, st>>>(xc, n, p, keys_in, idx_in);
-      if (dim == 3) key_kernel<T, 3><<<nb, 256, 0, st>>>(xc, n, p, keys_in, idx_in);
-    }
-    {
-      ScopedStage stg("sort.cub_radix_sort_pairs", st, 0, n);
-      size_t tb = tmp_bytes;
-      EFGP_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tb, keys_in, keys_out, idx_in, idx_out, (int)n, 0, bits, st));
-    }
-    int nbp = div_up(pos1 - lo, 256);
-    {
-      ScopedStage stg("sort.gather_kernel", st, 1, n);
-      if (dim == 1) gather_kernel<T, 1><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, lo, pos1, lo);
-      if (dim == 2) gather_kernel<T, 2><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, lo, pos1, lo);
-      if (dim == 3) gather_kernel<T, 3><<<nbp, 256, 0, st>>>(x, N, sp.P, p, idx_out, sp.perm, o0, o1, o2, lo, pos1, lo);
-    }
-    EFGP_CUDA(cudaGetLastError());
-  }
-  // scratch goes back to the pool; later users run on the same stream, so ordering is preserved
-  pool_free(tmp);
-  pool_free(keys_in);
-  pool_free(keys_out);
-  pool_free(idx_in);
-  pool_free(idx_out);
+  SortGeom g;
+  int nb1 = (int)std::min<uint32_t>(kMaxBuckets, ncell);
+  g.cpb = (ncell + nb1 - 1) / nb1;
+  g.nb1 = (int)((ncell + g.cpb - 1) / g.cpb);
+  g.g = (g.cpb + kMaxBins2 - 1) / kMaxBins2;          // > 1 only for grids above 2M cells (3-D): coarse order
+  g.nbins2 = (int)((g.cpb + g.g - 1) / g.g);
+  g.log2P = 0;
+  while ((1 << g.log2P) < sp.P) ++g.log2P;
+  if (dim == 1) build_td<T, 1>(sp, x, N, p, g, st);
+  if (dim == 2) build_td<T, 2>(sp, x, N, p, g, st);
+  if (dim == 3) build_td<T, 3>(sp, x, N, p, g, st);
 }
 
 void build_sorted_points(SortedPoints& sp, const void* x, int64_t N, int dim, int dtype, double h,

@@ -44,6 +44,17 @@ __device__ __forceinline__ void es_eval(const ESDev<T>& es, T s, T* __restrict__
   }
 }
 
+// 4-word record -> registers with 16-byte loads
+template <typename T>
+__device__ __forceinline__ void load_record4(const T* __restrict__ p, T* w) {
+  if constexpr (sizeof(T) == 8) {
+    ld_global_nc_256(reinterpret_cast<const double*>(p), w[0], w[1], w[2], w[3]);
+  } else {
+    float4 a = __ldg(reinterpret_cast<const float4*>(p));
+    w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w;
+  }
+}
+
 __device__ __forceinline__ int wrap_idx(int i, int n) {
   if (i < 0) i += n;
   if (i >= n) i -= n;
@@ -55,7 +66,7 @@ __device__ __forceinline__ int wrap_idx(int i, int n) {
 // ------------------------------------------------------------------ 1-D
 template <typename T, int W, bool HAS_C>
 __global__ void __launch_bounds__(kTileThreads)
-spread1d_kernel(const T* __restrict__ xs0, const T* __restrict__ cs, int P, int nf0, T* __restrict__ grid,
+spread1d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int nf0, T* __restrict__ grid,
                 const __grid_constant__ ESDev<T> es) {
   const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
   T acc[W];
@@ -65,7 +76,7 @@ spread1d_kernel(const T* __restrict__ xs0, const T* __restrict__ cs, int P, int 
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
   for (int j = 0; j < P; ++j) {
     const int64_t pos = base + (int64_t)j * kTileThreads;
-    T X = xs0[pos];
+    T X = rec[pos * 2];
     if (X < T(0)) break;
     T cv = HAS_C ? cs[pos] : T(1);
     int c0 = (int)X;
@@ -109,20 +120,19 @@ __device__ __forceinline__ void flush2d(T (&acc)[W][W], int c0, int c1, int nf0,
 
 template <typename T, int W, bool HAS_C>
 __global__ void __launch_bounds__(kTileThreads, 1)
-spread2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* __restrict__ cs, int P, int nf0,
+spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int nf0,
                 int nf1, T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
-  constexpr int NA = HAS_C ? 3 : 2;
   constexpr int S = kRingStages;
-  __shared__ T ring[S][NA][kTileThreads];
+  __shared__ __align__(16) T ring[S][kTileThreads][2];   // (X0, X1) of each thread's next points
+  __shared__ T cring[HAS_C ? S : 1][kTileThreads];
   const int t = threadIdx.x;
   const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + t;
   auto issue = [&](int j) {
     if (j < P) {
       const int64_t pos = base + (int64_t)j * kTileThreads;
       const int s = j % S;
-      cp_async_word<sizeof(T)>(&ring[s][0][t], xs0 + pos);
-      cp_async_word<sizeof(T)>(&ring[s][1][t], xs1 + pos);
-      if (HAS_C) cp_async_word<sizeof(T)>(&ring[s][NA - 1][t], cs + pos);
+      cp_async_word<2 * sizeof(T)>(&ring[s][t][0], rec + pos * 4);   // one 16-byte (8 for f32) copy per point
+      if (HAS_C) cp_async_word<sizeof(T)>(&cring[s][t], cs + pos);
     }
     cp_async_commit();
   };
@@ -138,10 +148,10 @@ spread2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* _
     issue(j + S - 1);
     cp_async_wait<S - 1>();
     const int s = j % S;
-    const T X0 = ring[s][0][t];
+    const T X0 = ring[s][t][0];
     if (X0 < T(0)) break;
-    const T X1 = ring[s][1][t];
-    const T cv = HAS_C ? ring[s][NA - 1][t] : T(1);
+    const T X1 = ring[s][t][1];
+    const T cv = HAS_C ? cring[s][t] : T(1);
     int c0 = (int)X0, c1 = (int)X1;
     if (c0 != cur0 || c1 != cur1) {
       if (cur0 >= 0) flush2d<T, W>(acc, cur0, cur1, nf0, nf1, grid);
@@ -166,24 +176,26 @@ spread2d_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* _
 // Points are still cell-sorted, so the reductions of neighbouring slots land in the same L2 lines.
 template <typename T, int W, int D, bool HAS_C>
 __global__ void __launch_bounds__(256)
-spread_direct_kernel(const T* __restrict__ xs0, const T* __restrict__ xs1, const T* __restrict__ xs2,
+spread_direct_kernel(const T* __restrict__ rec,
                      const T* __restrict__ cs, int64_t npos, int nf0, int nf1, int nf2, T* __restrict__ grid,
                      const __grid_constant__ ESDev<T> es) {
   int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= npos) return;
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
-  T X0 = xs0[n];
+  T Xr[4];
+  load_record4<T>(rec + n * 4, Xr);
+  T X0 = Xr[0];
   if (X0 < T(0)) return;
   T cv = HAS_C ? cs[n] : T(1);
   T k0[W], k1[W], k2[W];
   int c0 = (int)X0;
   es_eval<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
-  T X1 = xs1[n];
+  T X1 = Xr[1];
   int c1 = (int)X1;
   es_eval<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
   int c2 = 0;
   if (D == 3) {
-    T X2 = xs2[n];
+    T X2 = Xr[2];
     c2 = (int)X2;
     es_eval<T, W>(es, T(2) * (X2 - (T)c2) - T(1), k2);
   }
@@ -218,9 +230,7 @@ template <typename T, int W>
 static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st) {
   ESDev<T> es;
   es_to_dev<T>(k, es);
-  const T* x0 = (const T*)sp.xs[0];
-  const T* x1 = (const T*)sp.xs[1];
-  const T* x2 = (const T*)sp.xs[2];
+  const T* rec = (const T*)sp.rec;
   constexpr int kRegMaxW = sizeof(T) == 8 ? 9 : 10;
   const int nt = (int)sp.ntiles;
   char nm[48];
@@ -228,34 +238,34 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
   ScopedStage stg(nm, st, 1, sp.N);
   if (sp.dim == 1) {
     if (cs)
-      spread1d_kernel<T, W, true><<<nt, kTileThreads, 0, st>>>(x0, cs, sp.P, (int)sp.nf[0], grid, es);
+      spread1d_kernel<T, W, true><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, (int)sp.nf[0], grid, es);
     else
-      spread1d_kernel<T, W, false><<<nt, kTileThreads, 0, st>>>(x0, cs, sp.P, (int)sp.nf[0], grid, es);
+      spread1d_kernel<T, W, false><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, (int)sp.nf[0], grid, es);
   } else if (sp.dim == 2) {
     if constexpr (W <= kRegMaxW) {
       if (cs)
         spread2d_kernel<T, W, true>
-            <<<nt, kTileThreads, 0, st>>>(x0, x1, cs, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
+            <<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
       else
         spread2d_kernel<T, W, false>
-            <<<nt, kTileThreads, 0, st>>>(x0, x1, cs, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
+            <<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
     } else {
       int nb = div_up(sp.npos, 256);
       if (cs)
         spread_direct_kernel<T, W, 2, true>
-            <<<nb, 256, 0, st>>>(x0, x1, x2, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, es);
+            <<<nb, 256, 0, st>>>(rec, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, es);
       else
         spread_direct_kernel<T, W, 2, false>
-            <<<nb, 256, 0, st>>>(x0, x1, x2, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, es);
+            <<<nb, 256, 0, st>>>(rec, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, es);
     }
   } else {
     int nb = div_up(sp.npos, 256);
     if (cs)
       spread_direct_kernel<T, W, 3, true>
-          <<<nb, 256, 0, st>>>(x0, x1, x2, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, es);
+          <<<nb, 256, 0, st>>>(rec, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, es);
     else
       spread_direct_kernel<T, W, 3, false>
-          <<<nb, 256, 0, st>>>(x0, x1, x2, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, es);
+          <<<nb, 256, 0, st>>>(rec, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, es);
   }
   EFGP_CUDA(cudaGetLastError());
 }
