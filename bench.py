@@ -197,6 +197,7 @@ def algorithmic_bytes(stage, n, d=2, word=8):
         "sort.bin_scatter_kernel": word * d + 2 + word * d + 4,             # read coords, bin; write slots, Binv
         "permute.to_bucket_order": word + 4 + word,                         # read c, A; write tmp
         "permute.to_slot_order": 4 + word + word,                           # read Binv, tmp; write cs
+        "unpermute.slot_to_bucket_order": 4 + word + word,                  # read B, r; write tmp
         "unpermute.from_bucket_order": 4 + word + word,                     # read A, tmp; write out
     }
     if stage in per_point:

@@ -8,6 +8,7 @@
 // read-only path; the whole fine grid lives in L2) only when the cell changes.  Per point the
 // work is the kernel evaluation plus W^2 FMAs, and one scattered store of the result.
 #include "nufft.cuh"
+#include "stream_ring.cuh"
 
 namespace efgp {
 
@@ -76,7 +77,7 @@ interp1d_kernel(const T* __restrict__ rec, int P, int nf0,
     const int64_t pos = base + (int64_t)j * kTileThreads;
     T X = rec[pos * 2];
     if (X < T(0)) break;
-    const uint32_t bi = *reinterpret_cast<const uint32_t*>(rec + pos * 2 + 1);
+    const int64_t bi = pos;
     int c0 = (int)X;
     if (c0 != cur) {
 #pragma unroll
@@ -92,27 +93,37 @@ interp1d_kernel(const T* __restrict__ rec, int P, int nf0,
   }
 }
 
+// Narrow kernels (W <= 5) keep their W x W patch in <= 128 registers, so two CTAs share an SM; the point
+// records stream through a per-thread cp.async ring (stream_ring.cuh) deep enough to cover DRAM latency.
 template <typename T, int W>
-__global__ void __launch_bounds__(kTileThreads, 1)
+__global__ void __launch_bounds__(kTileThreads, (W <= 5 ? 2 : 1))
 interp2d_kernel(const T* __restrict__ rec, int P,
                 int nf0, int nf1, const T* __restrict__ grid, T* __restrict__ out, int64_t ostride,
                 const __grid_constant__ ESDev<T> es) {
-  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
+  constexpr int S = kRingStages;
+  __shared__ __align__(16) T ring[S][kTileThreads][2];      // (X0, X1) of each thread's next points
+  const int t = threadIdx.x;
+  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + t;
+  auto issue = [&](int j) {
+    if (j < P) {
+      const T* src = rec + (base + (int64_t)j * kTileThreads) * 4;
+      cp_async_word<2 * sizeof(T)>(&ring[j % S][t][0], src);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int j = 0; j < S - 1; ++j) issue(j);
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
   T g[W][W];
   int cur0 = -1, cur1 = -1;
-  T X0, X1, nX0 = T(-1), nX1 = T(0);
-  uint32_t pn, npn = 0;
-  load_point2<T>(rec + base * 4, X0, X1, pn);
-  if (P > 1) load_point2<T>(rec + (base + kTileThreads) * 4, nX0, nX1, npn);
   for (int j = 0; j < P; ++j) {
+    issue(j + S - 1);
+    cp_async_wait<S - 1>();
+    const int s = j % S;
+    const T X0 = ring[s][t][0];
     if (X0 < T(0)) break;
-    T fX0 = T(-1), fX1 = T(0);
-    uint32_t fpn = 0;
-    if (j + 2 < P) {
-      const int64_t pos = base + (int64_t)(j + 2) * kTileThreads;
-      load_point2<T>(rec + pos * 4, fX0, fX1, fpn);
-    }
+    const T X1 = ring[s][t][1];
+    const int64_t pn = base + (int64_t)j * kTileThreads;   // results in slot order: coalesced stores
     int c0 = (int)X0, c1 = (int)X1;
     if (c0 != cur0 || c1 != cur1) {
       int cols[W];
@@ -139,13 +150,8 @@ interp2d_kernel(const T* __restrict__ rec, int P,
       acc = fma(r, k0[i], acc);
     }
     out[pn] = acc;
-    X0 = nX0;
-    X1 = nX1;
-    pn = npn;
-    nX0 = fX0;
-    nX1 = fX1;
-    npn = fpn;
   }
+  cp_async_wait<0>();
 }
 
 // generic: wide 2-D kernels and 3-D, one slot per thread, gathers through L1/L2
@@ -162,7 +168,7 @@ interp_direct_kernel(const T* __restrict__ rec, int64_t npos, int nf0, int nf1, 
   load_record4i<T>(rec + n * 4, Xr);
   T X0 = Xr[0];
   if (X0 < T(0)) return;
-  const uint32_t bi = *reinterpret_cast<const uint32_t*>(&Xr[D]);
+  const int64_t bi = n;
   int c0 = (int)X0;
   es_eval_i<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
   T X1 = Xr[1];
@@ -254,10 +260,9 @@ void launch_interp(const SortedPoints& sp, const ESKernel& k, const void* grid, 
                    cudaStream_t st) {
   if (sp.N == 0) return;
   EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
-  // the kernels write bucket-order results tmp[Binv[slot]] (scatter inside an L2-sized window);
-  // unpermute_output then streams them back to original order through A
+  // the kernels write slot-order results (coalesced); unpermute_output gathers them back to original order
   const size_t esz = sp.dtype == 0 ? 4 : 8;
-  void* tmp = pool_alloc(esz * (size_t)sp.N);
+  void* tmp = pool_alloc(esz * (size_t)sp.npos);
   if (sp.dtype == 0)
     launch_t<float>(sp, k, (const float*)grid, (float*)tmp, 1, st);
   else

@@ -31,6 +31,7 @@ struct SortedPoints {
   int64_t npos = 0;     // ntiles * kTileThreads * P
   void* rec = nullptr;        // npos records
   uint32_t* A = nullptr;      // A[i] = level-1 (bucket-order) position of original point i      (N entries)
+  uint32_t* B = nullptr;      // B[a] = slot of the point at level-1 position a (inverse of the records' binv)
   uint32_t* tileStart = nullptr;  // [nb1][ntiles1]: first level-1 position of (bucket, 2048-point tile)
   int ntiles1 = 0, nb1 = 0;
   uint64_t last_use = 0;
@@ -90,8 +91,8 @@ void build_sorted_points(SortedPoints& sp, const void* x, int64_t N, int dim, in
 // ---- points.cu : cs[slot] = c[i * cstride] for the point i stored in that slot (npos entries), in two
 // sector-efficient stages (original -> bucket order -> slot order)
 void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, void* cs, cudaStream_t st);
-// out[i * ostride] = tmp[A[i]]: bucket-order results (written by interp through Binv) back to original order
-void unpermute_output(const SortedPoints& sp, const void* tmp, void* out, int64_t ostride, cudaStream_t st);
+// out[i * ostride] = r[B[A[i]]]: slot-order results (written coalesced by interp) back to original order
+void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t ostride, cudaStream_t st);
 
 // ---- spread.cu : grid (real, nf^d) += sum_n c_n psi(l - X_n).  cs == nullptr means all ones;
 // otherwise cs holds the strengths in SLOT order (permute_strengths).

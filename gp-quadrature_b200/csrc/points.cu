@@ -18,7 +18,8 @@
 //
 // Later transforms move per-point data through the same two stages: strengths c[i] -> tmp[A[i]]
 // (coalesced reads, bucket runs) -> cs[slot] = tmp[Binv[slot]] (gather inside an L2-sized window);
-// type-2 results go back the other way (interp writes tmp[Binv[slot]], then out[i] = tmp[A[i]]).
+// type-2 results are written in slot order (coalesced), gathered into bucket order (tmp[a] = r[B[a]],
+// B = Binv^-1, inside the bucket window) and streamed back as out[i] = tmp[A[i]].
 #include "nufft.cuh"
 #include <cub/device/device_scan.cuh>
 #include <algorithm>
@@ -28,6 +29,7 @@ namespace efgp {
 SortedPoints::~SortedPoints() {
   if (rec) pool_free(rec);
   if (A) pool_free(A);
+  if (B) pool_free(B);
   if (tileStart) pool_free(tileStart);
 }
 
@@ -286,7 +288,7 @@ __global__ void __launch_bounds__(kSortThreads)
 bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* __restrict__ R2,
                    const uint16_t* __restrict__ K2, const uint32_t* __restrict__ bucketStart,
                    const uint32_t* __restrict__ tile2Base, SortGeom g, const uint32_t* __restrict__ binStart,
-                   uint32_t* __restrict__ binCursor, T* __restrict__ rec) {
+                   uint32_t* __restrict__ binCursor, T* __restrict__ rec, uint32_t* __restrict__ B) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint32_t* cnt = (uint32_t*)smem_raw;   // [nbins2] counts, then running ranks
   uint32_t* base = cnt + g.nbins2;       // [nbins2] first sorted rank of this tile's points in the bin
@@ -319,6 +321,7 @@ bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* 
     for (int d = 0; d < D; ++d) w[d] = R[d][a];
     *reinterpret_cast<uint32_t*>(&w[D]) = a;
     store_record<T, RW>(rec + slot * RW, w);
+    B[a] = (uint32_t)slot;
   }
 }
 
@@ -408,13 +411,24 @@ to_bucket_order_kernel(const T* __restrict__ c, int64_t cstride, const uint32_t*
   }
 }
 
+// tmp[a] = r[B[a]]: slot-order results into bucket order.  a runs sequentially, so B and tmp stream and
+// the gathers from r stay inside the current bucket's L2-sized window.
+template <typename T>
+__global__ void __launch_bounds__(256)
+slot_to_bucket_order_kernel(const T* __restrict__ r, const uint32_t* __restrict__ B, int64_t N,
+                            T* __restrict__ tmp) {
+  int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= N) return;
+  tmp[a] = r[B[a]];
+}
+
 // out[i] = tmp[A[i]]: each bucket's run of this tile is read contiguously into shared memory, then every
-// point picks its value from there.
+// point picks its value from there and the output is written coalesced.
 template <typename T>
 __global__ void __launch_bounds__(kMaxBuckets)
-from_bucket_order_kernel(const T* __restrict__ tmp, const uint32_t* __restrict__ A, int64_t N,
-                         const uint32_t* __restrict__ tileStart, int ntiles1, int nb1, T* __restrict__ out,
-                         int64_t ostride) {
+from_bucket_order_kernel(const T* __restrict__ tmp, const uint32_t* __restrict__ A,
+                         int64_t N, const uint32_t* __restrict__ tileStart, int ntiles1, int nb1,
+                         T* __restrict__ out, int64_t ostride) {
   __shared__ T S[kSortTile];
   __shared__ uint32_t gstart[kMaxBuckets], lstart[kMaxBuckets], wsum[8];
   const int tid = threadIdx.x;
@@ -474,16 +488,28 @@ void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, v
   pool_free(tmp);  // stream-ordered reuse
 }
 
-void unpermute_output(const SortedPoints& sp, const void* tmp, void* out, int64_t ostride, cudaStream_t st) {
+void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t ostride, cudaStream_t st) {
   if (sp.N == 0) return;
-  ScopedStage stg("unpermute.from_bucket_order", st, 1, sp.N);
-  if (sp.dtype == 0)
-    from_bucket_order_kernel<float><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const float*)tmp, sp.A, sp.N, sp.tileStart,
-                                                                        sp.ntiles1, sp.nb1, (float*)out, ostride);
-  else
-    from_bucket_order_kernel<double><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const double*)tmp, sp.A, sp.N, sp.tileStart,
-                                                                         sp.ntiles1, sp.nb1, (double*)out, ostride);
+  const size_t esz = sp.dtype == 0 ? 4 : 8;
+  void* tmp = pool_alloc(esz * (size_t)sp.N);
+  {
+    ScopedStage stg("unpermute.slot_to_bucket_order", st, 1, sp.N);
+    if (sp.dtype == 0)
+      slot_to_bucket_order_kernel<float><<<div_up(sp.N, 256), 256, 0, st>>>((const float*)r, sp.B, sp.N, (float*)tmp);
+    else
+      slot_to_bucket_order_kernel<double><<<div_up(sp.N, 256), 256, 0, st>>>((const double*)r, sp.B, sp.N, (double*)tmp);
+  }
+  {
+    ScopedStage stg("unpermute.from_bucket_order", st, 1, sp.N);
+    if (sp.dtype == 0)
+      from_bucket_order_kernel<float><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const float*)tmp, sp.A, sp.N, sp.tileStart,
+                                                                          sp.ntiles1, sp.nb1, (float*)out, ostride);
+    else
+      from_bucket_order_kernel<double><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const double*)tmp, sp.A, sp.N, sp.tileStart,
+                                                                           sp.ntiles1, sp.nb1, (double*)out, ostride);
+  }
   EFGP_CUDA(cudaGetLastError());
+  pool_free(tmp);  // stream-ordered reuse
 }
 
 // ------------------------------------------------------------------ host driver
@@ -525,6 +551,7 @@ static void build_td(SortedPoints& sp, const T* x, int64_t N, const FoldParams<T
   void* scan_tmp = pool_alloc(scan_bytes);
 
   sp.A = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
+  sp.B = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
   sp.RW = rec_words(D);
   sp.rec = pool_alloc(sizeof(T) * (size_t)sp.RW * (size_t)sp.npos);
   T* rec = (T*)sp.rec;
@@ -575,7 +602,7 @@ static void build_td(SortedPoints& sp, const T* x, int64_t N, const FoldParams<T
       attr_set2 = true;
     }
     bin_scatter_kernel<T, D><<<ntiles2_max, kSortThreads, 2 * g.nbins2 * sizeof(uint32_t), st>>>(
-        R[0], R[1], R[2], K2, bucketStart, tile2Base, g, binStart, binCursor, rec);
+        R[0], R[1], R[2], K2, bucketStart, tile2Base, g, binStart, binCursor, rec, sp.B);
     if (sp.npos > N)
       pad_slots_kernel<T, D><<<div_up(sp.npos - N, 256), 256, 0, st>>>(N, sp.npos, g.log2P, rec);
   }

@@ -119,7 +119,7 @@ __device__ __forceinline__ void flush2d(T (&acc)[W][W], int c0, int c1, int nf0,
 }
 
 template <typename T, int W, bool HAS_C>
-__global__ void __launch_bounds__(kTileThreads, 1)
+__global__ void __launch_bounds__(kTileThreads, (W <= 5 ? 2 : 1))
 spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int nf0,
                 int nf1, T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
   constexpr int S = kRingStages;
