@@ -189,12 +189,12 @@ def algorithmic_bytes(stage, n, d=2, word=8):
     if stage.startswith("spread"):
         return n * word * (d + (0 if stage.endswith("_ones") else 1))      # coordinates (+ real strength)
     if stage.startswith("interp"):
-        return n * (word * d + 4 + word)                                    # coordinates + Binv + real result
+        return n * (word * d + word)                                        # coordinates + real result
     per_point = {
         "sort.bucket_hist_kernel": word * d,                                # read x
         "sort.bucket_scatter_kernel": word * d + word * d + 2 + 4,          # read x; write folded coords, bin, A
         "sort.bin_hist_kernel": 2,                                          # read level-2 bins
-        "sort.bin_scatter_kernel": word * d + 2 + word * d + 4,             # read coords, bin; write slots, Binv
+        "sort.bin_scatter_kernel": word * d + 2 + word * d + 4 + 4,         # read coords, bin; write record (coords, binv), B
         "permute.to_bucket_order": word + 4 + word,                         # read c, A; write tmp
         "permute.to_slot_order": 4 + word + word,                           # read Binv, tmp; write cs
         "unpermute.slot_to_bucket_order": 4 + word + word,                  # read B, r; write tmp
@@ -225,7 +225,8 @@ def main():
     from kernels.squared_exponential import SquaredExponential
 
     n_total = int(args.npts)
-    n_loc = n_total // world + (1 if rank < n_total % world else 0)
+    lo_pt, hi_pt = efgpnd.shard_bounds(n_total, world, rank)
+    n_loc = hi_pt - lo_pt
     x, y = synth(n_loc, 2, 1000 + rank, dev, torch.float64)
     opts = {"cg_tolerance": CG_TOL, "shard_points": world > 1}
     stats = {}

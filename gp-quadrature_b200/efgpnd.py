@@ -58,6 +58,36 @@ def _point_shard_group(opts):
     return group if dist.get_world_size(group) > 1 else None
 
 
+def _domain_length(x, group=None):
+    """L = max_d (max x_d - min x_d) (efgpnd.py:751), over ALL shards when the points are sharded: one
+    pass over the local x, then a MAX all-reduce of [max, -min]."""
+    d = x.shape[1]
+    lo_x, hi_x = torch.aminmax(x, dim=0)
+    if group is None:
+        return float(torch.max(hi_x - lo_x).item())
+    ext = torch.cat([hi_x, -lo_x])
+    torch.distributed.all_reduce(ext, op=torch.distributed.ReduceOp.MAX, group=group)
+    return float(torch.max(ext[:d] + ext[d:]).item())
+
+
+def _sum_over_shards(v_kernel, rhs, group=None):
+    """F^*1 and ws*F^*y are sums over points: ONE all-reduce of the two (cropped, deconvolved) mode grids
+    replaces the exchange of the sigma^d-times larger fine grids; every rank then solves the same system."""
+    if group is None:
+        return v_kernel, rhs
+    packed = torch.cat([v_kernel.reshape(-1), rhs.reshape(-1)])
+    torch.distributed.all_reduce(torch.view_as_real(packed), op=torch.distributed.ReduceOp.SUM, group=group)
+    nv = v_kernel.numel()
+    return packed[:nv].reshape(v_kernel.shape), packed[nv:].reshape(rhs.shape)
+
+
+def shard_bounds(n_total, world, rank):
+    """[lo, hi) of rank's contiguous point shard: sizes differ by at most one."""
+    base, extra = divmod(int(n_total), int(world))
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
 # ----------------------------------------------------------------------------- NUFFT
 _PLAN_CACHE: "OrderedDict[tuple, _ops.NufftPlan]" = OrderedDict()
 _PLAN_CACHE_SIZE = 3
@@ -742,15 +772,7 @@ class EFGPND(nn.Module):
             x = x[:, None]
         N, d = x.shape
         group = _point_shard_group(self.opts)
-        if group is None:
-            lo_x, hi_x = torch.aminmax(x, dim=0)            # one pass over x
-            L = float(torch.max(hi_x - lo_x).item())
-        else:
-            # points are sharded over the ranks: the box is the union of the shards' boxes
-            lo_x, hi_x = torch.aminmax(x, dim=0)
-            ext = torch.cat([hi_x, -lo_x])
-            torch.distributed.all_reduce(ext, op=torch.distributed.ReduceOp.MAX, group=group)
-            L = float(torch.max(ext[:d] + ext[d:]).item())
+        L = _domain_length(x, group)
         if L <= 1e-9:
             L = 1.0
         xis_1d, h_float, mtot = get_xis(kernel_obj=self.kernel, eps=self.eps, L=L, use_integral=True,
@@ -768,13 +790,7 @@ class EFGPND(nn.Module):
         v_kernel = compute_convolution_vector_vectorized_dD(m_conv, x, h_float).to(dtype=cdtype)
         nufft_op = NUFFT(x, xcen, h_float, nufft_eps, cdtype=cdtype, device=device)
         rhs = nufft_op.type1(y, OUT, scale=ws_r).reshape(-1)                     # ws * F^* y, fused
-        if group is not None:
-            # F^*1 and F^*y are sums over points: one NCCL all-reduce of the two (cropped, deconvolved)
-            # mode grids replaces the fine-grid exchange; every rank then solves the same M-sized system.
-            packed = torch.cat([v_kernel.reshape(-1), rhs])
-            torch.distributed.all_reduce(torch.view_as_real(packed), op=torch.distributed.ReduceOp.SUM, group=group)
-            v_kernel = packed[: v_kernel.numel()].reshape(v_kernel.shape)
-            rhs = packed[v_kernel.numel():]
+        v_kernel, rhs = _sum_over_shards(v_kernel, rhs, group)
         toeplitz = ToeplitzND(v_kernel, force_pow2=True)
         A_mean = create_A_mean(ws, toeplitz, s2, cdtype)
         center = tuple((s - 1) // 2 for s in v_kernel.shape)

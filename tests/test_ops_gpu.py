@@ -234,3 +234,46 @@ def test_operator_modes_and_cg(ops, d, m, dt):
                      minv=(1.0 / dg).cuda())
     assert itg2 == itr2 == 7
     assert rel(xg2, xr2) < (1e-9 if dt == torch.float64 else 1e-3)
+
+
+def test_points_outside_one_period_and_clustered(ops):
+    """phi may exceed one period (x_new outside the training box) and real data are
+    clustered (many points per cell in a few cells, empty cells elsewhere)."""
+    g = torch.Generator().manual_seed(9)
+    N, n, eps, h = 30000, 19, 1e-6, 0.45
+    centres = torch.rand(6, 2, dtype=torch.float64, generator=g) * 2 - 1
+    x = centres[torch.randint(0, 6, (N,), generator=g)] + 0.01 * torch.randn(N, 2, dtype=torch.float64, generator=g)
+    x[: N // 10] = torch.rand(N // 10, 2, dtype=torch.float64, generator=g) * 9 - 4.5     # several periods away
+    c = torch.randn(N, dtype=torch.float64, generator=g)
+    plan = ops.NufftPlan(x.cuda(), h)
+    phi = (2 * np.pi * h * x).T.contiguous()
+    ref = nudft.finufft_type1(phi, c.to(torch.complex128), (n, n), isign=-1, modeord=False)
+    assert rel(plan.type1(c.cuda(), (n, n), eps), ref) < 10 * eps
+    f = torch.randn(n, n, dtype=torch.complex128, generator=g)
+    ref2 = nudft.finufft_type2(phi, f, isign=+1, modeord=False)
+    assert rel(plan.type2(f.cuda(), (n, n), eps), ref2) < 10 * eps
+
+
+@pytest.mark.parametrize("d,N", [(2, 5_000_000), (3, 2_000_000), (1, 3_000_000)])
+def test_large_n_size_independent_properties(ops, d, N):
+    """At sizes the exact oracle cannot reach: (i) the generator's centre entry is N and F*1 is Hermitian,
+    (ii) type-2 of a single mode is that plane wave at every point (exercises the whole sort / permutation
+    machinery: a misplaced point shows up as a wrong phase), (iii) adjointness <F* c, f> = <c, F f>."""
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.rand(N, d, dtype=torch.float64, device="cuda", generator=g) * 2 - 1
+    h, eps, n = 0.43, 1e-7, 15
+    plan = ops.NufftPlan(x, h)
+    v = plan.type1(None, (n,) * d, eps)
+    centre = tuple([n // 2] * d)
+    assert abs(v[centre].real.item() - N) < 10 * eps * N and abs(v[centre].imag.item()) < 10 * eps * N
+    assert rel(v, torch.conj(torch.flip(v, dims=tuple(range(d))))) < 10 * eps
+    k = [3, -2, 1][:d]
+    f = torch.zeros((n,) * d, dtype=torch.complex128, device="cuda")
+    f[tuple(n // 2 + kk for kk in k)] = 1.0
+    wave = torch.exp(1j * 2 * np.pi * h * (x * torch.tensor(k, dtype=torch.float64, device="cuda")).sum(1))
+    assert rel(plan.type2(f, (n,) * d, eps), wave) < 10 * eps
+    c = torch.randn(N, dtype=torch.float64, device="cuda", generator=g)
+    fr = torch.randn((n,) * d, dtype=torch.complex128, device="cuda", generator=g)
+    lhs = torch.vdot(fr.reshape(-1), plan.type1(c, (n,) * d, eps).reshape(-1))          # <f, F* c>
+    rhs = torch.vdot(plan.type2(fr, (n,) * d, eps), c.to(torch.complex128))              # <F f, c>
+    assert abs(lhs - rhs) / abs(lhs) < 20 * eps
