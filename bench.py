@@ -63,11 +63,22 @@ def synth(n, d, seed, device, dtype):
 
 
 # ----------------------------------------------------------------------------- CPU reference arm
+def _host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_solve_step(x, y):
     """One posterior-mean solve with the oracle's restatement of the reference + the fast CPU NUFFT."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import torch
     import efgp_oracle as O
     import fast_nufft as F
+    # all host cores, also under torchrun (which exports OMP_NUM_THREADS=1)
+    F.NTHREADS = _host_threads()
+    torch.set_num_threads(_host_threads())
     kern = O.OracleKernel("se", 2, ELL, VAR)
     f = O.fit(x, y, kern, SIG2, EPS, NUFFT_EPS, cg_tol=CG_TOL, backend=F)
     mean = O.predict_mean(f, x, NUFFT_EPS, backend=F)
@@ -85,7 +96,7 @@ def cpu_baseline(n_sample, reps):
         t0 = time.perf_counter()
         f, _ = cpu_solve_step(x, y)
         best = min(best, time.perf_counter() - t0)
-    cores = max(F.num_threads(), torch.get_num_threads())
+    cores = _host_threads()
     return {"value": n_sample / best / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": f"{int(n_sample)} of the workload's points, full solve (2 type-1, CG {f.iters} its, 1 type-2), "
                       f"best of {reps}; oracle restatement of efgpnd.py + C/OpenMP ES-kernel NUFFT (FINUFFT absent)",
@@ -109,7 +120,7 @@ def run_reference(args):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import fast_nufft as F
     v = n_s / dt / 1e6
-    cores = max(F.num_threads(), torch.get_num_threads())
+    cores = _host_threads()
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": reps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",

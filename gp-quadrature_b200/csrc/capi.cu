@@ -89,6 +89,18 @@ int efgp_nufft_type1(efgp_nufft* nu, const void* strengths, int is_complex, int 
   })
 }
 
+int efgp_nufft_type1_pair(efgp_nufft* nu, const void* y, const int64_t* shape_gen, double eps_gen,
+                          const int64_t* shape_rhs, double eps_rhs, const void* scale, void* out_gen, void* out_rhs,
+                          void* stream) {
+  EFGP_TRY({
+    EFGP_CHECK(nu != nullptr && y != nullptr && shape_gen != nullptr && shape_rhs != nullptr && out_gen != nullptr &&
+                   out_rhs != nullptr,
+               "null argument");
+    efgp::nufft_type1_pair(nu->nu, y, shape_gen, eps_gen, shape_rhs, eps_rhs, scale, out_gen, out_rhs,
+                           (cudaStream_t)stream);
+  })
+}
+
 int efgp_nufft_type2(efgp_nufft* nu, const void* modes, int batch, const int64_t* shape, double eps,
                      int isign, int modeord, const void* scale, int real_out, void* out, void* stream) {
   EFGP_TRY({

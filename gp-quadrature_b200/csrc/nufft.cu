@@ -282,7 +282,8 @@ static SortedPoints* get_sorted(Nufft& nu, const int64_t* nf, int odd, cudaStrea
     nu.sorted.erase(nu.sorted.begin() + j);
   }
   std::unique_ptr<SortedPoints> sp(new SortedPoints());
-  build_sorted_points(*sp, nu.x, nu.N, nu.dim, nu.dtype, nu.h, nu.xcen, nf, odd, st);
+  build_sorted_points(*sp, nu.x, nu.pending_payload, nu.N, nu.dim, nu.dtype, nu.h, nu.xcen, nf, odd, st);
+  if (sp->has_payload) nu.fresh_payload_sp = sp.get();
   sp->last_use = ++nu.clock;
   nu.sorted.push_back(std::move(sp));
   return nu.sorted.back().get();
@@ -355,7 +356,7 @@ static ModeGeom make_geom(int dim, const int64_t* n, const int64_t* nf, int mode
 
 template <typename T>
 static void type1_t(Nufft& nu, const void* strengths, int is_complex, int batch, const int64_t* n, double eps,
-                    int isign, int modeord, const void* scale, void* out, cudaStream_t st) {
+                    int isign, int modeord, const void* scale, void* out, cudaStream_t st, bool payload_ok = false) {
   using C = typename cplx_of<T>::type;
   const int dim = nu.dim;
   GridChoice gc = choose_grid(nu, n, eps, st);
@@ -379,9 +380,15 @@ static void type1_t(Nufft& nu, const void* strengths, int is_complex, int batch,
       ScopedStage stg("type1.memset_fine", st, 0);
       EFGP_CUDA(cudaMemsetAsync(fine, 0, (size_t)nb * ncomp * cells * sizeof(T), st));
     }
-    T* cs = strengths ? (T*)nu.cperm.get((size_t)gc.sp->npos * sizeof(T)) : nullptr;
+    // strengths already ride in the records of a set sorted during this very call (nufft_type1_pair)
+    const bool from_rec = payload_ok && strengths && !is_complex && batch == 1 && gc.sp == nu.fresh_payload_sp;
+    T* cs = (strengths && !from_rec) ? (T*)nu.cperm.get((size_t)gc.sp->npos * sizeof(T)) : nullptr;
     for (int b = 0; b < nb; ++b) {
       for (int comp = 0; comp < ncomp; ++comp) {
+        if (from_rec) {
+          launch_spread(*gc.sp, gc.ker, nullptr, fine + (int64_t)(b * ncomp + comp) * cells, st, true);
+          continue;
+        }
         if (strengths) {
           const T* c = (const T*)strengths + (int64_t)(b0 + b) * nu.N * ncomp + comp;
           permute_strengths(*gc.sp, c, ncomp, cs, st);
@@ -459,6 +466,29 @@ void nufft_type1(Nufft& nu, const void* strengths, int is_complex, int batch, co
     type1_t<float>(nu, strengths, is_complex, batch, n, eps, isign, modeord, scale, out, st);
   else
     type1_t<double>(nu, strengths, is_complex, batch, n, eps, isign, modeord, scale, out, st);
+}
+
+void nufft_type1_pair(Nufft& nu, const void* y, const int64_t* shape_gen, double eps_gen, const int64_t* shape_rhs,
+                      double eps_rhs, const void* scale, void* out_gen, void* out_rhs, cudaStream_t st) {
+  for (int a = 0; a < nu.dim; ++a) EFGP_CHECK(shape_gen[a] >= 1 && shape_rhs[a] >= 1, "mode counts must be >= 1");
+  nu.pending_payload = nu.dim == 2 ? y : nullptr;
+  nu.fresh_payload_sp = nullptr;
+  try {
+    if (nu.dtype == 0)
+      type1_t<float>(nu, nullptr, 0, 1, shape_gen, eps_gen, -1, 0, nullptr, out_gen, st);
+    else
+      type1_t<double>(nu, nullptr, 0, 1, shape_gen, eps_gen, -1, 0, nullptr, out_gen, st);
+    nu.pending_payload = nullptr;
+    if (nu.dtype == 0)
+      type1_t<float>(nu, y, 0, 1, shape_rhs, eps_rhs, -1, 0, scale, out_rhs, st, true);
+    else
+      type1_t<double>(nu, y, 0, 1, shape_rhs, eps_rhs, -1, 0, scale, out_rhs, st, true);
+  } catch (...) {
+    nu.pending_payload = nullptr;
+    nu.fresh_payload_sp = nullptr;
+    throw;
+  }
+  nu.fresh_payload_sp = nullptr;
 }
 
 void nufft_type2(Nufft& nu, const void* modes, int batch, const int64_t* n, double eps, int isign, int modeord,

@@ -27,6 +27,7 @@ struct SortedPoints {
   int odd = 0;
   int P = 1;            // points per thread
   int RW = 2;           // words of T per record
+  bool has_payload = false;   // 2-D only: word 3 of every record holds a real per-point strength
   int64_t ntiles = 0;
   int64_t npos = 0;     // ntiles * kTileThreads * P
   void* rec = nullptr;        // npos records
@@ -82,11 +83,14 @@ struct Nufft {
   uint64_t clock = 0;
   std::vector<std::unique_ptr<SortedPoints>> sorted;  // small LRU cache
   DevBuf fine, spec, tmp, dec, cperm;
+  const void* pending_payload = nullptr;       // set by nufft_type1_pair: next sort carries these strengths
+  const SortedPoints* fresh_payload_sp = nullptr;  // the sorted set built with them during this call
 };
 
 // ---- points.cu
-void build_sorted_points(SortedPoints& sp, const void* x, int64_t N, int dim, int dtype, double h,
-                         const double* xcen, const int64_t* nf, int odd, cudaStream_t st);
+// payload: optional real (N,) strengths carried through the sort into the records (2-D only)
+void build_sorted_points(SortedPoints& sp, const void* x, const void* payload, int64_t N, int dim, int dtype,
+                         double h, const double* xcen, const int64_t* nf, int odd, cudaStream_t st);
 
 // ---- points.cu : cs[slot] = c[i * cstride] for the point i stored in that slot (npos entries), in two
 // sector-efficient stages (original -> bucket order -> slot order)
@@ -96,7 +100,9 @@ void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t 
 
 // ---- spread.cu : grid (real, nf^d) += sum_n c_n psi(l - X_n).  cs == nullptr means all ones;
 // otherwise cs holds the strengths in SLOT order (permute_strengths).
-void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, void* grid, cudaStream_t st);
+// from_record: take the strengths from the records' payload word instead of cs (needs sp.has_payload)
+void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, void* grid, cudaStream_t st,
+                   bool from_record = false);
 
 // ---- interp.cu : out[i * ostride] = sum_l grid[l] psi(l - X_i)  (i = original point index)
 void launch_interp(const SortedPoints& sp, const ESKernel& k, const void* grid, void* out,
@@ -105,6 +111,10 @@ void launch_interp(const SortedPoints& sp, const ESKernel& k, const void* grid, 
 // ---- nufft.cu
 void nufft_type1(Nufft& nu, const void* strengths, int is_complex, int batch, const int64_t* n, double eps,
                  int isign, int modeord, const void* scale, void* out, cudaStream_t st);
+// F^*1 on shape_gen at eps_gen and scale * F^*y on shape_rhs at eps_rhs in one call: one sort, y carried
+// through it as record payload (no strength permutation)
+void nufft_type1_pair(Nufft& nu, const void* y, const int64_t* shape_gen, double eps_gen, const int64_t* shape_rhs,
+                      double eps_rhs, const void* scale, void* out_gen, void* out_rhs, cudaStream_t st);
 void nufft_type2(Nufft& nu, const void* modes, int batch, const int64_t* n, double eps, int isign, int modeord,
                  const void* scale, int real_out, void* out, cudaStream_t st);
 

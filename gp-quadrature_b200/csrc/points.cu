@@ -129,14 +129,15 @@ bucket_hist_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortGeom
 }
 
 // One CTA: bucket-sort its 2048 points in shared memory, then write each bucket's run contiguously.
-template <typename T, int D>
+// NS = D staged words per point, or D + 1 when a per-point payload (real strengths y) rides along.
+template <typename T, int D, int NS>
 __global__ void __launch_bounds__(kSortThreads)
-bucket_scatter_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortGeom g, int ntiles1,
-                      const uint32_t* __restrict__ tileStart, T* __restrict__ R0, T* __restrict__ R1,
-                      T* __restrict__ R2, uint16_t* __restrict__ K2, uint32_t* __restrict__ A) {
+bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64_t N, FoldParams<T> p, SortGeom g,
+                      int ntiles1, const uint32_t* __restrict__ tileStart, T* __restrict__ R0, T* __restrict__ R1,
+                      T* __restrict__ R2, T* __restrict__ R3, uint16_t* __restrict__ K2, uint32_t* __restrict__ A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  T* S = (T*)smem_raw;                                   // [D][kSortTile]
-  uint16_t* SK = (uint16_t*)(S + D * kSortTile);         // level-2 bin
+  T* S = (T*)smem_raw;                                   // [NS][kSortTile]
+  uint16_t* SK = (uint16_t*)(S + NS * kSortTile);        // level-2 bin
   uint16_t* SB = SK + kSortTile;                         // level-1 bucket
   uint32_t* cnt = (uint32_t*)(SB + kSortTile);           // [kMaxBuckets]
   uint32_t* lstart = cnt + kMaxBuckets;
@@ -145,7 +146,7 @@ bucket_scatter_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortG
   const int64_t tile = blockIdx.x;
   if (tid < kMaxBuckets) cnt[tid] = 0;
   __syncthreads();
-  T X[kSortPer][D];
+  T X[kSortPer][NS];
   uint32_t bk[kSortPer], lr[kSortPer];
   uint16_t k2[kSortPer];
 #pragma unroll
@@ -154,6 +155,7 @@ bucket_scatter_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortG
     bk[k] = 0xffffffffu;
     if (i < N) {
       uint32_t key = fold_point<T, D>(x, i, p, X[k]);
+      if (NS > D) X[k][D] = ypay[i];
       uint32_t b = key / g.cpb;
       bk[k] = b;
       k2[k] = (uint16_t)((key - b * g.cpb) / g.g);
@@ -188,7 +190,7 @@ bucket_scatter_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortG
       int64_t i = tile * kSortTile + k * kSortThreads + tid;
       uint32_t lp = lstart[bk[k]] + lr[k];
 #pragma unroll
-      for (int a = 0; a < D; ++a) S[a * kSortTile + lp] = X[k][a];
+      for (int a = 0; a < NS; ++a) S[a * kSortTile + lp] = X[k][a];
       SK[lp] = k2[k];
       SB[lp] = (uint16_t)bk[k];
       A[i] = gstart[bk[k]] + lr[k];
@@ -197,12 +199,12 @@ bucket_scatter_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortG
   __syncthreads();
   const int64_t rem = N - tile * kSortTile;
   const int n_tile = rem < kSortTile ? (int)rem : kSortTile;
-  T* R[3] = {R0, R1, R2};
+  T* R[4] = {R0, R1, R2, R3};
   for (int lp = tid; lp < n_tile; lp += kSortThreads) {
     uint32_t b = SB[lp];
     uint32_t a = gstart[b] + ((uint32_t)lp - lstart[b]);
 #pragma unroll
-    for (int d = 0; d < D; ++d) R[d][a] = S[d * kSortTile + lp];
+    for (int d = 0; d < NS; ++d) R[d][a] = S[d * kSortTile + lp];
     K2[a] = SK[lp];
   }
 }
@@ -286,7 +288,7 @@ bin_hist_kernel(const uint16_t* __restrict__ K2, const uint32_t* __restrict__ bu
 template <typename T, int D>
 __global__ void __launch_bounds__(kSortThreads)
 bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* __restrict__ R2,
-                   const uint16_t* __restrict__ K2, const uint32_t* __restrict__ bucketStart,
+                   const T* __restrict__ RY, const uint16_t* __restrict__ K2, const uint32_t* __restrict__ bucketStart,
                    const uint32_t* __restrict__ tile2Base, SortGeom g, const uint32_t* __restrict__ binStart,
                    uint32_t* __restrict__ binCursor, T* __restrict__ rec, uint32_t* __restrict__ B) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -320,6 +322,7 @@ bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* 
 #pragma unroll
     for (int d = 0; d < D; ++d) w[d] = R[d][a];
     *reinterpret_cast<uint32_t*>(&w[D]) = a;
+    if (D == 2 && RY) w[3] = RY[a];      // payload rides in the record's spare word
     store_record<T, RW>(rec + slot * RW, w);
     B[a] = (uint32_t)slot;
   }
@@ -524,8 +527,9 @@ static int pick_points_per_thread(int64_t N) {
 }
 
 template <typename T, int D>
-static void build_td(SortedPoints& sp, const T* x, int64_t N, const FoldParams<T>& p, const SortGeom& g,
-                     cudaStream_t st) {
+static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, const FoldParams<T>& p,
+                     const SortGeom& g, cudaStream_t st) {
+  if (D != 2) ypay = nullptr;   // only the 2-D record has a spare word
   const int ntiles1 = div_up(N, kSortTile);
   const int64_t nhist = (int64_t)g.nb1 * ntiles1;
   const int64_t nbin = (int64_t)g.nb1 * g.nbins2;
@@ -543,6 +547,8 @@ static void build_td(SortedPoints& sp, const T* x, int64_t N, const FoldParams<T
   uint32_t* binCursor = binStart + nbin;
   T* R[3] = {nullptr, nullptr, nullptr};
   for (int a = 0; a < D; ++a) R[a] = (T*)pool_alloc(sizeof(T) * (size_t)N);
+  T* RY = ypay ? (T*)pool_alloc(sizeof(T) * (size_t)N) : nullptr;
+  sp.has_payload = ypay != nullptr;
   uint16_t* K2 = (uint16_t*)pool_alloc(sizeof(uint16_t) * (size_t)N);
   size_t scan_bytes = 0, sb2 = 0;
   EFGP_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, tileHist, tileStart, (int)nhist, st));
@@ -569,17 +575,25 @@ static void build_td(SortedPoints& sp, const T* x, int64_t N, const FoldParams<T
   }
   {
     ScopedStage stg("sort.bucket_scatter_kernel", st, 1, N);
-    const size_t smem = (size_t)D * kSortTile * sizeof(T) + 2 * kSortTile * sizeof(uint16_t) +
+    const int ns = D + (ypay ? 1 : 0);
+    const size_t smem = (size_t)ns * kSortTile * sizeof(T) + 2 * kSortTile * sizeof(uint16_t) +
                         3 * kMaxBuckets * sizeof(uint32_t);
+    const int smem_max = (int)(4 * kSortTile * sizeof(double) + 2 * kSortTile * sizeof(uint16_t) +
+                               3 * kMaxBuckets * sizeof(uint32_t));
     static bool attr_set = false;
     if (!attr_set) {
-      EFGP_CUDA(cudaFuncSetAttribute(bucket_scatter_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)(3 * kSortTile * sizeof(double) + 2 * kSortTile * sizeof(uint16_t) +
-                                           3 * kMaxBuckets * sizeof(uint32_t))));
+      EFGP_CUDA(cudaFuncSetAttribute(bucket_scatter_kernel<T, D, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     smem_max));
+      EFGP_CUDA(cudaFuncSetAttribute(bucket_scatter_kernel<T, D, D + 1>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
       attr_set = true;
     }
-    bucket_scatter_kernel<T, D><<<ntiles1, kSortThreads, smem, st>>>(x, N, p, g, ntiles1, tileStart, R[0], R[1],
-                                                                     R[2], K2, sp.A);
+    if (ypay)
+      bucket_scatter_kernel<T, D, D + 1><<<ntiles1, kSortThreads, smem, st>>>(
+          x, ypay, N, p, g, ntiles1, tileStart, R[0], R[1], RY, nullptr, K2, sp.A);   // D == 2: word 2 = payload
+    else
+      bucket_scatter_kernel<T, D, D><<<ntiles1, kSortThreads, smem, st>>>(x, nullptr, N, p, g, ntiles1, tileStart,
+                                                                          R[0], R[1], R[2], nullptr, K2, sp.A);
   }
   const int ntiles2_max = ntiles1 + g.nb1;
   {
@@ -602,20 +616,21 @@ static void build_td(SortedPoints& sp, const T* x, int64_t N, const FoldParams<T
       attr_set2 = true;
     }
     bin_scatter_kernel<T, D><<<ntiles2_max, kSortThreads, 2 * g.nbins2 * sizeof(uint32_t), st>>>(
-        R[0], R[1], R[2], K2, bucketStart, tile2Base, g, binStart, binCursor, rec, sp.B);
+        R[0], R[1], R[2], RY, K2, bucketStart, tile2Base, g, binStart, binCursor, rec, sp.B);
     if (sp.npos > N)
       pad_slots_kernel<T, D><<<div_up(sp.npos - N, 256), 256, 0, st>>>(N, sp.npos, g.log2P, rec);
   }
   EFGP_CUDA(cudaGetLastError());
   pool_free(scan_tmp);
   pool_free(K2);
+  if (RY) pool_free(RY);
   for (int a = 0; a < D; ++a) pool_free(R[a]);
   pool_free(meta);
   pool_free(tileHist);
 }
 
 template <typename T>
-static void build_t(SortedPoints& sp, const T* x, int64_t N, int dim, double h, const double* xcen,
+static void build_t(SortedPoints& sp, const T* x, const T* ypay, int64_t N, int dim, double h, const double* xcen,
                     const int64_t* nf, int odd, cudaStream_t st) {
   FoldParams<T> p;
   p.h = (T)h;
@@ -644,13 +659,13 @@ static void build_t(SortedPoints& sp, const T* x, int64_t N, int dim, double h, 
   g.nbins2 = (int)((g.cpb + g.g - 1) / g.g);
   g.log2P = 0;
   while ((1 << g.log2P) < sp.P) ++g.log2P;
-  if (dim == 1) build_td<T, 1>(sp, x, N, p, g, st);
-  if (dim == 2) build_td<T, 2>(sp, x, N, p, g, st);
-  if (dim == 3) build_td<T, 3>(sp, x, N, p, g, st);
+  if (dim == 1) build_td<T, 1>(sp, x, ypay, N, p, g, st);
+  if (dim == 2) build_td<T, 2>(sp, x, ypay, N, p, g, st);
+  if (dim == 3) build_td<T, 3>(sp, x, ypay, N, p, g, st);
 }
 
-void build_sorted_points(SortedPoints& sp, const void* x, int64_t N, int dim, int dtype, double h,
-                         const double* xcen, const int64_t* nf, int odd, cudaStream_t st) {
+void build_sorted_points(SortedPoints& sp, const void* x, const void* payload, int64_t N, int dim, int dtype,
+                         double h, const double* xcen, const int64_t* nf, int odd, cudaStream_t st) {
   sp.dim = dim;
   sp.dtype = dtype;
   sp.N = N;
@@ -658,9 +673,9 @@ void build_sorted_points(SortedPoints& sp, const void* x, int64_t N, int dim, in
   for (int a = 0; a < kMaxDim; ++a) sp.nf[a] = a < dim ? nf[a] : 1;
   if (N == 0) return;
   if (dtype == 0)
-    build_t<float>(sp, (const float*)x, N, dim, h, xcen, nf, odd, st);
+    build_t<float>(sp, (const float*)x, (const float*)payload, N, dim, h, xcen, nf, odd, st);
   else
-    build_t<double>(sp, (const double*)x, N, dim, h, xcen, nf, odd, st);
+    build_t<double>(sp, (const double*)x, (const double*)payload, N, dim, h, xcen, nf, odd, st);
 }
 
 }  // namespace efgp

@@ -118,7 +118,8 @@ __device__ __forceinline__ void flush2d(T (&acc)[W][W], int c0, int c1, int nf0,
   }
 }
 
-template <typename T, int W, bool HAS_C>
+// HAS_C: 0 = all-ones strengths, 1 = strengths in slot order (cs), 2 = strengths in the records' payload word
+template <typename T, int W, int HAS_C>
 __global__ void __launch_bounds__(kTileThreads, (W <= 5 ? 2 : 1))
 spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int nf0,
                 int nf1, T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
@@ -132,7 +133,8 @@ spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
       const int64_t pos = base + (int64_t)j * kTileThreads;
       const int s = j % S;
       cp_async_word<2 * sizeof(T)>(&ring[s][t][0], rec + pos * 4);   // one 16-byte (8 for f32) copy per point
-      if (HAS_C) cp_async_word<sizeof(T)>(&cring[s][t], cs + pos);
+      if (HAS_C == 1) cp_async_word<sizeof(T)>(&cring[s][t], cs + pos);
+      if (HAS_C == 2) cp_async_word<sizeof(T)>(&cring[s][t], rec + pos * 4 + 3);
     }
     cp_async_commit();
   };
@@ -174,7 +176,7 @@ spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
 
 // ------------------------------------------------------------------ generic d (2-D wide kernels, 3-D): per-point REDs
 // Points are still cell-sorted, so the reductions of neighbouring slots land in the same L2 lines.
-template <typename T, int W, int D, bool HAS_C>
+template <typename T, int W, int D, int HAS_C>
 __global__ void __launch_bounds__(256)
 spread_direct_kernel(const T* __restrict__ rec,
                      const T* __restrict__ cs, int64_t npos, int nf0, int nf1, int nf2, T* __restrict__ grid,
@@ -186,7 +188,7 @@ spread_direct_kernel(const T* __restrict__ rec,
   load_record4<T>(rec + n * 4, Xr);
   T X0 = Xr[0];
   if (X0 < T(0)) return;
-  T cv = HAS_C ? cs[n] : T(1);
+  T cv = HAS_C == 1 ? cs[n] : (HAS_C == 2 ? Xr[3] : T(1));
   T k0[W], k1[W], k2[W];
   int c0 = (int)X0;
   es_eval<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
@@ -227,55 +229,57 @@ spread_direct_kernel(const T* __restrict__ rec,
 }
 
 template <typename T, int W>
-static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st) {
+static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st, bool from_record) {
   ESDev<T> es;
   es_to_dev<T>(k, es);
   const T* rec = (const T*)sp.rec;
   constexpr int kRegMaxW = sizeof(T) == 8 ? 9 : 10;
   const int nt = (int)sp.ntiles;
+  const int mode = from_record ? 2 : (cs ? 1 : 0);
   char nm[48];
-  snprintf(nm, sizeof(nm), "spread%dd_w%d_%s%s", sp.dim, W, sizeof(T) == 8 ? "f64" : "f32", cs ? "" : "_ones");
+  snprintf(nm, sizeof(nm), "spread%dd_w%d_%s%s", sp.dim, W, sizeof(T) == 8 ? "f64" : "f32",
+           mode == 0 ? "_ones" : (mode == 2 ? "_rec" : ""));
   ScopedStage stg(nm, st, 1, sp.N);
+  const int nf0 = (int)sp.nf[0], nf1 = (int)sp.nf[1], nf2 = (int)sp.nf[2];
   if (sp.dim == 1) {
     if (cs)
-      spread1d_kernel<T, W, true><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, (int)sp.nf[0], grid, es);
+      spread1d_kernel<T, W, true><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es);
     else
-      spread1d_kernel<T, W, false><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, (int)sp.nf[0], grid, es);
+      spread1d_kernel<T, W, false><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es);
   } else if (sp.dim == 2) {
     if constexpr (W <= kRegMaxW) {
-      if (cs)
-        spread2d_kernel<T, W, true>
-            <<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
+      if (mode == 2)
+        spread2d_kernel<T, W, 2><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es);
+      else if (mode == 1)
+        spread2d_kernel<T, W, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es);
       else
-        spread2d_kernel<T, W, false>
-            <<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid, es);
+        spread2d_kernel<T, W, 0><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es);
     } else {
       int nb = div_up(sp.npos, 256);
-      if (cs)
-        spread_direct_kernel<T, W, 2, true>
-            <<<nb, 256, 0, st>>>(rec, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, es);
+      if (mode == 2)
+        spread_direct_kernel<T, W, 2, 2><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es);
+      else if (mode == 1)
+        spread_direct_kernel<T, W, 2, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es);
       else
-        spread_direct_kernel<T, W, 2, false>
-            <<<nb, 256, 0, st>>>(rec, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, es);
+        spread_direct_kernel<T, W, 2, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es);
     }
   } else {
     int nb = div_up(sp.npos, 256);
     if (cs)
-      spread_direct_kernel<T, W, 3, true>
-          <<<nb, 256, 0, st>>>(rec, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, es);
+      spread_direct_kernel<T, W, 3, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es);
     else
-      spread_direct_kernel<T, W, 3, false>
-          <<<nb, 256, 0, st>>>(rec, cs, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, es);
+      spread_direct_kernel<T, W, 3, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es);
   }
   EFGP_CUDA(cudaGetLastError());
 }
 
 template <typename T>
-static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st) {
+static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st,
+                     bool from_record) {
   switch (k.W) {
 #define EFGP_CASE(w) \
   case w:            \
-    launch_w<T, w>(sp, k, cs, grid, st); \
+    launch_w<T, w>(sp, k, cs, grid, st, from_record); \
     break;
     EFGP_CASE(2) EFGP_CASE(3) EFGP_CASE(4) EFGP_CASE(5) EFGP_CASE(6) EFGP_CASE(7) EFGP_CASE(8) EFGP_CASE(9)
     EFGP_CASE(10) EFGP_CASE(11) EFGP_CASE(12) EFGP_CASE(13) EFGP_CASE(14) EFGP_CASE(15) EFGP_CASE(16)
@@ -285,13 +289,15 @@ static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
   }
 }
 
-void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, void* grid, cudaStream_t st) {
+void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, void* grid, cudaStream_t st,
+                   bool from_record) {
   if (sp.N == 0) return;
+  EFGP_CHECK(!from_record || (sp.has_payload && sp.dim == 2), "sorted point set carries no strength payload");
   EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
   if (sp.dtype == 0)
-    launch_t<float>(sp, k, (const float*)cs, (float*)grid, st);
+    launch_t<float>(sp, k, (const float*)cs, (float*)grid, st, from_record);
   else
-    launch_t<double>(sp, k, (const double*)cs, (double*)grid, st);
+    launch_t<double>(sp, k, (const double*)cs, (double*)grid, st, from_record);
 }
 
 }  // namespace efgp

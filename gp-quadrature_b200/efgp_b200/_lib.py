@@ -27,6 +27,7 @@ _SIGNATURES = {
     "efgp_nufft_destroy": (None, [vp]),
     "efgp_nufft_type1": (ctypes.c_int, [vp, vp, ctypes.c_int, ctypes.c_int, c_i64p, ctypes.c_double,
                                         ctypes.c_int, ctypes.c_int, vp, vp, vp]),
+    "efgp_nufft_type1_pair": (ctypes.c_int, [vp, vp, c_i64p, ctypes.c_double, c_i64p, ctypes.c_double, vp, vp, vp, vp]),
     "efgp_nufft_type2": (ctypes.c_int, [vp, vp, ctypes.c_int, c_i64p, ctypes.c_double, ctypes.c_int,
                                         ctypes.c_int, vp, ctypes.c_int, vp, vp]),
     "efgp_nufft_plan_info": (ctypes.c_int, [vp, c_i64p, ctypes.c_double, c_i64p, c_intp]),

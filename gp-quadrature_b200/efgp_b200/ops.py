@@ -112,6 +112,28 @@ class NufftPlan:
             return out.reshape(tuple(vals.shape[:-1]) + out_shape)
         return out.reshape(out_shape)
 
+    def type1_pair(self, y, shape_gen, eps_gen, shape_rhs, eps_rhs, scale=None):
+        """(F^*1 on shape_gen at eps_gen, scale * F^*y on shape_rhs at eps_rhs) with one sort that carries y."""
+        shape_gen = tuple(int(s) for s in shape_gen)
+        shape_rhs = tuple(int(s) for s in shape_rhs)
+        if len(shape_gen) != self.d or len(shape_rhs) != self.d:
+            raise ValueError("shapes do not match the dimension")
+        _require_cuda(y, "y")
+        if y.is_complex() or y.numel() != self.N:
+            raise ValueError("y must be a real (N,) tensor")
+        yv = y.to(self.rdtype).reshape(self.N).contiguous()
+        M = 1
+        for s in shape_rhs:
+            M *= s
+        sc = self._scale(scale, M)
+        out_gen = torch.empty(shape_gen, dtype=self.cdtype, device=self.device)
+        out_rhs = torch.empty(shape_rhs, dtype=self.cdtype, device=self.device)
+        with torch.cuda.device(self.device):
+            check(_lib.lib().efgp_nufft_type1_pair(self._h, _ptr(yv), i64_array(shape_gen), float(eps_gen),
+                                                   i64_array(shape_rhs), float(eps_rhs), _ptr(sc), _ptr(out_gen),
+                                                   _ptr(out_rhs), _stream(self.device)))
+        return out_gen, out_rhs
+
     def type2(self, fk, shape, eps, isign=+1, modeord=False, scale=None, real_out=False):
         """fk (*shape) / (M,) or batched (B, …) complex -> (N,) or (B, N), real if real_out."""
         shape = tuple(int(s) for s in shape)

@@ -777,19 +777,21 @@ class EFGPND(nn.Module):
             L = 1.0
         xis_1d, h_float, mtot = get_xis(kernel_obj=self.kernel, eps=self.eps, L=L, use_integral=True,
                                         l2scaled=False)
+        OUT = (mtot,) * d
+        m_conv = (mtot - 1) // 2
+        xcen = torch.zeros(d, device=device, dtype=rdtype)
+        # Both O(N) transforms of the fit in one library call (one sort, y carried as payload), enqueued
+        # first so the host-side set-up of xis / ws below overlaps the device work:
+        #   v_kernel = F^* 1 on (4m+1)^d at the reference's fixed eps 6e-8 (efgpnd.py:1395-1421, :789-790)
+        #   Fy       = F^* y on mtot^d at nufft_eps                        (efgpnd.py:786)
+        nufft_op = NUFFT(x, xcen, h_float, nufft_eps, cdtype=cdtype, device=device)
+        v_kernel, Fy = nufft_op._plan.type1_pair(y, (4 * m_conv + 1,) * d, 6e-8, OUT, nufft_eps)
         h = torch.tensor(h_float, device=device, dtype=rdtype)
         xis_1d = xis_1d.to(device=device, dtype=rdtype)
         xis = torch.stack(torch.meshgrid(*(xis_1d for _ in range(d)), indexing="ij"), dim=-1).view(-1, d)
         xis.h_float = h_float
-        OUT = (mtot,) * d
-        xcen = torch.zeros(d, device=device, dtype=rdtype)
         ws = torch.sqrt(self.kernel.spectral_density(xis).to(dtype=cdtype) * (h ** d)).to(dtype=cdtype)
-        ws_r = ws.real.contiguous()
-        m_conv = (mtot - 1) // 2
-        # generator first: its finer grid (and sort) is reused by the y transform
-        v_kernel = compute_convolution_vector_vectorized_dD(m_conv, x, h_float).to(dtype=cdtype)
-        nufft_op = NUFFT(x, xcen, h_float, nufft_eps, cdtype=cdtype, device=device)
-        rhs = nufft_op.type1(y, OUT, scale=ws_r).reshape(-1)                     # ws * F^* y, fused
+        rhs = ws * Fy.reshape(-1)                                                # ws * F^* y
         v_kernel, rhs = _sum_over_shards(v_kernel, rhs, group)
         toeplitz = ToeplitzND(v_kernel, force_pow2=True)
         A_mean = create_A_mean(ws, toeplitz, s2, cdtype)

@@ -54,6 +54,14 @@ int efgp_nufft_type1(efgp_nufft* nu, const void* strengths, int is_complex, int 
                      const int64_t* out_shape, double eps, int isign, int modeord, const void* scale,
                      void* out, void* stream);
 
+/* The two type-1 transforms of a fit in one call (EFGPND._compute_common_parameters, efgpnd.py:786-790:
+ * rhs = ws * F^* y and compute_convolution_vector_vectorized_dD = F^* 1 at eps 6e-8): out_gen is
+ * (*shape_gen) = F^* 1 at eps_gen, out_rhs is (*shape_rhs) = scale * F^* y at eps_rhs, y real (npts,).
+ * One sort of the points serves both and carries y as payload (no strength permutation pass). */
+int efgp_nufft_type1_pair(efgp_nufft* nu, const void* y, const int64_t* shape_gen, double eps_gen,
+                          const int64_t* shape_rhs, double eps_rhs, const void* scale, void* out_gen, void* out_rhs,
+                          void* stream);
+
 /* NUFFT.type2 -> pff.finufft_type2(phi, fk, eps, isign=+1, modeord) (efgpnd.py:1510-1549, 1679).
  * modes: (batch, *shape) complex; scale: optional real diagonal applied to the modes first
  * (ws * beta, efgpnd.py:922).  out: (batch, npts) complex, or real when real_out != 0 (exactly the
