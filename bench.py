@@ -204,6 +204,8 @@ def algorithmic_bytes(stage, n, d=2, word=8):
     per_point = {
         "sort.bucket_hist_kernel": word * d,                                # read x
         "sort.bucket_scatter_kernel": word * d + word * d + 2 + 4,          # read x; write folded coords, bin, A
+        "sort.bucket_scatter_kernel_pay": word * d + word + word * d + word + 2 + 4,   # ... plus the y payload in and out
+        "sort.bin_scatter_kernel_pay": word * d + word + 2 + word * d + word + 4 + 4,  # ... plus y into the record
         "sort.bin_hist_kernel": 2,                                          # read level-2 bins
         "sort.bin_scatter_kernel": word * d + 2 + word * d + 4 + 4,         # read coords, bin; write record (coords, binv), B
         "permute.to_bucket_order": word + 4 + word,                         # read c, A; write tmp

@@ -574,7 +574,7 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
     EFGP_CUDA(cudaMemsetAsync(binCursor, 0, sizeof(uint32_t) * (size_t)nbin, st));
   }
   {
-    ScopedStage stg("sort.bucket_scatter_kernel", st, 1, N);
+    ScopedStage stg(ypay ? "sort.bucket_scatter_kernel_pay" : "sort.bucket_scatter_kernel", st, 1, N);
     const int ns = D + (ypay ? 1 : 0);
     const size_t smem = (size_t)ns * kSortTile * sizeof(T) + 2 * kSortTile * sizeof(uint16_t) +
                         3 * kMaxBuckets * sizeof(uint32_t);
@@ -608,7 +608,7 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
     EFGP_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, tb, binCount, binStart, (int)nbin, st));
   }
   {
-    ScopedStage stg("sort.bin_scatter_kernel", st, 2, N);
+    ScopedStage stg(ypay ? "sort.bin_scatter_kernel_pay" : "sort.bin_scatter_kernel", st, 2, N);
     static bool attr_set2 = false;
     if (!attr_set2) {
       EFGP_CUDA(cudaFuncSetAttribute(bin_scatter_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -135,7 +135,9 @@ class NUFFT:
     def phi(self):
         """(d, N) phases 2*pi*h*(x - xcen), materialised only if a caller asks (efgpnd.py:1451)."""
         if self._phi is None:
-            self._phi = (2 * math.pi * self._h * (self._x - self._xcen)).T.contiguous().to(
+            xc = torch.as_tensor(self._xcen if self._xcen is not None else 0.0, dtype=self._x.dtype,
+                                 device=self._x.device)
+            self._phi = (2 * math.pi * self._h * (self._x - xc)).T.contiguous().to(
                 device=self.device, dtype=self.dtype)
         return self._phi
 
@@ -247,7 +249,9 @@ class _FusedOperator:
         self.mode = mode
         self.cdtype = cdtype
         w = ws.detach()
-        self._real_ws = (not w.is_complex()) or bool((w.imag == 0).all())
+        # EFGP weights are sqrt(S h^d) >= 0 stored as complex (efgpnd.py:98, 779-780).  Tensors built by this
+        # module are tagged so the zero-imaginary test (a device->host sync) only runs for foreign weights.
+        self._real_ws = (not w.is_complex()) or getattr(ws, "_efgp_real", False) or bool((w.imag == 0).all())
         self.ws_real = (w.real if w.is_complex() else w).to(device=toeplitz.device).contiguous()
 
     def __call__(self, v):
@@ -779,18 +783,22 @@ class EFGPND(nn.Module):
                                         l2scaled=False)
         OUT = (mtot,) * d
         m_conv = (mtot - 1) // 2
-        xcen = torch.zeros(d, device=device, dtype=rdtype)
+        xcen = [0.0] * d
         # Both O(N) transforms of the fit in one library call (one sort, y carried as payload), enqueued
         # first so the host-side set-up of xis / ws below overlaps the device work:
         #   v_kernel = F^* 1 on (4m+1)^d at the reference's fixed eps 6e-8 (efgpnd.py:1395-1421, :789-790)
         #   Fy       = F^* y on mtot^d at nufft_eps                        (efgpnd.py:786)
         nufft_op = NUFFT(x, xcen, h_float, nufft_eps, cdtype=cdtype, device=device)
         v_kernel, Fy = nufft_op._plan.type1_pair(y, (4 * m_conv + 1,) * d, 6e-8, OUT, nufft_eps)
-        h = torch.tensor(h_float, device=device, dtype=rdtype)
-        xis_1d = xis_1d.to(device=device, dtype=rdtype)
+        # xis / ws are built on the device from scalars only: a pageable host->device copy (torch.tensor(h),
+        # xis_1d.to(device)) would make the host wait for the whole sort + spread queued above.
+        hm = (mtot - 1) // 2
+        xis_1d = (torch.arange(-hm, hm + 1, device=device, dtype=torch.float64) * h_float).to(rdtype)
         xis = torch.stack(torch.meshgrid(*(xis_1d for _ in range(d)), indexing="ij"), dim=-1).view(-1, d)
         xis.h_float = h_float
-        ws = torch.sqrt(self.kernel.spectral_density(xis).to(dtype=cdtype) * (h ** d)).to(dtype=cdtype)
+        hd = torch.tensor(h_float, dtype=rdtype) ** d          # CPU scalar, same arithmetic as the reference's h ** d
+        ws = torch.sqrt(self.kernel.spectral_density(xis).to(dtype=cdtype) * float(hd)).to(dtype=cdtype)
+        ws._efgp_real = True
         rhs = ws * Fy.reshape(-1)                                                # ws * F^* y
         v_kernel, rhs = _sum_over_shards(v_kernel, rhs, group)
         toeplitz = ToeplitzND(v_kernel, force_pow2=True)
@@ -808,6 +816,7 @@ class EFGPND(nn.Module):
         beta = solver.solve()
         self.last_fit_stats = {"mean_cg_iters": int(solver.iters_completed), "mtot": int(mtot), "h": h_float,
                                "feature_count": int(ws.numel())}
+        ws._efgp_real = True
         self._beta = beta
         self._xis = xis
         self._ws = ws
@@ -844,10 +853,10 @@ class EFGPND(nn.Module):
             B, d = x_new.shape
             beta, xis, ws, toeplitz = self._beta, self._xis, self._ws, self._toeplitz
             h_float = xis.h_float
-            h = torch.tensor(h_float, device=device, dtype=rdtype)
+            h = h_float                      # python scalars: no host->device copies on the predict path
             mtot = int(round(xis.shape[0] ** (1.0 / d)))
-            A_var = create_A_var(ws, toeplitz, s2, cdtype)
-            xcen = torch.zeros(d, device=device, dtype=rdtype)
+            A_var = create_A_var(ws, toeplitz, s2, cdtype) if return_variance else None
+            xcen = [0.0] * d
             OUT = (mtot,) * d
             nufft_op = NUFFT(x_new, xcen, h_float, nufft_eps, cdtype=cdtype, device=device)
             with rf("predict_mean"):

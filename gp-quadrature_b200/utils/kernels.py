@@ -44,6 +44,8 @@ class GetTruncationBound:
         mid = (a + b) / 2
         for _ in range(self.max_iterations):
             mid = (a + b) / 2
+            if mid == a or mid == b:
+                break          # interval collapsed to adjacent floats: every later midpoint is this one
             if self._f(mid) > self.eps:
                 a = mid
             else:
