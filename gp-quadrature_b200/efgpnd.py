@@ -58,6 +58,20 @@ def _point_shard_group(opts):
     return group if dist.get_world_size(group) > 1 else None
 
 
+def _probe_shard_group(opts):
+    """Process group over which the Hutchinson probes of compute_gradients are sharded, or None.
+    opts["shard_probes"] is True (default group) or a group; every rank holds ALL points and runs its share
+    of the probes; the partial trace sums are all-reduced.  Ranks must seed torch
+    identically before the call (the per-probe seeds derive from the global CPU generator)."""
+    g = opts.get("shard_probes", None) if opts else None
+    if not g:
+        return None
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        raise EfgpError("opts['shard_probes'] needs an initialised torch.distributed process group")
+    return dist.group.WORLD if g is True else g
+
+
 def _domain_length(x, group=None):
     """L = max_d (max x_d - min x_d) (efgpnd.py:751), over ALL shards when the points are sharded: one
     pass over the local x, then a MAX all-reduce of [max, -min]."""
@@ -318,6 +332,16 @@ def _rademacher_like_reference(shape, rdtype, device):
     return z.to(device)
 
 
+def _rademacher_seeded(n, rdtype, device, seed):
+    """One +-1 probe of length n from its own generator: independent of how probes are split over ranks."""
+    draw_dev = torch.device(PROBE_DEVICE) if PROBE_DEVICE is not None else device
+    g = torch.Generator(device=draw_dev).manual_seed(int(seed))
+    z = torch.empty(n, device=draw_dev, dtype=rdtype)
+    z.bernoulli_(0.5, generator=g)
+    z.mul_(2).sub_(1)
+    return z.to(device)
+
+
 # ----------------------------------------------------------------------------- posterior variance
 def diag_sums_nd(A_apply, J, xis_flat, max_cg_iter, cg_tol, ws):
     """Lag sums c[r] = mean_j xcorr(ws * A_var^-1 (ws * eta_j), eta_j) from J Rademacher probes
@@ -435,7 +459,7 @@ def efgpnd_gradient_batched(
         mean_cg_init: Optional[torch.Tensor] = None,
         use_mean_cg_preconditioner: bool = True,
         use_trace_cg_preconditioner: bool = True,
-        log_marginal_probes=100, log_marginal_steps=25):
+        log_marginal_probes=100, log_marginal_steps=25, probe_group=None):
     """Hutchinson + CG gradient of the negative log marginal likelihood w.r.t. (kernel hypers, sigma^2)
     in positive space; same stages, probe order (Z then V) and statistics as the reference
     (efgpnd.py:17-317).  x0 / x1 are ignored and recomputed, as there (efgpnd.py:72-73).
@@ -529,45 +553,79 @@ def efgpnd_gradient_batched(
                 term2_kernel[variance_idx] = (y_alpha - s2 * alpha_norm) / var_scalar
             term2 = torch.cat((term2_kernel, alpha_norm.unsqueeze(0)))
 
+        def trace_partials(t_lo, t_hi, probe_seed):
+            """Un-normalised Hutchinson sums over probes [t_lo, t_hi): (sum_t Z_t.Alpha_t per kernel hyper,
+            sum_t Re<V_t, Beta_noise_t>, CG iterations, rows).  probe_seed None: the reference's draws (one
+            (T, N) block then one (T, M) block from the global generator, efgpnd.py:179-181, 199-201);
+            otherwise probe t is drawn from its own generator seeded with probe_seed + t, so the result does
+            not depend on how the probes are split over ranks."""
+            Tl = t_hi - t_lo
+            nk = len(trace_idx)
+            if Tl == 0:
+                return torch.zeros(nk, device=device, dtype=rdtype), torch.zeros((), device=device, dtype=rdtype), 0, 0
+            if probe_seed is None:
+                Zl = _rademacher_like_reference((Tl, N), rdtype, device) if nk > 0 else None
+                Vl = _rademacher_like_reference((Tl, M), rdtype, device).to(cdtype)
+            else:
+                Zl = torch.stack([_rademacher_seeded(N, rdtype, device, probe_seed + 2 * t)
+                                  for t in range(t_lo, t_hi)]) if nk > 0 else None
+                Vl = torch.stack([_rademacher_seeded(M, rdtype, device, probe_seed + 2 * t + 1)
+                                  for t in range(t_lo, t_hi)]).to(cdtype)
+            if nk > 0:
+                fadjZ = nufft_op.type1(Zl, OUT).reshape(Tl, -1)
+                Di_FZ_all = torch.stack([Dprime[:, i] * fadjZ for i in trace_idx], dim=0).reshape(-1, M)
+                B_all_kernel = (ws * toeplitz(Di_FZ_all)).reshape(nk, Tl, -1)
+            else:
+                B_all_kernel = torch.empty((0, Tl, M), device=device, dtype=cdtype)
+            B_noise = (ws * toeplitz(ws * Vl)).reshape(Tl, -1)
+            B_all = torch.cat((B_all_kernel, B_noise.unsqueeze(0)), dim=0).reshape((nk + 1) * Tl, -1)
+            with rf("7_batch_cg_solve"):
+                cg_trace = ConjugateGradients(A_apply, B_all, torch.zeros_like(B_all), tol=cg_tol,
+                                              early_stopping=early_stopping, M_inv_apply=trace_M_inv)
+                Beta_all = cg_trace.solve()
+            with rf("7.5_compute_alpha"):
+                rows_k = nk * Tl
+                Beta_kernel = Beta_all[:rows_k]
+                Beta_noise = Beta_all[rows_k:]
+                sums = torch.zeros(nk, Tl, device=device, dtype=rdtype)
+                if nk > 0:
+                    # Alpha = (F(D'F*Z) - F(ws beta_k)) / sigma^2 = F(D'F*Z - ws beta_k) / sigma^2, real part only
+                    resid_modes = Di_FZ_all - ws * Beta_kernel
+                    chunk = max(1, min(Tl, int((2 << 30) // max(1, N * 8))))
+                    for slot in range(nk):
+                        for t0 in range(0, Tl, chunk):
+                            rm = resid_modes[slot * Tl + t0: slot * Tl + min(Tl, t0 + chunk)]
+                            a_chunk = nufft_op.type2(rm, OUT, real_out=True).reshape(-1, N)
+                            sums[slot, t0:t0 + a_chunk.shape[0]] = (Zl[t0:t0 + a_chunk.shape[0]] * a_chunk).sum(dim=1)
+                noise_sum = (Vl.conj() * Beta_noise).sum(dim=1).real.sum()
+            return sums.sum(dim=1), noise_sum, int(cg_trace.iters_completed), int(B_all.shape[0])
+
         with rf("6_monte_carlo_trace"):
             T = trace_samples
             nk = len(trace_idx)
-            if nk > 0:
-                Z = _rademacher_like_reference((T, N), rdtype, device)
-                fadjZ = nufft_op.type1(Z, OUT).reshape(T, -1)
-                Di_FZ_all = torch.stack([Dprime[:, i] * fadjZ for i in trace_idx], dim=0).reshape(-1, M)
-                B_all_kernel = (ws * toeplitz(Di_FZ_all)).reshape(nk, T, -1)
+            if probe_group is None:
+                k_sums, n_sum, trace_iters, trace_rows = trace_partials(0, T, None)
             else:
-                Z = None
-                B_all_kernel = torch.empty((0, T, M), device=device, dtype=cdtype)
-            V = _rademacher_like_reference((T, M), rdtype, device).to(cdtype)
-            B_noise = (ws * toeplitz(ws * V)).reshape(T, -1)
-            B_all = torch.cat((B_all_kernel, B_noise.unsqueeze(0)), dim=0).reshape((nk + 1) * T, -1)
-
-        with rf("7_batch_cg_solve"):
-            cg_trace = ConjugateGradients(A_apply, B_all, torch.zeros_like(B_all), tol=cg_tol,
-                                          early_stopping=early_stopping, M_inv_apply=trace_M_inv)
-            Beta_all = cg_trace.solve()
-
-        with rf("7.5_compute_alpha"):
-            rows_k = nk * T
-            Beta_kernel = Beta_all[:rows_k]
-            Beta_noise = Beta_all[rows_k:]
+                # probes sharded over the ranks (SURVEY.md 8e): every rank holds all N points and runs
+                # T / world probes end to end; ONE all-reduce of nk + 1 partial sums (+ one MAX of the
+                # iteration count for the statistics) assembles term1
+                import torch.distributed as dist
+                world, rank = dist.get_world_size(probe_group), dist.get_rank(probe_group)
+                t_lo, t_hi = shard_bounds(T, world, rank)
+                seed = torch.randint(0, 2 ** 31 - 1, (1,)).item()      # global CPU generator: same on all ranks
+                k_sums, n_sum, trace_iters, trace_rows = trace_partials(t_lo, t_hi, seed)
+                packed = torch.cat([k_sums, n_sum.reshape(1)]).to(torch.float64)
+                dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=probe_group)
+                k_sums, n_sum = packed[:nk].to(rdtype), packed[nk].to(rdtype)
+                it = torch.tensor([trace_iters, trace_rows], device=device, dtype=torch.int64)
+                dist.all_reduce(it[:1], op=dist.ReduceOp.MAX, group=probe_group)
+                dist.all_reduce(it[1:], op=dist.ReduceOp.SUM, group=probe_group)
+                trace_iters, trace_rows = int(it[0]), int(it[1])
             term1 = torch.empty(num_hypers, device=device, dtype=rdtype)
-            if nk > 0:
-                # Alpha = (F(D'F*Z) - F(ws beta_k)) / sigma^2 = F(D'F*Z - ws beta_k) / sigma^2, real part only
-                resid_modes = Di_FZ_all - ws * Beta_kernel
-                sums = torch.zeros(nk, T, device=device, dtype=rdtype)
-                chunk = max(1, min(T, int((2 << 30) // max(1, N * 8))))
-                for slot in range(nk):
-                    for t0 in range(0, T, chunk):
-                        rm = resid_modes[slot * T + t0: slot * T + min(T, t0 + chunk)]
-                        a_chunk = nufft_op.type2(rm, OUT, real_out=True).reshape(-1, N)
-                        sums[slot, t0:t0 + a_chunk.shape[0]] = (Z[t0:t0 + a_chunk.shape[0]] * a_chunk).sum(dim=1)
-                term1_kernel = sums.mean(dim=1) / s2
-                for slot, k_idx in enumerate(trace_idx):
-                    term1[k_idx] = term1_kernel[slot]
-            term1_noise = N / s2 - ((V.conj() * Beta_noise).sum(dim=1).real / s2).mean()
+            term1_kernel = k_sums / T / s2
+            for slot, k_idx in enumerate(trace_idx):
+                term1[k_idx] = term1_kernel[slot]
+            term1_noise = N / s2 - n_sum / s2 / T
             if variance_idx is not None:
                 term1[variance_idx] = (N - s2 * term1_noise) / kernel.get_hyper("variance")
             term1[-1] = term1_noise
@@ -578,8 +636,8 @@ def efgpnd_gradient_batched(
         if stats_out is not None:
             stats_out.update({
                 "mean_cg_iters": int(cg_mean.iters_completed),
-                "trace_cg_iters": int(cg_trace.iters_completed),
-                "trace_num_rhs": int(B_all.shape[0]),
+                "trace_cg_iters": int(trace_iters),
+                "trace_num_rhs": int(trace_rows),
                 "feature_count": int(M),
                 "mtot": int(mtot),
                 "trace_samples": int(T),
@@ -723,6 +781,7 @@ class EFGPND(nn.Module):
         if cg_tol is None:
             cg_tol = 0.1 * self.eps
         stats = {}
+        kwargs.setdefault("probe_group", _probe_shard_group(self.opts))
         result = efgpnd_gradient_batched(
             self.x, self.y, sigmasq=self._gp_params.sig2, kernel=self.kernel, eps=self.eps,
             trace_samples=trace_samples, x0=None, x1=None, do_profiling=do_profiling, nufft_eps=nufft_eps,
