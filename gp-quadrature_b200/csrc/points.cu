@@ -71,7 +71,10 @@ constexpr int kMaxBins2 = 8192;
 constexpr int kSortThreads = 256;
 constexpr int kSortPer = 8;
 static_assert(kSortThreads == kMaxBuckets, "the permutation kernels use one thread per bucket");
+constexpr int kL1Threads = 512;   // level-1 kernels: 512 threads x 4 points (fewer live registers per thread,
+constexpr int kL1Per = 4;         // 3 CTAs = 1536 threads per SM) over the same 2048-point tile
 constexpr int kSortTile = kSortThreads * kSortPer;  // 2048 points per CTA (43 KB of staging: 5 CTAs per SM)
+static_assert(kL1Threads * kL1Per == kSortTile, "level-1 and permutation kernels share one tile size");
 
 // fine-grid coordinate of one coordinate value, shifted by 1/2 for odd widths, in [0, nf)
 template <typename T>
@@ -107,7 +110,7 @@ __device__ __forceinline__ int64_t slot_of_rank(int64_t r, int log2P) {
 
 // ------------------------------------------------------------------ level 1
 template <typename T, int D>
-__global__ void __launch_bounds__(kSortThreads)
+__global__ void __launch_bounds__(kL1Threads)
 bucket_hist_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortGeom g, int ntiles1,
                    uint32_t* __restrict__ tileHist) {
   __shared__ uint32_t cnt[kMaxBuckets];
@@ -116,8 +119,8 @@ bucket_hist_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortGeom
   if (tid < kMaxBuckets) cnt[tid] = 0;
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < kSortPer; ++k) {
-    int64_t i = tile * kSortTile + k * kSortThreads + tid;
+  for (int k = 0; k < kL1Per; ++k) {
+    int64_t i = tile * kSortTile + k * kL1Threads + tid;
     if (i < N) {
       T X[D];
       uint32_t key = fold_point<T, D>(x, i, p, X);
@@ -125,13 +128,13 @@ bucket_hist_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortGeom
     }
   }
   __syncthreads();
-  for (int b = tid; b < g.nb1; b += kSortThreads) tileHist[(int64_t)b * ntiles1 + tile] = cnt[b];
+  for (int b = tid; b < g.nb1; b += kL1Threads) tileHist[(int64_t)b * ntiles1 + tile] = cnt[b];
 }
 
 // One CTA: bucket-sort its 2048 points in shared memory, then write each bucket's run contiguously.
 // NS = D staged words per point, or D + 1 when a per-point payload (real strengths y) rides along.
 template <typename T, int D, int NS>
-__global__ void __launch_bounds__(kSortThreads)
+__global__ void __launch_bounds__(kL1Threads, 3)
 bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64_t N, FoldParams<T> p, SortGeom g,
                       int ntiles1, const uint32_t* __restrict__ tileStart, T* __restrict__ R0, T* __restrict__ R1,
                       T* __restrict__ R2, T* __restrict__ R3, uint16_t* __restrict__ K2, uint32_t* __restrict__ A) {
@@ -146,12 +149,12 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
   const int64_t tile = blockIdx.x;
   if (tid < kMaxBuckets) cnt[tid] = 0;
   __syncthreads();
-  T X[kSortPer][NS];
-  uint32_t bk[kSortPer], lr[kSortPer];
-  uint16_t k2[kSortPer];
+  T X[kL1Per][NS];
+  uint32_t bk[kL1Per], lr[kL1Per];
+  uint16_t k2[kL1Per];
 #pragma unroll
-  for (int k = 0; k < kSortPer; ++k) {
-    int64_t i = tile * kSortTile + k * kSortThreads + tid;
+  for (int k = 0; k < kL1Per; ++k) {
+    int64_t i = tile * kSortTile + k * kL1Threads + tid;
     bk[k] = 0xffffffffu;
     if (i < N) {
       uint32_t key = fold_point<T, D>(x, i, p, X[k]);
@@ -185,9 +188,9 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
   }
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < kSortPer; ++k) {
+  for (int k = 0; k < kL1Per; ++k) {
     if (bk[k] != 0xffffffffu) {
-      int64_t i = tile * kSortTile + k * kSortThreads + tid;
+      int64_t i = tile * kSortTile + k * kL1Threads + tid;
       uint32_t lp = lstart[bk[k]] + lr[k];
 #pragma unroll
       for (int a = 0; a < NS; ++a) S[a * kSortTile + lp] = X[k][a];
@@ -200,7 +203,7 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
   const int64_t rem = N - tile * kSortTile;
   const int n_tile = rem < kSortTile ? (int)rem : kSortTile;
   T* R[4] = {R0, R1, R2, R3};
-  for (int lp = tid; lp < n_tile; lp += kSortThreads) {
+  for (int lp = tid; lp < n_tile; lp += kL1Threads) {
     uint32_t b = SB[lp];
     uint32_t a = gstart[b] + ((uint32_t)lp - lstart[b]);
 #pragma unroll
@@ -564,7 +567,7 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
 
   {
     ScopedStage stg("sort.bucket_hist_kernel", st, 1, N);
-    bucket_hist_kernel<T, D><<<ntiles1, kSortThreads, 0, st>>>(x, N, p, g, ntiles1, tileHist);
+    bucket_hist_kernel<T, D><<<ntiles1, kL1Threads, 0, st>>>(x, N, p, g, ntiles1, tileHist);
   }
   {
     ScopedStage stg("sort.scans", st, 0, 0);
@@ -589,10 +592,10 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
       attr_set = true;
     }
     if (ypay)
-      bucket_scatter_kernel<T, D, D + 1><<<ntiles1, kSortThreads, smem, st>>>(
+      bucket_scatter_kernel<T, D, D + 1><<<ntiles1, kL1Threads, smem, st>>>(
           x, ypay, N, p, g, ntiles1, tileStart, R[0], R[1], RY, nullptr, K2, sp.A);   // D == 2: word 2 = payload
     else
-      bucket_scatter_kernel<T, D, D><<<ntiles1, kSortThreads, smem, st>>>(x, nullptr, N, p, g, ntiles1, tileStart,
+      bucket_scatter_kernel<T, D, D><<<ntiles1, kL1Threads, smem, st>>>(x, nullptr, N, p, g, ntiles1, tileStart,
                                                                           R[0], R[1], R[2], nullptr, K2, sp.A);
   }
   const int ntiles2_max = ntiles1 + g.nb1;
