@@ -154,6 +154,95 @@ interp2d_kernel(const T* __restrict__ rec, int P,
   cp_async_wait<0>();
 }
 
+// ------------------------------------------------------------------ 3-D, shared-memory staged grid tiles
+// Mirror of spread3d_tile_kernel (spread.cu): points arrive tile-major; a CTA stages the current 8^3 tile
+// plus halo of the fine grid in shared memory ONCE and every point of the tile gathers its W^3 values from
+// there (one warp per point, lanes over the W x W cells of a plane, shuffle reduction) instead of W^3
+// loads from L2 per point.  Results are written in slot order (coalesced).
+constexpr int kT3ThreadsI = 128;
+constexpr int kT3BatchI = 32;
+constexpr int kT3ChunkI = 1024;
+
+template <typename T, int W>
+__host__ __device__ constexpr size_t tile3i_smem_bytes() {
+  constexpr int E = kTile3 + W - 1;
+  return sizeof(T) * (size_t)(E * E * E + kT3BatchI * 3 * W) + sizeof(int) * kT3BatchI * 4;
+}
+
+template <typename T, int W>
+__global__ void __launch_bounds__(kT3ThreadsI)
+interp3d_tile_kernel(const T* __restrict__ rec, int64_t N, int nf0, int nf1, int nf2, const T* __restrict__ grid,
+                     T* __restrict__ out, const __grid_constant__ ESDev<T> es) {
+  constexpr int E = kTile3 + W - 1;
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* S = reinterpret_cast<T*>(smem_raw);        // [E][E][E] tile + halo of the fine grid
+  T* KW = S + E * E * E;                        // [batch][3][W]
+  int* BI = reinterpret_cast<int*>(KW + kT3BatchI * 3 * W);   // [batch][4]: tile id, cell0, cell1, cell2
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nt1 = (nf1 + kTile3 - 1) / kTile3, nt2 = (nf2 + kTile3 - 1) / kTile3;
+  const int64_t p0 = (int64_t)blockIdx.x * kT3ChunkI;
+  const int64_t p1 = p0 + kT3ChunkI < N ? p0 + kT3ChunkI : N;
+  int cur_tile = -1, tb0 = 0, tb1 = 0, tb2 = 0;
+  for (int64_t b0 = p0; b0 < p1; b0 += kT3BatchI) {
+    const int nb = (int)(p1 - b0 < kT3BatchI ? p1 - b0 : kT3BatchI);
+    __syncthreads();   // previous batch fully consumed
+    if (tid < 3 * nb) {
+      const int pt = tid / 3, ax = tid - 3 * pt;
+      const T X = rec[(b0 + pt) * 4 + ax];
+      const int c = (int)X;
+      T kk[W];
+      es_eval_i<T, W>(es, T(2) * (X - (T)c) - T(1), kk);
+#pragma unroll
+      for (int i = 0; i < W; ++i) KW[(pt * 3 + ax) * W + i] = kk[i];
+      BI[pt * 4 + 1 + ax] = c;
+    }
+    __syncthreads();
+    if (tid < nb)
+      BI[tid * 4] = ((BI[tid * 4 + 1] / kTile3) * nt1 + BI[tid * 4 + 2] / kTile3) * nt2 + BI[tid * 4 + 3] / kTile3;
+    __syncthreads();
+    int p = 0;
+    while (p < nb) {           // uniform control flow
+      const int t = BI[p * 4];
+      if (t != cur_tile) {
+        cur_tile = t;
+        tb2 = (t % nt2) * kTile3;
+        tb1 = ((t / nt2) % nt1) * kTile3;
+        tb0 = (t / (nt2 * nt1)) * kTile3;
+        __syncthreads();       // everyone finished reading the old tile
+        for (int e = tid; e < E * E * E; e += kT3ThreadsI) {
+          int e0 = e / (E * E), e1 = (e / E) % E, e2 = e % E;
+          int64_t gi = ((int64_t)wrap_i(tb0 - OFF + e0, nf0) * nf1 + wrap_i(tb1 - OFF + e1, nf1)) * nf2 +
+                       wrap_i(tb2 - OFF + e2, nf2);
+          S[e] = __ldg(grid + gi);
+        }
+        __syncthreads();
+      }
+      int q = p + 1;
+      while (q < nb && BI[q * 4] == t) ++q;
+      for (int pt = p + warp; pt < q; pt += kT3ThreadsI / 32) {     // one warp per point
+        const int l0 = BI[pt * 4 + 1] - tb0, l1 = BI[pt * 4 + 2] - tb1, l2 = BI[pt * 4 + 3] - tb2;
+        const T* k0 = KW + (pt * 3 + 0) * W;
+        const T* k1 = KW + (pt * 3 + 1) * W;
+        const T* k2 = KW + (pt * 3 + 2) * W;
+        T acc = T(0);
+        for (int r = lane; r < W * W; r += 32) {
+          const int j = r / W, l = r - j * W;
+          const T* col = S + ((l0 * E + l1 + j) * E + l2 + l);
+          T ssum = T(0);
+#pragma unroll
+          for (int i = 0; i < W; ++i) ssum = fma(col[i * E * E], k0[i], ssum);
+          acc = fma(ssum, k1[j] * k2[l], acc);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+        if (lane == 0) out[b0 + pt] = acc;
+      }
+      p = q;
+    }
+  }
+}
+
 // generic: wide 2-D kernels and 3-D, one slot per thread, gathers through L1/L2
 template <typename T, int W, int D>
 __global__ void __launch_bounds__(256)
@@ -233,6 +322,13 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* grid, T
       interp_direct_kernel<T, W, 2><<<div_up(sp.npos, 256), 256, 0, st>>>(
           rec, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, out, ostride, es);
     }
+  } else if (getenv("EFGP_3D_TILE_INTERP")) {
+    // measured slower than the per-point gather below (one thread per point gathering through L1/L2 is
+    // instruction-lean; the tile-major sort gives it the locality): kept for A/B runs only
+    const size_t smem = tile3i_smem_bytes<T, W>();
+    EFGP_CUDA(cudaFuncSetAttribute(interp3d_tile_kernel<T, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    interp3d_tile_kernel<T, W><<<div_up(sp.N, kT3ChunkI), kT3ThreadsI, smem, st>>>(
+        rec, sp.N, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, out, es);
   } else {
     interp_direct_kernel<T, W, 3><<<div_up(sp.npos, 256), 256, 0, st>>>(
         rec, sp.npos, (int)sp.nf[0], (int)sp.nf[1], (int)sp.nf[2], grid, out, ostride, es);

@@ -19,6 +19,7 @@ namespace efgp {
 // run), and its j-th point is stored at slot  tile*kTileThreads*P + j*kTileThreads + t  so that at every
 // step j a warp reads 32 consecutive records (fully coalesced, prefetchable).  Slots past N hold X[0] = -1.
 constexpr int kTileThreads = 256;
+constexpr int kTile3 = 8;   // 3-D: edge (in cells) of the fine-grid tiles the sort groups points by
 struct SortedPoints {
   int dim = 0;
   int dtype = 1;  // 0 f32, 1 f64

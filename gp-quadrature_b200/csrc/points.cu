@@ -56,6 +56,7 @@ struct FoldParams {
   T nf[kMaxDim];
   int inf[kMaxDim];
   T shift;
+  int ntile[kMaxDim];   // 3-D: fine-grid tiles of kTile3 cells per axis (tile-major sort keys), else unused
 };
 
 struct SortGeom {
@@ -88,13 +89,26 @@ __device__ __forceinline__ T fold_coord(T xv, T h, T xc, T nf, T shift, int inf)
   return X;
 }
 
+// Sort key of a point.  1-D / 2-D: the flattened (row-major) cell index.  3-D: TILE-major -- cells are grouped
+// in kTile3^3 blocks and the key is (tile index) * kTile3^3 + (cell within the tile), so that all points of a
+// tile are consecutive after the sort: the 3-D spread / interp kernels stage one tile (+ halo) of the fine
+// grid in shared memory at a time (spread.cu, interp.cu).
 template <typename T, int D>
 __device__ __forceinline__ uint32_t fold_point(const T* __restrict__ x, int64_t i, const FoldParams<T>& p, T* X) {
   uint32_t key = 0;
+  int c[D];
 #pragma unroll
   for (int a = 0; a < D; ++a) {
     X[a] = fold_coord(x[i * D + a], p.h, p.xcen[a], p.nf[a], p.shift, p.inf[a]);
-    key = key * (uint32_t)p.inf[a] + (uint32_t)(int)X[a];
+    c[a] = (int)X[a];
+    key = key * (uint32_t)p.inf[a] + (uint32_t)c[a];
+  }
+  if (D == 3) {
+    const uint32_t tile = ((uint32_t)(c[0] / kTile3) * p.ntile[1] + (uint32_t)(c[1] / kTile3)) * p.ntile[2] +
+                          (uint32_t)(c[2] / kTile3);
+    const uint32_t within = ((uint32_t)(c[0] % kTile3) * kTile3 + (uint32_t)(c[1] % kTile3)) * kTile3 +
+                            (uint32_t)(c[2] % kTile3);
+    key = tile * (kTile3 * kTile3 * kTile3) + within;
   }
   return key;
 }
@@ -645,6 +659,8 @@ static void build_t(SortedPoints& sp, const T* x, const T* ypay, int64_t N, int 
     p.inf[a] = a < dim ? (int)nf[a] : 1;
     if (a < dim) cells *= (double)nf[a];
   }
+  for (int a = 0; a < kMaxDim; ++a) p.ntile[a] = a < dim ? (p.inf[a] + kTile3 - 1) / kTile3 : 1;
+  if (dim == 3) cells = (double)p.ntile[0] * p.ntile[1] * p.ntile[2] * (kTile3 * kTile3 * kTile3);  // key space
   EFGP_CHECK(cells < 4.0e9, "fine grid has too many cells for 32-bit cell indices");
   EFGP_CHECK(N < (int64_t)2147483000, "N must be < 2^31");
   const uint32_t ncell = (uint32_t)cells;
@@ -659,6 +675,20 @@ static void build_t(SortedPoints& sp, const T* x, const T* ypay, int64_t N, int 
   g.cpb = (ncell + nb1 - 1) / nb1;
   g.nb1 = (int)((ncell + g.cpb - 1) / g.cpb);
   g.g = (g.cpb + kMaxBins2 - 1) / kMaxBins2;          // > 1 only for grids above 2M cells (3-D): coarse order
+  if (dim == 3) {
+    // keep tiles contiguous in the final order: level-2 bins must not straddle tiles, so buckets hold whole
+    // tiles and a bin is a power-of-two fraction of a tile (or, for huge grids, a group of whole tiles)
+    const uint32_t tcells = kTile3 * kTile3 * kTile3;
+    g.cpb = (g.cpb + tcells - 1) / tcells * tcells;
+    g.nb1 = (int)((ncell + g.cpb - 1) / g.cpb);
+    uint32_t gmin = (g.cpb + kMaxBins2 - 1) / kMaxBins2;
+    if (gmin <= tcells) {
+      g.g = 1;
+      while (g.g < gmin) g.g <<= 1;
+    } else {
+      g.g = (gmin + tcells - 1) / tcells * tcells;
+    }
+  }
   g.nbins2 = (int)((g.cpb + g.g - 1) / g.g);
   g.log2P = 0;
   while ((1 << g.log2P) < sp.P) ++g.log2P;

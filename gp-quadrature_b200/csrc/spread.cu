@@ -174,6 +174,147 @@ spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
   if (cur0 >= 0) flush2d<T, W>(acc, cur0, cur1, nf0, nf1, grid);
 }
 
+// ------------------------------------------------------------------ 3-D, shared-memory tile accumulation
+// Points arrive tile-major (points.cu: 8^3-cell tiles).  A CTA takes a chunk of consecutive sorted points and
+// accumulates them into a shared-memory copy of the current tile plus its W-1 halo ((8+W-1)^3 values);
+// when the tile changes (or the chunk ends) the copy is added to the global grid with one RED per NONZERO
+// entry -- ~2e3-5e3 REDs per tile visit instead of W^3 (125..729) REDs per point.
+//
+// No shared-memory atomics (sm_100a has no native fp64 shared atomic): the 4 warps own disjoint x-planes
+// of the shared tile (plane s0 belongs to warp s0 & 3), every warp walks all points of the batch and adds
+// only the planes it owns, lanes covering the W x W cells of a plane.  Plain LDS/DFMA/STS, no races, no
+// barriers inside a batch.  Kernel weights for a batch of 32 points are evaluated once by 96 threads.
+constexpr int kT3Threads = 128;
+constexpr int kT3Batch = 32;
+constexpr int kT3Chunk = 1024;
+
+template <typename T, int W>
+__host__ __device__ constexpr size_t tile3_smem_bytes() {
+  constexpr int E = kTile3 + W - 1;
+  constexpr int EP = E | 1;   // odd row stride: rows of a plane fall in different shared-memory banks
+  return sizeof(T) * (size_t)(E * E * EP + kT3Batch * 3 * W + kT3Batch) + sizeof(int) * kT3Batch * 4;
+}
+
+template <typename T, int W, bool HAS_C>
+__global__ void __launch_bounds__(kT3Threads)
+spread3d_tile_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int64_t N, int nf0, int nf1, int nf2,
+                     T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
+  constexpr int E = kTile3 + W - 1;
+  constexpr int EP = E | 1;   // padded (odd) row stride
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  int* BI = reinterpret_cast<int*>(smem_raw);   // [batch][4]: tile id, cell0, cell1, cell2 (16-byte aligned)
+  T* S = reinterpret_cast<T*>(smem_raw + sizeof(int) * kT3Batch * 4);   // [E][E][EP] tile + halo
+  T* KW = S + E * E * EP;                       // [batch][3][W] kernel weights
+  T* CV = KW + kT3Batch * 3 * W;                // [batch] strengths
+  __shared__ unsigned segmask;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nt1 = (nf1 + kTile3 - 1) / kTile3, nt2 = (nf2 + kTile3 - 1) / kTile3;
+  const int64_t p0 = (int64_t)blockIdx.x * kT3Chunk;
+  const int64_t p1 = p0 + kT3Chunk < N ? p0 + kT3Chunk : N;
+  for (int e = tid; e < E * E * EP; e += kT3Threads) S[e] = T(0);
+  int cur_tile = -1, tb0 = 0, tb1 = 0, tb2 = 0;
+  // the (j, l) cells of a W x W plane this lane covers: fixed for the whole kernel
+  constexpr int R = (W * W + 31) / 32;
+  int cj[R], cl[R], cofs[R];
+#pragma unroll
+  for (int rr = 0; rr < R; ++rr) {
+    int r = lane + 32 * rr;
+    if (r >= W * W) r = 0;
+    cj[rr] = r / W;
+    cl[rr] = r - cj[rr] * W;
+    cofs[rr] = cj[rr] * EP + cl[rr];
+  }
+
+  auto flush = [&]() {   // add the tile copy to the grid and clear it (same thread reads and clears an entry)
+    for (int e = tid; e < E * E * EP; e += kT3Threads) {
+      T v = S[e];
+      if (v != T(0)) {   // (the pad column is never written, so it stays zero)
+        int e0 = e / (E * EP), e1 = (e / EP) % E, e2 = e % EP;
+        int64_t gi = ((int64_t)wrap_idx(tb0 - OFF + e0, nf0) * nf1 + wrap_idx(tb1 - OFF + e1, nf1)) * nf2 +
+                     wrap_idx(tb2 - OFF + e2, nf2);
+        atomicAdd(grid + gi, v);
+        S[e] = T(0);
+      }
+    }
+  };
+
+  for (int64_t b0 = p0; b0 < p1; b0 += kT3Batch) {
+    const int nb = (int)(p1 - b0 < kT3Batch ? p1 - b0 : kT3Batch);
+    __syncthreads();   // previous batch fully consumed (KW / BI reuse), S zeroing visible
+    if (tid < 3 * nb) {
+      const int pt = tid / 3, ax = tid - 3 * pt;
+      const T X = rec[(b0 + pt) * 4 + ax];
+      const int c = (int)X;
+      T kk[W];
+      es_eval<T, W>(es, T(2) * (X - (T)c) - T(1), kk);
+#pragma unroll
+      for (int i = 0; i < W; ++i) KW[(pt * 3 + ax) * W + i] = kk[i];
+      BI[pt * 4 + 1 + ax] = c;
+    } else if (tid >= 96 && tid < 96 + nb) {
+      CV[tid - 96] = HAS_C ? cs[b0 + tid - 96] : T(1);
+    }
+    __syncthreads();
+    if (tid < 32) {            // tile id per point, and a bit mask of the points that START a new tile run
+      int t = -2;
+      if (tid < nb) {
+        t = ((BI[tid * 4 + 1] / kTile3) * nt1 + BI[tid * 4 + 2] / kTile3) * nt2 + BI[tid * 4 + 3] / kTile3;
+        BI[tid * 4] = t;
+      }
+      int tprev = __shfl_up_sync(0xffffffffu, t, 1);
+      unsigned m = __ballot_sync(0xffffffffu, tid == 0 || t != tprev);
+      if (tid == 0) segmask = m;
+    }
+    __syncthreads();
+    const unsigned starts = segmask;
+    int p = 0;
+    while (p < nb) {           // uniform control flow: every thread reads the same shared values
+      const int t = BI[p * 4];
+      if (t != cur_tile) {
+        if (cur_tile >= 0) {
+          __syncthreads();     // all warps done with the old tile
+          flush();
+          __syncthreads();
+        }
+        cur_tile = t;
+        tb2 = (t % nt2) * kTile3;
+        tb1 = ((t / nt2) % nt1) * kTile3;
+        tb0 = (t / (nt2 * nt1)) * kTile3;
+      }
+      const unsigned later = p + 1 < 32 ? (starts >> (p + 1)) << (p + 1) : 0u;   // run starts after p
+      int q = later ? __ffs(later) - 1 : nb;
+      if (q > nb) q = nb;
+      for (int pt = p; pt < q; ++pt) {
+        const int4 bi = *reinterpret_cast<const int4*>(BI + pt * 4);
+        const int l0 = bi.y - tb0;
+        const int ifirst = (warp - l0) & 3;       // first x-plane of this footprint owned by this warp
+        if (ifirst >= W) continue;
+        const T cv = CV[pt];
+        const T* k0 = KW + (pt * 3 + 0) * W;
+        const T* k1 = KW + (pt * 3 + 1) * W;
+        const T* k2 = KW + (pt * 3 + 2) * W;
+        T wjl[R];
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr) wjl[rr] = cv * k1[cj[rr]] * k2[cl[rr]];
+        T* base = S + ((l0 * E + (bi.z - tb1)) * EP + (bi.w - tb2));
+#pragma unroll 1
+        for (int i = ifirst; i < W; i += 4) {
+          const T a = k0[i];
+          T* plane = base + i * (E * EP);
+#pragma unroll
+          for (int rr = 0; rr < R; ++rr)
+            if (rr + 1 < R || lane + 32 * rr < W * W) plane[cofs[rr]] = fma(a, wjl[rr], plane[cofs[rr]]);
+        }
+      }
+      p = q;
+    }
+  }
+  if (cur_tile >= 0) {
+    __syncthreads();
+    flush();
+  }
+}
+
 // ------------------------------------------------------------------ generic d (2-D wide kernels, 3-D): per-point REDs
 // Points are still cell-sorted, so the reductions of neighbouring slots land in the same L2 lines.
 template <typename T, int W, int D, int HAS_C>
@@ -263,12 +404,24 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
       else
         spread_direct_kernel<T, W, 2, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es);
     }
-  } else {
+  } else if (getenv("EFGP_3D_DIRECT")) {   // per-point REDs (kept for A/B measurements)
     int nb = div_up(sp.npos, 256);
     if (cs)
       spread_direct_kernel<T, W, 3, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es);
     else
       spread_direct_kernel<T, W, 3, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es);
+  } else {
+    const size_t smem = tile3_smem_bytes<T, W>();
+    int nb = div_up(sp.N, kT3Chunk);
+    if (cs) {
+      EFGP_CUDA(cudaFuncSetAttribute(spread3d_tile_kernel<T, W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+      spread3d_tile_kernel<T, W, true><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es);
+    } else {
+      EFGP_CUDA(cudaFuncSetAttribute(spread3d_tile_kernel<T, W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+      spread3d_tile_kernel<T, W, false><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es);
+    }
   }
   EFGP_CUDA(cudaGetLastError());
 }
