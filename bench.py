@@ -340,8 +340,15 @@ def main():
         top = max(own, key=lambda k: own[k]["ms"])
         v = own[top]
         ach = algorithmic_bytes(top, v["units"]) / v["ms"] / 1e6
+        # DRAM bytes per launch from the committed `ncu --set full` capture of this kernel (same N only)
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "ncu_r01_traffic.json")
+        if os.path.exists(tpath):
+            ent = json.load(open(tpath)).get(top)
+            if ent and ent.get("npts") == v["units"] // max(1, v["launches"]):
+                traffic = ent["dram_bytes_per_launch"]
         roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                    "traffic": None, "peak_source": peak_src, "avg_launch_ms": v["ms"] / v["launches"],
+                    "traffic": traffic, "peak_source": peak_src, "avg_launch_ms": v["ms"] / v["launches"],
                     "algorithmic_bytes_per_launch": algorithmic_bytes(top, v["units"]) / v["launches"],
                     "points_per_launch": v["units"] / v["launches"]}
     launches = sum(v["launches"] for v in stages.values())
