@@ -27,6 +27,13 @@ from utils.kernels import get_xis
 from efgp_b200 import ops as _ops
 from efgp_b200._lib import EfgpError
 
+# FFT size of the Toeplitz embedding built by EFGPND itself.  The reference pads 4m+1 to the next power of two
+# (efgpnd.py:791, :1269); any size >= 4m+1 gives the same product up to rounding (the circular wrap lands outside
+# the crop window), so the fit / variance / gradient paths use the next 2-3-5-smooth
+# size instead: 85 -> 90 rather than 128 is 2.9x less data per CG iteration in 3-D.  ToeplitzND's own default
+# (force_pow2=True) is unchanged, and .fft_shape reports what was used.
+_TOEPLITZ_POW2 = False
+
 # Where Rademacher probes are drawn.  None: on the data's device with torch's generator for that
 # device (what the reference's code does for CUDA inputs).  "cpu": drawn on the host with exactly the
 # reference's CPU calls and uploaded -- used by the parity tests, because the reference itself can
@@ -522,7 +529,7 @@ def efgpnd_gradient_batched(
             # generator first: the F*y / F beta transforms then reuse its (finer) sorted grid
             v_kernel = compute_convolution_vector_vectorized_dD(m_conv, x, h_f).to(dtype=cdtype)
             nufft_op = NUFFT(x, xcen, h_f, nufft_eps, cdtype=cdtype, device=device)
-            toeplitz = ToeplitzND(v_kernel, force_pow2=True)
+            toeplitz = ToeplitzND(v_kernel, force_pow2=_TOEPLITZ_POW2)
             A_apply = create_A_mean(ws, toeplitz, s2, cdtype)
             center = tuple((s - 1) // 2 for s in v_kernel.shape)
             diag_scale = v_kernel[center].real
@@ -860,7 +867,7 @@ class EFGPND(nn.Module):
         ws._efgp_real = True
         rhs = ws * Fy.reshape(-1)                                                # ws * F^* y
         v_kernel, rhs = _sum_over_shards(v_kernel, rhs, group)
-        toeplitz = ToeplitzND(v_kernel, force_pow2=True)
+        toeplitz = ToeplitzND(v_kernel, force_pow2=_TOEPLITZ_POW2)
         A_mean = create_A_mean(ws, toeplitz, s2, cdtype)
         center = tuple((s - 1) // 2 for s in v_kernel.shape)
         mean_M_inv = None
