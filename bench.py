@@ -203,15 +203,15 @@ def algorithmic_bytes(stage, n, d=2, word=8):
         return n * (word * d + word)                                        # coordinates + real result
     per_point = {
         "sort.bucket_hist_kernel": word * d,                                # read x
-        "sort.bucket_scatter_kernel": word * d + word * d + 2 + 4,          # read x; write folded coords, bin, A
-        "sort.bucket_scatter_kernel_pay": word * d + word + word * d + word + 2 + 4,   # ... plus the y payload in and out
+        "sort.bucket_scatter_kernel": word * d + word * d + 2 + 2,          # read x; write folded coords, bin, A (uint16)
+        "sort.bucket_scatter_kernel_pay": word * d + word + word * d + word + 2 + 2,   # ... plus the y payload in and out
         "sort.bin_scatter_kernel_pay": word * d + word + 2 + word * d + word + 4 + 4,  # ... plus y into the record
         "sort.bin_hist_kernel": 2,                                          # read level-2 bins
         "sort.bin_scatter_kernel": word * d + 2 + word * d + 4 + 4,         # read coords, bin; write record (coords, binv), B
-        "permute.to_bucket_order": word + 4 + word,                         # read c, A; write tmp
+        "permute.to_bucket_order": word + 2 + word,                         # read c, A; write tmp
         "permute.to_slot_order": 4 + word + word,                           # read Binv, tmp; write cs
         "unpermute.slot_to_bucket_order": 4 + word + word,                  # read B, r; write tmp
-        "unpermute.from_bucket_order": 4 + word + word,                     # read A, tmp; write out
+        "unpermute.from_bucket_order": 2 + word + word,                     # read A, tmp; write out
     }
     if stage in per_point:
         return n * per_point[stage]

@@ -34,11 +34,13 @@ struct TzGeomC {
   int64_t M, Ftot;
 };
 
-__device__ __forceinline__ void tzc_offsets(const TzGeomC& g, int64_t k, int64_t& pad_off, int64_t& crop_off) {
+__device__ __forceinline__ void tzc_offsets(const TzGeomC& g, int64_t k64, int64_t& pad_off, int64_t& crop_off) {
   int id[kMaxDim] = {0, 0, 0};
+  uint32_t k = (uint32_t)k64;          // M < 2^31 (checked on the host): 32-bit divisions
   for (int a = g.dim - 1; a >= 0; --a) {
-    id[a] = (int)(k % g.n[a]);
-    k /= g.n[a];
+    const uint32_t q = k / (uint32_t)g.n[a];
+    id[a] = (int)(k - q * (uint32_t)g.n[a]);
+    k = q;
   }
   pad_off = 0;
   crop_off = 0;
@@ -48,7 +50,8 @@ __device__ __forceinline__ void tzc_offsets(const TzGeomC& g, int64_t k, int64_t
   }
 }
 
-constexpr int kMaxChunks = 64;
+constexpr int kMaxChunks = 256;    // <= blockDim: a block re-reduces a row's partials with one value per thread
+constexpr int kChunkLen = 512;     // two elements per thread: the small-M kernels are latency chains otherwise
 
 struct CgScal {
   double* rz;        // [2][B]
@@ -76,12 +79,18 @@ __device__ __forceinline__ double block_sum(double v, double* sh) {
   return s;  // valid in thread 0
 }
 
+// Sum of a row's <= 256 chunk partials, same value (and summation order) in every thread of every block.
 __device__ __forceinline__ double sum_partials(const double* p, int nc) {
+  __shared__ double shp[9];
+  double v = (int)threadIdx.x < nc ? p[threadIdx.x] : 0.0;
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();                       // protects shp against the previous call's readers
+  if ((threadIdx.x & 31) == 0) shp[threadIdx.x >> 5] = v;
+  __syncthreads();
   double s = 0;
-  for (int i = 0; i < nc; ++i) s += p[i];
+  for (int i = 0; i < (int)(blockDim.x >> 5); ++i) s += shp[i];
   return s;
 }
-
 // r = b - Ax0 (Ax0 in Ap), p = minv * r, partials of <r, minv r> and ||b||^2
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -116,11 +125,11 @@ cg_init_kernel(const typename cplx_of<T>::type* __restrict__ b, const typename c
   }
 }
 
-__global__ void cg_init_scal_kernel(CgScal s) {
-  int row = blockIdx.x * blockDim.x + threadIdx.x;
-  if (row >= s.B) return;
+__global__ void __launch_bounds__(256) cg_init_scal_kernel(CgScal s) {   // one block per row
+  const int row = blockIdx.x;
   double rz = sum_partials(s.p_rz + row * s.NC, s.NC);
   double bb = sqrt(sum_partials(s.p_rr + row * s.NC, s.NC));
+  if (threadIdx.x != 0) return;
   s.rz[s.B + row] = rz;  // parity 1 == "previous" for iteration 0
   s.denom[row] = bb > 0 ? bb : 1.0;
   s.act[s.B + row] = 1;
@@ -279,13 +288,13 @@ cg_C_kernel(typename cplx_of<T>::type* __restrict__ x, typename cplx_of<T>::type
 }
 
 // After `it` iterations: register rows that converged in iteration it-1.
-__global__ void cg_final_kernel(int it, double tol, int early, int batched, CgScal s) {
-  int row = blockIdx.x * blockDim.x + threadIdx.x;
-  if (row >= s.B || it <= 0) return;
+__global__ void __launch_bounds__(256) cg_final_kernel(int it, double tol, int early, int batched, CgScal s) {
+  const int row = blockIdx.x;           // one block per row
+  if (it <= 0) return;
   const int prev = (it & 1) ^ 1;
   if (!s.act[prev * s.B + row]) return;
   double rz_new;
-  if (row_converged(s, row, tol, early, batched, rz_new)) {
+  if (row_converged(s, row, tol, early, batched, rz_new) && threadIdx.x == 0) {
     s.act[prev * s.B + row] = 0;
     s.conv_iter[row] = it - 1;
     atomicSub(&s.counters[0], 1);
@@ -322,7 +331,7 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   C *r = vec, *p = vec + (int64_t)B * M, *Ap = vec + (int64_t)2 * B * M;
   CgScal s;
   s.B = B;
-  s.NC = (int)std::min<int64_t>(kMaxChunks, std::max<int64_t>(1, (M + 2047) / 2048));
+  s.NC = (int)std::min<int64_t>(kMaxChunks, std::max<int64_t>(1, (M + kChunkLen - 1) / kChunkLen));
   s.len = (M + s.NC - 1) / s.NC;
   size_t nd = (size_t)2 * B + B + (size_t)3 * B * s.NC;
   size_t ni = (size_t)2 * B + B + 4;
@@ -354,7 +363,7 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   {
     ScopedStage stg_init("cg.init", st, 2);
     cg_init_kernel<T><<<grid, 256, 0, st>>>(b, Ap, minv, r, p, M, s);
-    cg_init_scal_kernel<<<div_up(B, 128), 128, 0, st>>>(s);
+    cg_init_scal_kernel<<<B, 256, 0, st>>>(s);
   }
   EFGP_CUDA(cudaGetLastError());
 
@@ -362,8 +371,15 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   if (!h_counters) EFGP_CUDA(cudaMallocHost(&h_counters, 2 * sizeof(int)));
   h_counters[0] = B;
   h_counters[1] = -1;
+  // When to look at the convergence counters first: every read-back stalls the host behind the stream, after
+  // which the remaining iterations are launch-bound.  Solves of the same kind (operator mode, single/batched)
+  // repeat with nearly the same iteration count in the EFGP loop, so the first check is scheduled where the
+  // previous such solve stopped; iterations past convergence are no-ops (rows are frozen on the device).
+  static int hint[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
+  int& my_hint = hint[mode][batched ? 1 : 0];
   int it = 0;
-  int check = 4;
+  int check = my_hint > 0 ? std::min(my_hint, 64) : 4;
+  bool first = true;
   ScopedStage stg("cg.iterations", st, 0);
   while (it < max_iter) {
     int until = std::min(max_iter, it + check);
@@ -378,16 +394,22 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
     }
     EFGP_CUDA(cudaGetLastError());
     if (early) {
-      cg_final_kernel<<<div_up(B, 128), 128, 0, st>>>(it, tol, early, batched, s);
+      cg_final_kernel<<<B, 256, 0, st>>>(it, tol, early, batched, s);
       EFGP_CUDA(cudaMemcpyAsync(h_counters, s.counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
       EFGP_CUDA(cudaStreamSynchronize(st));
       if (h_counters[0] <= 0) break;
     }
-    if (check < 32) check *= 2;
+    if (first) {
+      first = false;
+      check = 4;
+    } else if (check < 32) {
+      check *= 2;
+    }
   }
   if (!early) EFGP_CUDA(cudaStreamSynchronize(st));
   all_conv = early && h_counters[0] <= 0;
   jmax = h_counters[1];
+  if (all_conv) my_hint = jmax + 1;      // iterations 0..jmax: the final kernel then sees every row converged
 }
 
 void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void* minv, const void* b, void* x,
@@ -396,6 +418,7 @@ void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void*
   EFGP_CHECK(batch >= 1, "batch must be >= 1");
   EFGP_CHECK(mode >= 0 && mode <= 3, "unknown operator mode");
   EFGP_CHECK(mode == kModeT || ws != nullptr, "ws is required for Gv / A_mean / A_var");
+  EFGP_CHECK(t.M < (int64_t)1 << 31, "Toeplitz block too large for the 32-bit index arithmetic of the CG kernels");
   if (max_iter < 0) max_iter = (int)std::min<int64_t>(2 * t.M, 2147483647);
   size_t esz = t.dtype == 0 ? 8 : 16;
   int group = (int)std::max<int64_t>(1, std::min<int64_t>(batch, (int64_t)((12ull << 30) / ((size_t)t.Ftot * esz))));

@@ -10,6 +10,9 @@
 // transforms; complex type-2 outputs are the transforms of the Hermitian and anti-Hermitian parts
 // of the mode array), so every FFT is R2C/C2R on half the data of a complex transform.
 #include "nufft.cuh"
+#include <mutex>
+#include <map>
+#include <utility>
 #include <cmath>
 #include <algorithm>
 
@@ -292,6 +295,23 @@ static SortedPoints* get_sorted(Nufft& nu, const int64_t* nf, int odd, cudaStrea
 // Pick the fine grid, kernel and sorted point set for `n` modes at tolerance eps.  An existing
 // sorted set on a finer grid is reused when possible (larger effective upsampling -> narrower
 // kernel, and no second sort): this is how the F*y transform shares the Toeplitz-vector grid.
+// The polynomial fit of the ES kernel depends on (W, sigma) only and costs tens of microseconds of host time
+// right in front of the first kernel launch of every transform: keep the fitted tables for the process.
+static void es_build_cached(ESKernel& k, int W, double sigma) {
+  static auto* cache = new std::map<std::pair<int, double>, ESKernel>();
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  auto key = std::make_pair(W, sigma);
+  auto it = cache->find(key);
+  if (it == cache->end()) {
+    ESKernel fresh;
+    es_build(fresh, W, sigma, 0);
+    if (cache->size() > 256) cache->clear();
+    it = cache->emplace(key, fresh).first;
+  }
+  k = it->second;
+}
+
 static GridChoice choose_grid(Nufft& nu, const int64_t* n, double eps, cudaStream_t st) {
   GridChoice gc;
   const int max_w = kMaxW;
@@ -324,7 +344,7 @@ static GridChoice choose_grid(Nufft& nu, const int64_t* n, double eps, cudaStrea
     for (int a = 0; a < nu.dim; ++a) fits = fits && best->nf[a] >= 2 * w;
     if (fits) {
       for (int a = 0; a < kMaxDim; ++a) gc.nf[a] = best->nf[a];
-      es_build(gc.ker, w, std::min(sigma, 4.0), 0);
+      es_build_cached(gc.ker, w, std::min(sigma, 4.0));
       best->last_use = ++nu.clock;
       gc.sp = best;
       return gc;
@@ -334,7 +354,7 @@ static GridChoice choose_grid(Nufft& nu, const int64_t* n, double eps, cudaStrea
   for (int a = 0; a < nu.dim; ++a) sigma = std::min(sigma, (double)own[a] / (double)n[a]);
   int w = es_width_for(eps, std::min(sigma, 4.0), max_w);
   for (int a = 0; a < kMaxDim; ++a) gc.nf[a] = own[a];
-  es_build(gc.ker, w, std::min(sigma, 4.0), 0);
+  es_build_cached(gc.ker, w, std::min(sigma, 4.0));
   gc.sp = get_sorted(nu, gc.nf, w & 1, st);
   return gc;
 }

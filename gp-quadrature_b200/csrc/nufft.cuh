@@ -32,7 +32,7 @@ struct SortedPoints {
   int64_t ntiles = 0;
   int64_t npos = 0;     // ntiles * kTileThreads * P
   void* rec = nullptr;        // npos records
-  uint32_t* A = nullptr;      // A[i] = level-1 (bucket-order) position of original point i      (N entries)
+  uint16_t* A = nullptr;      // A[i] = position of original point i inside its 2048-point tile, bucket-major (N entries)
   uint32_t* B = nullptr;      // B[a] = slot of the point at level-1 position a (inverse of the records' binv)
   uint32_t* tileStart = nullptr;  // [nb1][ntiles1]: first level-1 position of (bucket, 2048-point tile)
   int ntiles1 = 0, nb1 = 0;

@@ -20,6 +20,7 @@
 // (coalesced reads, bucket runs) -> cs[slot] = tmp[Binv[slot]] (gather inside an L2-sized window);
 // type-2 results are written in slot order (coalesced), gathered into bucket order (tmp[a] = r[B[a]],
 // B = Binv^-1, inside the bucket window) and streamed back as out[i] = tmp[A[i]].
+#include <cstdlib>
 #include "nufft.cuh"
 #include <cub/device/device_scan.cuh>
 #include <algorithm>
@@ -68,6 +69,7 @@ struct SortGeom {
 };
 
 constexpr int kMaxBuckets = 256;
+constexpr int kDefaultBuckets = 128;
 constexpr int kMaxBins2 = 8192;
 constexpr int kSortThreads = 256;
 constexpr int kSortPer = 8;
@@ -151,7 +153,7 @@ template <typename T, int D, int NS>
 __global__ void __launch_bounds__(kL1Threads, 3)
 bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64_t N, FoldParams<T> p, SortGeom g,
                       int ntiles1, const uint32_t* __restrict__ tileStart, T* __restrict__ R0, T* __restrict__ R1,
-                      T* __restrict__ R2, T* __restrict__ R3, uint16_t* __restrict__ K2, uint32_t* __restrict__ A) {
+                      T* __restrict__ R2, T* __restrict__ R3, uint16_t* __restrict__ K2, uint16_t* __restrict__ A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* S = (T*)smem_raw;                                   // [NS][kSortTile]
   uint16_t* SK = (uint16_t*)(S + NS * kSortTile);        // level-2 bin
@@ -159,8 +161,11 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
   uint32_t* cnt = (uint32_t*)(SB + kSortTile);           // [kMaxBuckets]
   uint32_t* lstart = cnt + kMaxBuckets;
   uint32_t* gstart = lstart + kMaxBuckets;
+  __shared__ uint32_t wtot[kMaxBuckets / 32];
   const int tid = threadIdx.x;
   const int64_t tile = blockIdx.x;
+  // this tile's first output position in every bucket: issued now, consumed after the local scan
+  const uint32_t gs = tid < g.nb1 ? tileStart[(int64_t)tid * ntiles1 + tile] : 0u;
   if (tid < kMaxBuckets) cnt[tid] = 0;
   __syncthreads();
   T X[kL1Per][NS];
@@ -180,25 +185,23 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
     }
   }
   __syncthreads();
+  uint32_t c = 0, v = 0;
   if (tid < kMaxBuckets) {   // exclusive scan of the 256 bucket counts: warp scans + 8 warp totals
-    const uint32_t c = cnt[tid];
-    uint32_t v = c;
+    c = cnt[tid];
+    v = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
       if ((tid & 31) >= o) v += u;
     }
-    if ((tid & 31) == 31) gstart[tid >> 5] = v;   // gstart doubles as scratch for the warp totals
-    lstart[tid] = v - c;
+    if ((tid & 31) == 31) wtot[tid >> 5] = v;
   }
   __syncthreads();
-  uint32_t woff = 0;
-  if (tid < kMaxBuckets)
-    for (int q = 0; q < (tid >> 5); ++q) woff += gstart[q];
-  __syncthreads();
   if (tid < kMaxBuckets) {
-    lstart[tid] += woff;
-    gstart[tid] = tid < g.nb1 ? tileStart[(int64_t)tid * ntiles1 + tile] : 0u;
+    uint32_t woff = 0;
+    for (int q = 0; q < (tid >> 5); ++q) woff += wtot[q];
+    lstart[tid] = v - c + woff;
+    gstart[tid] = gs;
   }
   __syncthreads();
 #pragma unroll
@@ -210,7 +213,7 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
       for (int a = 0; a < NS; ++a) S[a * kSortTile + lp] = X[k][a];
       SK[lp] = k2[k];
       SB[lp] = (uint16_t)bk[k];
-      A[i] = gstart[bk[k]] + lr[k];
+      A[i] = (uint16_t)lp;      // tile-local position in bucket-major order (< kSortTile)
     }
   }
   __syncthreads();
@@ -232,11 +235,12 @@ __device__ __forceinline__ void store_record(T* dst, const T (&w)[RW]) {
   if constexpr (sizeof(T) * RW == 32) {
     const double* wd = reinterpret_cast<const double*>(w);
     st_global_256(reinterpret_cast<double*>(dst), wd[0], wd[1], wd[2], wd[3]);
-  } else if constexpr (sizeof(T) * RW == 16) {
-    const double* wd = reinterpret_cast<const double*>(w);
-    reinterpret_cast<double2*>(dst)[0] = make_double2(wd[0], wd[1]);
+  } else if constexpr (sizeof(T) == 8) {            // 1-D double: (X, index) = 16 bytes
+    reinterpret_cast<double2*>(dst)[0] = make_double2((double)w[0], (double)w[1]);
+  } else if constexpr (RW == 4) {                   // float records: 16 bytes, values stay in registers
+    reinterpret_cast<float4*>(dst)[0] = make_float4((float)w[0], (float)w[1], (float)w[2], (float)w[3]);
   } else {
-    reinterpret_cast<double*>(dst)[0] = *reinterpret_cast<const double*>(w);
+    reinterpret_cast<float2*>(dst)[0] = make_float2((float)w[0], (float)w[1]);
   }
 }
 
@@ -302,8 +306,11 @@ bin_hist_kernel(const uint16_t* __restrict__ K2, const uint32_t* __restrict__ bu
   }
 }
 
+// One level-2 tile (<= 2048 consecutive points of one bucket): all of the tile's words are loaded into registers
+// FIRST (8 points x 4 loads per thread in flight, their latency hidden behind the histogram phase), K2 is read
+// once, and every point leaves as ONE 256-bit record store.
 template <typename T, int D>
-__global__ void __launch_bounds__(kSortThreads)
+__global__ void __launch_bounds__(kSortThreads, 3)
 bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* __restrict__ R2,
                    const T* __restrict__ RY, const uint16_t* __restrict__ K2, const uint32_t* __restrict__ bucketStart,
                    const uint32_t* __restrict__ tile2Base, SortGeom g, const uint32_t* __restrict__ binStart,
@@ -314,33 +321,47 @@ bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* 
   int b;
   uint32_t s, e;
   if (!level2_tile_range(bucketStart, tile2Base, g.nb1, b, s, e)) return;
-  for (int q = threadIdx.x; q < g.nbins2; q += kSortThreads) cnt[q] = 0;
-  __syncthreads();
-  for (uint32_t a = s + threadIdx.x; a < e; a += kSortThreads) atomicAdd(&cnt[K2[a]], 1u);
-  __syncthreads();
-  for (int q = threadIdx.x; q < g.nbins2; q += kSortThreads) {
-    uint32_t c = cnt[q];
-    if (c) {
-      int64_t gb = (int64_t)b * g.nbins2 + q;
-      base[q] = binStart[gb] + atomicAdd(&binCursor[gb], c);
-    }
-    cnt[q] = 0;
-  }
-  __syncthreads();
   const T* R[3] = {R0, R1, R2};
   constexpr int RW = rec_words(D);
-  for (uint32_t a = s + threadIdx.x; a < e; a += kSortThreads) {
-    uint32_t q = K2[a];
-    uint32_t r = base[q] + atomicAdd(&cnt[q], 1u);
+  constexpr uint32_t kNone = 0xffffffffu;
+  uint32_t q[kSortPer];
+  T w[kSortPer][RW];
+#pragma unroll
+  for (int k = 0; k < kSortPer; ++k) {
+    const uint32_t a = s + k * kSortThreads + threadIdx.x;
+    q[k] = kNone;
+#pragma unroll
+    for (int d = 0; d < RW; ++d) w[k][d] = T(0);
+    if (a < e) {
+      q[k] = K2[a];
+#pragma unroll
+      for (int d = 0; d < D; ++d) w[k][d] = R[d][a];
+      if (D == 2 && RY) w[k][3] = RY[a];     // payload rides in the record's spare word
+    }
+  }
+  for (int i = threadIdx.x; i < g.nbins2; i += kSortThreads) cnt[i] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < kSortPer; ++k)
+    if (q[k] != kNone) atomicAdd(&cnt[q[k]], 1u);
+  __syncthreads();
+  for (int i = threadIdx.x; i < g.nbins2; i += kSortThreads) {
+    uint32_t c = cnt[i];
+    if (c) {
+      int64_t gb = (int64_t)b * g.nbins2 + i;
+      base[i] = binStart[gb] + atomicAdd(&binCursor[gb], c);
+    }
+    cnt[i] = 0;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < kSortPer; ++k) {
+    if (q[k] == kNone) continue;
+    const uint32_t a = s + k * kSortThreads + threadIdx.x;
+    uint32_t r = base[q[k]] + atomicAdd(&cnt[q[k]], 1u);
     int64_t slot = slot_of_rank((int64_t)r, g.log2P);
-    T w[RW];
-#pragma unroll
-    for (int d = 0; d < RW; ++d) w[d] = T(0);
-#pragma unroll
-    for (int d = 0; d < D; ++d) w[d] = R[d][a];
-    *reinterpret_cast<uint32_t*>(&w[D]) = a;
-    if (D == 2 && RY) w[3] = RY[a];      // payload rides in the record's spare word
-    store_record<T, RW>(rec + slot * RW, w);
+    *reinterpret_cast<uint32_t*>(&w[k][D]) = a;
+    store_record<T, RW>(rec + slot * RW, w[k]);
     B[a] = (uint32_t)slot;
   }
 }
@@ -389,86 +410,104 @@ __device__ __forceinline__ void tile_bucket_ranges(const uint32_t* __restrict__ 
   lstart[tid] = woff + v - c;
   __syncthreads();
 }
-// last b in [0, n) with key[b] <= v (key ascending, key[0] <= v)
-__device__ __forceinline__ int last_le(const uint32_t* key, int n, uint32_t v) {
-  int lo = 0, hi = n;
-  while (hi - lo > 1) {
-    int mid = (lo + hi) >> 1;
-    if (key[mid] <= v) lo = mid; else hi = mid;
-  }
-  return lo;
+// Lanes-per-bucket of the run copies below: the power of two nearest the mean run length kSortTile / nb1.
+__host__ __device__ inline int run_group_shift(int nb1) {
+  int per = kSortTile / (nb1 > 0 ? nb1 : 1);
+  int sh = 3;
+  while (sh < 5 && (1 << sh) < per) ++sh;
+  return sh;   // 8, 16 or 32 lanes
 }
 
-// tmp[A[i]] = c[i]: the tile's values are bucket-ordered in shared memory, then each bucket's run is written
-// contiguously (full sectors, few L2 requests) instead of one scattered 8-byte store per point.
+// tmp[a(i)] = c[i]: the tile's values are bucket-ordered in shared memory through A (tile-local position of
+// point i in bucket-major order), then each bucket's run is written contiguously by a group of lanes (full
+// sectors, few L2 requests) instead of one scattered 8-byte store per point.
 template <typename T>
 __global__ void __launch_bounds__(kMaxBuckets)
-to_bucket_order_kernel(const T* __restrict__ c, int64_t cstride, const uint32_t* __restrict__ A, int64_t N,
-                       const uint32_t* __restrict__ tileStart, int ntiles1, int nb1, T* __restrict__ tmp) {
+to_bucket_order_kernel(const T* __restrict__ c, int64_t cstride, const uint16_t* __restrict__ A, int64_t N,
+                       const uint32_t* __restrict__ tileStart, int ntiles1, int nb1, int gshift,
+                       T* __restrict__ tmp) {
   __shared__ T S[kSortTile];
-  __shared__ uint8_t SB[kSortTile];
   __shared__ uint32_t gstart[kMaxBuckets], lstart[kMaxBuckets], wsum[8];
   const int tid = threadIdx.x;
   const int64_t tile = blockIdx.x;
-  tile_bucket_ranges(tileStart, ntiles1, nb1, N, tile, gstart, lstart, wsum);
+  T v[kSortPer];
+  uint32_t lp[kSortPer];
 #pragma unroll
   for (int k = 0; k < kSortPer; ++k) {
     int64_t i = tile * kSortTile + k * kSortThreads + tid;
+    lp[k] = 0xffffffffu;
     if (i < N) {
-      uint32_t a = A[i];
-      int b = last_le(gstart, nb1, a);
-      uint32_t lp = lstart[b] + (a - gstart[b]);
-      S[lp] = c[i * cstride];
-      SB[lp] = (uint8_t)b;
+      lp[k] = A[i];
+      v[k] = c[i * cstride];
     }
   }
+  tile_bucket_ranges(tileStart, ntiles1, nb1, N, tile, gstart, lstart, wsum);
+#pragma unroll
+  for (int k = 0; k < kSortPer; ++k)
+    if (lp[k] != 0xffffffffu) S[lp[k]] = v[k];
   __syncthreads();
   const int64_t rem = N - tile * kSortTile;
-  const int n_tile = rem < kSortTile ? (int)rem : kSortTile;
-  for (int lp = tid; lp < n_tile; lp += kSortThreads) {
-    int b = SB[lp];
-    tmp[gstart[b] + ((uint32_t)lp - lstart[b])] = S[lp];
+  const uint32_t n_tile = rem < kSortTile ? (uint32_t)rem : (uint32_t)kSortTile;
+  const int G = 1 << gshift, lane = tid & (G - 1);
+  for (int b = tid >> gshift; b < nb1; b += (kMaxBuckets >> gshift)) {
+    const uint32_t ls = lstart[b], gs = gstart[b];
+    const uint32_t cnt = (b + 1 < nb1 ? lstart[b + 1] : n_tile) - ls;
+    for (uint32_t j = lane; j < cnt; j += G) tmp[gs + j] = S[ls + j];
   }
 }
 
 // tmp[a] = r[B[a]]: slot-order results into bucket order.  a runs sequentially, so B and tmp stream and
-// the gathers from r stay inside the current bucket's L2-sized window.
+// the gathers from r stay inside the current bucket's L2-sized window.  Four positions per thread: one
+// 16-byte load of B, four independent gathers in flight.
 template <typename T>
 __global__ void __launch_bounds__(256)
 slot_to_bucket_order_kernel(const T* __restrict__ r, const uint32_t* __restrict__ B, int64_t N,
                             T* __restrict__ tmp) {
-  int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (a >= N) return;
-  tmp[a] = r[B[a]];
+  const int64_t a0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (a0 + 3 < N) {
+    const uint4 bv = __ldg(reinterpret_cast<const uint4*>(B + a0));
+    const T v0 = r[bv.x], v1 = r[bv.y], v2 = r[bv.z], v3 = r[bv.w];
+    if constexpr (sizeof(T) == 8) {
+      st_global_256(reinterpret_cast<double*>(tmp + a0), v0, v1, v2, v3);
+    } else {
+      reinterpret_cast<float4*>(tmp + a0)[0] = make_float4(v0, v1, v2, v3);
+    }
+  } else {
+    for (int64_t a = a0; a < N; ++a) tmp[a] = r[B[a]];
+  }
 }
 
-// out[i] = tmp[A[i]]: each bucket's run of this tile is read contiguously into shared memory, then every
-// point picks its value from there and the output is written coalesced.
+// out[i] = tmp[a(i)]: each bucket's run of this tile is read contiguously into shared memory by a group of
+// lanes, then every point picks its value at its tile-local position A[i] and the output is written coalesced.
 template <typename T>
 __global__ void __launch_bounds__(kMaxBuckets)
-from_bucket_order_kernel(const T* __restrict__ tmp, const uint32_t* __restrict__ A,
-                         int64_t N, const uint32_t* __restrict__ tileStart, int ntiles1, int nb1,
+from_bucket_order_kernel(const T* __restrict__ tmp, const uint16_t* __restrict__ A,
+                         int64_t N, const uint32_t* __restrict__ tileStart, int ntiles1, int nb1, int gshift,
                          T* __restrict__ out, int64_t ostride) {
   __shared__ T S[kSortTile];
   __shared__ uint32_t gstart[kMaxBuckets], lstart[kMaxBuckets], wsum[8];
   const int tid = threadIdx.x;
   const int64_t tile = blockIdx.x;
+  uint32_t lp[kSortPer];
+#pragma unroll
+  for (int k = 0; k < kSortPer; ++k) {      // issued first: consumed after the staging phase
+    int64_t i = tile * kSortTile + k * kSortThreads + tid;
+    lp[k] = i < N ? (uint32_t)A[i] : 0xffffffffu;
+  }
   tile_bucket_ranges(tileStart, ntiles1, nb1, N, tile, gstart, lstart, wsum);
   const int64_t rem = N - tile * kSortTile;
-  const int n_tile = rem < kSortTile ? (int)rem : kSortTile;
-  for (int lp = tid; lp < n_tile; lp += kSortThreads) {
-    int b = last_le(lstart, nb1, (uint32_t)lp);
-    S[lp] = tmp[gstart[b] + ((uint32_t)lp - lstart[b])];
+  const uint32_t n_tile = rem < kSortTile ? (uint32_t)rem : (uint32_t)kSortTile;
+  const int G = 1 << gshift, lane = tid & (G - 1);
+  for (int b = tid >> gshift; b < nb1; b += (kMaxBuckets >> gshift)) {
+    const uint32_t ls = lstart[b], gs = gstart[b];
+    const uint32_t cnt = (b + 1 < nb1 ? lstart[b + 1] : n_tile) - ls;
+    for (uint32_t j = lane; j < cnt; j += G) S[ls + j] = tmp[gs + j];
   }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < kSortPer; ++k) {
     int64_t i = tile * kSortTile + k * kSortThreads + tid;
-    if (i < N) {
-      uint32_t a = A[i];
-      int b = last_le(gstart, nb1, a);
-      out[i * ostride] = S[lstart[b] + (a - gstart[b])];
-    }
+    if (lp[k] != 0xffffffffu) out[i * ostride] = S[lp[k]];
   }
 }
 
@@ -486,14 +525,15 @@ void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, v
   if (sp.npos == 0) return;
   const size_t esz = sp.dtype == 0 ? 4 : 8;
   void* tmp = pool_alloc(esz * (size_t)sp.N);
+  const int gsh = run_group_shift(sp.nb1);
   {
     ScopedStage stg("permute.to_bucket_order", st, 1, sp.N);
     if (sp.dtype == 0)
       to_bucket_order_kernel<float><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const float*)c, cstride, sp.A, sp.N,
-                                                                        sp.tileStart, sp.ntiles1, sp.nb1, (float*)tmp);
+                                                                        sp.tileStart, sp.ntiles1, sp.nb1, gsh, (float*)tmp);
     else
       to_bucket_order_kernel<double><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const double*)c, cstride, sp.A, sp.N,
-                                                                         sp.tileStart, sp.ntiles1, sp.nb1, (double*)tmp);
+                                                                         sp.tileStart, sp.ntiles1, sp.nb1, gsh, (double*)tmp);
   }
   {
     ScopedStage stg("permute.to_slot_order", st, 1, sp.N);
@@ -512,21 +552,22 @@ void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t 
   if (sp.N == 0) return;
   const size_t esz = sp.dtype == 0 ? 4 : 8;
   void* tmp = pool_alloc(esz * (size_t)sp.N);
+  const int gsh = run_group_shift(sp.nb1);
   {
     ScopedStage stg("unpermute.slot_to_bucket_order", st, 1, sp.N);
     if (sp.dtype == 0)
-      slot_to_bucket_order_kernel<float><<<div_up(sp.N, 256), 256, 0, st>>>((const float*)r, sp.B, sp.N, (float*)tmp);
+      slot_to_bucket_order_kernel<float><<<div_up(sp.N, 1024), 256, 0, st>>>((const float*)r, sp.B, sp.N, (float*)tmp);
     else
-      slot_to_bucket_order_kernel<double><<<div_up(sp.N, 256), 256, 0, st>>>((const double*)r, sp.B, sp.N, (double*)tmp);
+      slot_to_bucket_order_kernel<double><<<div_up(sp.N, 1024), 256, 0, st>>>((const double*)r, sp.B, sp.N, (double*)tmp);
   }
   {
     ScopedStage stg("unpermute.from_bucket_order", st, 1, sp.N);
     if (sp.dtype == 0)
       from_bucket_order_kernel<float><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const float*)tmp, sp.A, sp.N, sp.tileStart,
-                                                                          sp.ntiles1, sp.nb1, (float*)out, ostride);
+                                                                          sp.ntiles1, sp.nb1, gsh, (float*)out, ostride);
     else
       from_bucket_order_kernel<double><<<sp.ntiles1, kMaxBuckets, 0, st>>>((const double*)tmp, sp.A, sp.N, sp.tileStart,
-                                                                           sp.ntiles1, sp.nb1, (double*)out, ostride);
+                                                                           sp.ntiles1, sp.nb1, gsh, (double*)out, ostride);
   }
   EFGP_CUDA(cudaGetLastError());
   pool_free(tmp);  // stream-ordered reuse
@@ -573,7 +614,7 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
   scan_bytes = std::max(scan_bytes, sb2);
   void* scan_tmp = pool_alloc(scan_bytes);
 
-  sp.A = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
+  sp.A = (uint16_t*)pool_alloc(sizeof(uint16_t) * (size_t)N);
   sp.B = (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N);
   sp.RW = rec_words(D);
   sp.rec = pool_alloc(sizeof(T) * (size_t)sp.RW * (size_t)sp.npos);
@@ -671,7 +712,18 @@ static void build_t(SortedPoints& sp, const T* x, const T* ypay, int64_t N, int 
   sp.npos = sp.ntiles * tile_len;
 
   SortGeom g;
-  int nb1 = (int)std::min<uint32_t>(kMaxBuckets, ncell);
+  // Level-1 bucket count.  Fewer buckets = longer per-tile runs (2048 / nb1 points: fuller sectors in the bucket
+  // scatter and in the un-permute), more buckets = smaller level-2 windows and histograms.  Measured at N = 1e8
+  // on 288^2 cells: 256 / 128 / 64 buckets -> 9.39 / 9.03 / 9.08 ms per solve.  Grids with more than
+  // 128 * kMaxBins2 cells take up to 256 buckets to keep the level-2 sort exact.  EFGP_SORT_BUCKETS overrides.
+  static const int nb1_env = [] {
+    const char* e = std::getenv("EFGP_SORT_BUCKETS");
+    int v = e ? std::atoi(e) : 0;
+    return v >= 1 && v <= kMaxBuckets ? v : 0;
+  }();
+  int nb1_want = nb1_env ? nb1_env
+                         : (int)std::min<uint32_t>(kMaxBuckets, std::max<uint32_t>(kDefaultBuckets, (ncell + kMaxBins2 - 1) / kMaxBins2));
+  int nb1 = (int)std::min<uint32_t>((uint32_t)nb1_want, ncell);
   g.cpb = (ncell + nb1 - 1) / nb1;
   g.nb1 = (int)((ncell + g.cpb - 1) / g.cpb);
   g.g = (g.cpb + kMaxBins2 - 1) / kMaxBins2;          // > 1 only for grids above 2M cells (3-D): coarse order

@@ -23,7 +23,7 @@ from torch.optim import Adam
 
 from cg import ConjugateGradients
 from kernels.kernel_params import GPParams
-from utils.kernels import get_xis
+from utils.kernels import get_xis, truncation_bounds
 from efgp_b200 import ops as _ops
 from efgp_b200._lib import EfgpError
 
@@ -79,16 +79,22 @@ def _probe_shard_group(opts):
     return dist.group.WORLD if g is True else g
 
 
-def _domain_length(x, group=None):
-    """L = max_d (max x_d - min x_d) (efgpnd.py:751), over ALL shards when the points are sharded: one
-    pass over the local x, then a MAX all-reduce of [max, -min]."""
+def _domain_length_async(x, group=None):
+    """Enqueue L = max_d (max x_d - min x_d) (efgpnd.py:751), over ALL shards when the points are sharded: one
+    pass over the local x, then a MAX all-reduce of [max, -min].  Returns a 0-d device tensor; the caller reads
+    it (the one unavoidable host sync of a fit: every grid size depends on it) after doing its L-independent
+    host work."""
     d = x.shape[1]
     lo_x, hi_x = torch.aminmax(x, dim=0)
     if group is None:
-        return float(torch.max(hi_x - lo_x).item())
+        return torch.max(hi_x - lo_x)
     ext = torch.cat([hi_x, -lo_x])
     torch.distributed.all_reduce(ext, op=torch.distributed.ReduceOp.MAX, group=group)
-    return float(torch.max(ext[:d] + ext[d:]).item())
+    return torch.max(ext[:d] + ext[d:])
+
+
+def _domain_length(x, group=None):
+    return float(_domain_length_async(x, group).item())
 
 
 def _sum_over_shards(v_kernel, rhs, group=None):
@@ -725,6 +731,7 @@ class EFGPND(nn.Module):
         self._beta = None
         self._xis = None
         self._ws = None
+        self._ws_real = None
         self._toeplitz = None
         self._fitted = False
         self._cached_params = {}
@@ -842,11 +849,13 @@ class EFGPND(nn.Module):
             x = x[:, None]
         N, d = x.shape
         group = _point_shard_group(self.opts)
-        L = _domain_length(x, group)
+        L_dev = _domain_length_async(x, group)
+        bounds = truncation_bounds(self.kernel, self.eps)      # host bisections overlap the device reduction
+        L = float(L_dev.item())
         if L <= 1e-9:
             L = 1.0
         xis_1d, h_float, mtot = get_xis(kernel_obj=self.kernel, eps=self.eps, L=L, use_integral=True,
-                                        l2scaled=False)
+                                        l2scaled=False, bounds=bounds)
         OUT = (mtot,) * d
         m_conv = (mtot - 1) // 2
         xcen = [0.0] * d
@@ -886,6 +895,7 @@ class EFGPND(nn.Module):
         self._beta = beta
         self._xis = xis
         self._ws = ws
+        self._ws_real = A_mean.ws_real          # contiguous real weights, reused by predict's fused type-2 scaling
         self._toeplitz = toeplitz
         self._fitted = True
         self._fit_params = self._current_params()
@@ -926,7 +936,7 @@ class EFGPND(nn.Module):
             OUT = (mtot,) * d
             nufft_op = NUFFT(x_new, xcen, h_float, nufft_eps, cdtype=cdtype, device=device)
             with rf("predict_mean"):
-                yhat = nufft_op.type2(beta, OUT, scale=ws.real.contiguous(), real_out=True)   # Re F(ws beta)
+                yhat = nufft_op.type2(beta, OUT, scale=self._ws_real, real_out=True)          # Re F(ws beta)
             out = {"mean": yhat}
             with rf("compute_variance"):
                 if return_variance:
@@ -936,7 +946,8 @@ class EFGPND(nn.Module):
                         h=h, xcen=xcen, hutchinson_probes=hutchinson_probes, nufft_eps=nufft_eps, device=device,
                         rdtype=rdtype, cdtype=cdtype)
                 else:
-                    out["var"] = torch.full((B,), float("nan"), device=device, dtype=rdtype)
+                    # (B,) of NaN like the reference (efgpnd.py:948), as a broadcast view: no O(B) fill kernel
+                    out["var"] = torch.full((1,), float("nan"), device=device, dtype=rdtype).expand(B)
             with rf("compute_log_marginal"):
                 if compute_log_marginal:
                     out["log_marginal"] = self._compute_log_marginal(beta=beta, ws=ws, sigmasq=s2, toeplitz=toeplitz,

@@ -59,7 +59,29 @@ def _scalar_bound(eps, f):
     return g.find_truncation_bound()
 
 
-def get_xis(kernel_obj, eps, L, use_integral=False, l2scaled=False, dtype=torch.float64, trunc_eps=None):
+def truncation_bounds(kernel_obj, eps, dtype=torch.float64, trunc_eps=None):
+    """(Ltime, Lfreq): the eps-supports of k(r) and of |r|^(d-1) S(r)/S(0) (utils/kernels.py:91-104).  They do
+    not depend on the domain size L, so a caller can run the two bisections while the device still reduces
+    the bounding box of the points, and hand the result to get_xis(..., bounds=...)."""
+    dim = kernel_obj.dimension
+    if trunc_eps is None:
+        trunc_eps = eps
+    if hasattr(kernel_obj, "_scalar_closures"):
+        kf, sf = kernel_obj._scalar_closures()
+        Ltime = _scalar_bound(eps, kf)
+        s0 = sf(0.0)
+        Lfreq = _scalar_bound(trunc_eps, lambda r: abs(r ** (dim - 1)) * sf(r) / s0)
+    else:  # any object with tensor-valued kernel / spectral_density, exactly as the reference does it
+        Ltime = GetTruncationBound(eps, kernel_obj.kernel, dtype=dtype).find_truncation_bound()
+        zero = torch.tensor(0, device="cpu", dtype=dtype)
+        Lfreq = GetTruncationBound(
+            trunc_eps, lambda r: abs(r ** (dim - 1)) * kernel_obj.spectral_density(r)
+            / kernel_obj.spectral_density(zero), dtype=dtype).find_truncation_bound()
+    return Ltime, Lfreq
+
+
+def get_xis(kernel_obj, eps, L, use_integral=False, l2scaled=False, dtype=torch.float64, trunc_eps=None,
+            bounds=None):
     """1-D equispaced Fourier nodes for tolerance eps on a domain of size L (utils/kernels.py:72-143)."""
     dim = kernel_obj.dimension
     if trunc_eps is None:
@@ -69,17 +91,7 @@ def get_xis(kernel_obj, eps, L, use_integral=False, l2scaled=False, dtype=torch.
     else:
         L_val = float(L)
     if use_integral:
-        if hasattr(kernel_obj, "_scalar_closures"):
-            kf, sf = kernel_obj._scalar_closures()
-            Ltime = _scalar_bound(eps, kf)
-            s0 = sf(0.0)
-            Lfreq = _scalar_bound(trunc_eps, lambda r: abs(r ** (dim - 1)) * sf(r) / s0)
-        else:  # any object with tensor-valued kernel / spectral_density, exactly as the reference does it
-            Ltime = GetTruncationBound(eps, kernel_obj.kernel, dtype=dtype).find_truncation_bound()
-            zero = torch.tensor(0, device="cpu", dtype=dtype)
-            Lfreq = GetTruncationBound(
-                trunc_eps, lambda r: abs(r ** (dim - 1)) * kernel_obj.spectral_density(r)
-                / kernel_obj.spectral_density(zero), dtype=dtype).find_truncation_bound()
+        Ltime, Lfreq = bounds if bounds is not None else truncation_bounds(kernel_obj, eps, dtype, trunc_eps)
         h_spacing = 1 / (L_val + Ltime)
         hm = math.ceil(Lfreq / h_spacing)
     else:
