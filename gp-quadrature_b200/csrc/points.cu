@@ -480,7 +480,7 @@ slot_to_bucket_order_kernel(const T* __restrict__ r, const uint32_t* __restrict_
 // out[i] = tmp[a(i)]: each bucket's run of this tile is read contiguously into shared memory by a group of
 // lanes, then every point picks its value at its tile-local position A[i] and the output is written coalesced.
 template <typename T>
-__global__ void __launch_bounds__(kMaxBuckets)
+__global__ void __launch_bounds__(kMaxBuckets, 5)
 from_bucket_order_kernel(const T* __restrict__ tmp, const uint16_t* __restrict__ A,
                          int64_t N, const uint32_t* __restrict__ tileStart, int ntiles1, int nb1, int gshift,
                          T* __restrict__ out, int64_t ostride) {
@@ -497,11 +497,27 @@ from_bucket_order_kernel(const T* __restrict__ tmp, const uint16_t* __restrict__
   tile_bucket_ranges(tileStart, ntiles1, nb1, N, tile, gstart, lstart, wsum);
   const int64_t rem = N - tile * kSortTile;
   const uint32_t n_tile = rem < kSortTile ? (uint32_t)rem : (uint32_t)kSortTile;
-  const int G = 1 << gshift, lane = tid & (G - 1);
-  for (int b = tid >> gshift; b < nb1; b += (kMaxBuckets >> gshift)) {
-    const uint32_t ls = lstart[b], gs = gstart[b];
-    const uint32_t cnt = (b + 1 < nb1 ? lstart[b + 1] : n_tile) - ls;
-    for (uint32_t j = lane; j < cnt; j += G) S[ls + j] = tmp[gs + j];
+  const int G = 1 << gshift, lane = tid & (G - 1), ngroups = kMaxBuckets >> gshift;
+  // first G elements of 4 runs per lane group at a time: their global loads are in flight together
+  for (int b0 = tid >> gshift; b0 < nb1; b0 += 4 * ngroups) {
+    uint32_t ls[4], gs[4], cnt[4];
+    T v[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int b = b0 + q * ngroups;
+      cnt[q] = 0;
+      if (b < nb1) {
+        ls[q] = lstart[b];
+        gs[q] = gstart[b];
+        cnt[q] = (b + 1 < nb1 ? lstart[b + 1] : n_tile) - ls[q];
+        if ((uint32_t)lane < cnt[q]) v[q] = tmp[gs[q] + lane];
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if ((uint32_t)lane < cnt[q]) S[ls[q] + lane] = v[q];
+      for (uint32_t j = lane + G; j < cnt[q]; j += G) S[ls[q] + j] = tmp[gs[q] + j];   // long runs (clustered points)
+    }
   }
   __syncthreads();
 #pragma unroll
