@@ -218,6 +218,20 @@ def algorithmic_bytes(stage, n, d=2, word=8):
     return None
 
 
+def algorithmic_flops(stage, n, d=2):
+    """FP64 flops (FMA = 2) the spreading / interpolation kernels need for n points: per dimension the even/odd
+    Horner evaluation of the W piecewise polynomials of degree W + 2 (spread.cu es_eval), then W^d FMAs."""
+    import re
+    m = re.match(r"(spread|interp)\dd_w(\d+)_", stage)
+    if not m:
+        return None
+    W = int(m.group(2))
+    deg = W + 2
+    ne, no = deg // 2 + 1, (deg + 1) // 2
+    horner = (W // 2) * (2 * (ne + no - 2) + 3) + (2 * (ne - 1) if W % 2 else 0) + 4
+    return n * (d * horner + 2 * W ** d + W)
+
+
 def bind_to_gpu_numa_node(local):
     """Pin this rank to the CPUs next to its GPU so that its pinned staging buffers (first touch) and the
     H2D / D2H DMA stay on the GPU's own NUMA node; 8 ranks otherwise share one node's memory controllers."""
@@ -324,20 +338,65 @@ def main():
             m = solve(xd, yd)
             mh.copy_(m, non_blocking=True)
 
+        def timed(run_steps):
+            barrier()
+            e0.record()
+            run_steps()
+            e1.record()
+            barrier()
+            tt = torch.tensor([e0.elapsed_time(e1) / args.steps], device=dev, dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return float(tt.item())
+
+        # (1) serial: copy in, solve, copy out, one step after the other on one stream
         e2e_step()
-        barrier()
-        e0.record()
-        for _ in range(args.steps):
-            e2e_step()
-        e1.record()
-        barrier()
-        t = torch.tensor([e0.elapsed_time(e1) / args.steps], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_e2e = float(t.item())
+        ms_serial = timed(lambda: [e2e_step() for _ in range(args.steps)])
+
+        # (2) double-buffered, what a serving loop does: the upload of step k+1 (copy stream) runs while step k
+        # is solved (compute stream) and the result of step k goes back on a third stream.  Every step still
+        # uploads its own 24 B/pt and downloads its own 8 B/pt inside the timed region.
+        cur = torch.cuda.current_stream()
+        s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+        xdb, ydb = [xd, torch.empty_like(x)], [yd, torch.empty_like(y)]
+        mhb = [mh, torch.empty((n_loc,), dtype=torch.float64, pin_memory=True)]
+        ev_in = [torch.cuda.Event(), torch.cuda.Event()]
+        ev_free = [torch.cuda.Event(), torch.cuda.Event()]
+
+        def upload(b):
+            with torch.cuda.stream(s_in):
+                s_in.wait_event(ev_free[b])          # the solve that last read buffer b has finished
+                xdb[b].copy_(xh, non_blocking=True)
+                ydb[b].copy_(yh, non_blocking=True)
+                ev_in[b].record(s_in)
+
+        def pipelined(nsteps):
+            s_in.wait_stream(cur)
+            s_out.wait_stream(cur)
+            upload(0)
+            for k in range(nsteps):
+                b = k & 1
+                if k + 1 < nsteps:
+                    upload(b ^ 1)                    # enqueued BEFORE solve(k): overlaps it
+                cur.wait_event(ev_in[b])
+                m = solve(xdb[b], ydb[b])
+                ev_free[b].record(cur)
+                with torch.cuda.stream(s_out):
+                    s_out.wait_event(ev_free[b])
+                    mhb[b].copy_(m, non_blocking=True)
+                    m.record_stream(s_out)
+            cur.wait_stream(s_in)
+            cur.wait_stream(s_out)
+
+        pipelined(2)
+        ms_e2e = timed(lambda: pipelined(args.steps))
         e2e = {"value": n_total / ms_e2e / 1e3, "unit": UNIT, "ms_per_step": ms_e2e,
                "h2d_bytes_per_step": (xh.numel() + yh.numel()) * 8 * world,
                "d2h_bytes_per_step": mh.numel() * 8 * world,
+               "mode": "double-buffered: H2D of step k+1 and D2H of step k overlap the solve of step k (3 streams); "
+                       "every step uploads its own inputs and downloads its own result inside the timed region",
+               "serial": {"value": n_total / ms_serial / 1e3, "ms_per_step": ms_serial,
+                          "mode": "copy in, solve, copy out back to back on one stream"},
                "api": "EFGPND(x, y, SquaredExponential, ...).predict(x, return_variance=False) on buffers copied "
                       "from pinned host memory; posterior mean copied back"}
 
@@ -377,6 +436,22 @@ def main():
                     "traffic": traffic, "peak_source": peak_src, "avg_launch_ms": v["ms"] / v["launches"],
                     "algorithmic_bytes_per_launch": algorithmic_bytes(top, v["units"]) / v["launches"],
                     "points_per_launch": v["units"] / v["launches"]}
+        fl = algorithmic_flops(top, v["units"])
+        if fl is not None:
+            # the spreading kernels are FP64-pipe bound, not HBM bound (ncu: FP64 pipe ~68 % busy, DRAM ~24 %):
+            # report the FP64 fraction against a DFMA peak measured on this device in this run
+            fp64_peak = _lib.measure_fp64_peak()
+            roofline["fp64"] = {"achieved": fl / v["ms"] / 1e9, "peak": fp64_peak, "unit": "TFLOP/s",
+                                "frac": fl / v["ms"] / 1e9 / fp64_peak, "flops_per_point": fl / v["units"],
+                                "peak_source": "measured in this run (efgp_measure_fp64_peak: pure DFMA kernel)"}
+        # the dominant kernel that IS bounded by HBM, for comparison
+        hbm_own = {k: w for k, w in own.items() if algorithmic_flops(k, 1) is None}
+        if hbm_own and top not in hbm_own:
+            t2 = max(hbm_own, key=lambda k: hbm_own[k]["ms"])
+            a2 = algorithmic_bytes(t2, hbm_own[t2]["units"]) / hbm_own[t2]["ms"] / 1e6
+            roofline["dominant_hbm_bound_kernel"] = {"kernel": t2, "achieved": a2, "peak": peak, "unit": "GB/s",
+                                                      "frac": a2 / peak,
+                                                      "avg_launch_ms": hbm_own[t2]["ms"] / hbm_own[t2]["launches"]}
     launches = sum(v["launches"] for v in stages.values())
 
     line = {"metric": METRIC, "value": n_total / ms / 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -50,6 +50,61 @@ int efgp_pool_trim(void) {
   EFGP_TRY({ efgp::pool_trim(); })
 }
 
+// FP64 FMA throughput of this device, measured: 16 independent DFMA chains per thread, 8 warps x 8 CTAs per SM.
+// The roofline denominator of the FP64-pipe-bound spreading kernels (bench.py); not used on the product path.
+namespace {
+__global__ void __launch_bounds__(256) fp64_peak_kernel(double* out, int iters, double seed) {
+  double a[16];
+#pragma unroll
+  for (int q = 0; q < 16; ++q) a[q] = seed + q + threadIdx.x;
+  const double m = 1.0000001, c = 1e-9;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int q = 0; q < 16; ++q) a[q] = fma(a[q], m, c);
+  }
+  double s = 0;
+#pragma unroll
+  for (int q = 0; q < 16; ++q) s += a[q];
+  if (s == 12345.678) out[0] = s;   // never true: keeps the chains alive
+}
+}  // namespace
+
+static double measure_fp64_peak(cudaStream_t st) {
+  int dev = 0;
+  int sms = 0;
+  EFGP_CUDA(cudaGetDevice(&dev));
+  EFGP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  double* d = (double*)efgp::pool_alloc(sizeof(double));
+  cudaEvent_t e0;
+  cudaEvent_t e1;
+  EFGP_CUDA(cudaEventCreate(&e0));
+  EFGP_CUDA(cudaEventCreate(&e1));
+  const int iters = 8192;
+  const int blocks = sms * 8;
+  double best = 0;
+  for (int r = 0; r < 4; ++r) {
+    EFGP_CUDA(cudaEventRecord(e0, st));
+    fp64_peak_kernel<<<blocks, 256, 0, st>>>(d, iters, 1.0 + r);
+    EFGP_CUDA(cudaEventRecord(e1, st));
+    EFGP_CUDA(cudaEventSynchronize(e1));
+    float ms = 0;
+    EFGP_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    double tf = 2.0 * 16.0 * iters * 256.0 * blocks / (ms * 1e-3) * 1e-12;
+    if (r > 0 && tf > best) best = tf;
+  }
+  EFGP_CUDA(cudaEventDestroy(e0));
+  EFGP_CUDA(cudaEventDestroy(e1));
+  efgp::pool_free(d);
+  return best;
+}
+
+int efgp_measure_fp64_peak(double* tflops, void* stream) {
+  EFGP_TRY({
+    EFGP_CHECK(tflops != nullptr, "null output");
+    *tflops = measure_fp64_peak((cudaStream_t)stream);
+  })
+}
+
 int efgp_nufft_create(efgp_nufft** out, int dim, int dtype) {
   EFGP_TRY({
     EFGP_CHECK(out != nullptr, "null output handle");

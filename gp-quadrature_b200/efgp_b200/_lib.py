@@ -22,6 +22,7 @@ _SIGNATURES = {
     "efgp_timing_enable": (ctypes.c_int, [ctypes.c_int]),
     "efgp_timing_report": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_int64]),
     "efgp_pool_trim": (ctypes.c_int, []),
+    "efgp_measure_fp64_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.c_void_p]),
     "efgp_nufft_create": (ctypes.c_int, [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_int]),
     "efgp_nufft_set_points": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_double, c_dblp, vp]),
     "efgp_nufft_destroy": (None, [vp]),
@@ -94,3 +95,10 @@ def timing_report():
         name, scopes, launches, units, ms = line.rsplit(",", 4)
         out[name] = {"scopes": int(scopes), "launches": int(launches), "units": int(units), "ms": float(ms)}
     return out
+
+
+def measure_fp64_peak(stream=None):
+    """Measured FP64 FMA throughput of the current device in TFLOP/s (diagnostic for bench.py)."""
+    out = ctypes.c_double(0.0)
+    check(lib().efgp_measure_fp64_peak(ctypes.byref(out), ctypes.c_void_p(stream or 0)))
+    return float(out.value)

@@ -32,10 +32,13 @@ const char* efgp_last_error(void);
 /* ---- diagnostics (no reference counterpart; the reference's torch.profiler ranges, efgpnd.py:46-59).
  * efgp_timing_enable(1) starts recording CUDA events around every launch group the library issues;
  * efgp_timing_report writes "stage,scopes,launches,units,total_ms\n" lines (synchronises the device).
- * efgp_pool_trim releases the cached device scratch blocks. */
+ * efgp_pool_trim releases the cached device scratch blocks.
+ * efgp_measure_fp64_peak times a pure DFMA kernel: the FP64 roofline denominator bench.py reports for the
+ * FP64-pipe-bound spreading kernels (MEASURED_PEAKS.json only holds HBM and bf16 peaks). */
 int efgp_timing_enable(int on);
 int efgp_timing_report(char* buf, int64_t cap);
 int efgp_pool_trim(void);
+int efgp_measure_fp64_peak(double* tflops, void* stream);
 
 /* ---- NUFFT: replaces class NUFFT (efgpnd.py:1423-1549) and the pytorch_finufft calls under it */
 
