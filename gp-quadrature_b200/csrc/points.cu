@@ -96,12 +96,24 @@ __device__ __forceinline__ T fold_coord(T xv, T h, T xc, T nf, T shift, int inf)
 // tile are consecutive after the sort: the 3-D spread / interp kernels stage one tile (+ halo) of the fine
 // grid in shared memory at a time (spread.cu, interp.cu).
 template <typename T, int D>
+__device__ __forceinline__ uint32_t fold_values(const T* xv, const FoldParams<T>& p, T* X);
+
+template <typename T, int D>
 __device__ __forceinline__ uint32_t fold_point(const T* __restrict__ x, int64_t i, const FoldParams<T>& p, T* X) {
+  T xv[D];
+#pragma unroll
+  for (int a = 0; a < D; ++a) xv[a] = x[i * D + a];
+  return fold_values<T, D>(xv, p, X);
+}
+
+// xv may alias X
+template <typename T, int D>
+__device__ __forceinline__ uint32_t fold_values(const T* xv, const FoldParams<T>& p, T* X) {
   uint32_t key = 0;
   int c[D];
 #pragma unroll
   for (int a = 0; a < D; ++a) {
-    X[a] = fold_coord(x[i * D + a], p.h, p.xcen[a], p.nf[a], p.shift, p.inf[a]);
+    X[a] = fold_coord(xv[a], p.h, p.xcen[a], p.nf[a], p.shift, p.inf[a]);
     c[a] = (int)X[a];
     key = key * (uint32_t)p.inf[a] + (uint32_t)c[a];
   }
@@ -662,12 +674,16 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
       attr_set = true;
     }
-    if (ypay)
+    // (A persistent variant that prefetched the next tile's inputs during the write-out was measured slower:
+    // 1.81 vs 1.31 ms at N = 1e8 -- three independent CTAs per SM overlap the phases better than one CTA's
+    // software pipeline.)
+    if (ypay) {
       bucket_scatter_kernel<T, D, D + 1><<<ntiles1, kL1Threads, smem, st>>>(
           x, ypay, N, p, g, ntiles1, tileStart, R[0], R[1], RY, nullptr, K2, sp.A);   // D == 2: word 2 = payload
-    else
+    } else {
       bucket_scatter_kernel<T, D, D><<<ntiles1, kL1Threads, smem, st>>>(x, nullptr, N, p, g, ntiles1, tileStart,
                                                                           R[0], R[1], R[2], nullptr, K2, sp.A);
+    }
   }
   const int ntiles2_max = ntiles1 + g.nb1;
   {
