@@ -1,0 +1,38 @@
+"""Small GPU checks of the pieces around the hot path: diagnostics entry points and the predict() return contract."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def test_fp64_peak_probe_is_plausible():
+    from efgp_b200 import _lib
+    tf = _lib.measure_fp64_peak()
+    assert 1.0 < tf < 200.0          # B200: ~37 TFLOP/s DFMA
+
+
+def test_predict_without_variance_returns_nan_vector_like_reference():
+    """efgpnd.py:946-948: var is a (B,) tensor of NaN when return_variance=False."""
+    import efgpnd
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.rand(4000, 2, dtype=torch.float64, device="cuda", generator=g)
+    y = torch.sin(4 * x[:, 0]) + 0.1 * torch.randn(4000, dtype=torch.float64, device="cuda", generator=g)
+    m = efgpnd.EFGPND(x, y, "SE", sigmasq=0.05, eps=1e-3, estimate_params=False)
+    xn = x[:100]
+    mean, var = m.predict(xn, return_variance=False)
+    assert mean.shape == (100,) and var.shape == (100,)
+    assert var.dtype == x.dtype and var.device == x.device
+    assert bool(torch.isnan(var).all())
+    assert bool(torch.isfinite(mean).all())
+
+
+def test_timing_report_counts_points():
+    from efgp_b200 import _lib, ops
+    x = torch.rand(50_000, 2, dtype=torch.float64, device="cuda")
+    _lib.timing_enable(True)
+    plan = ops.NufftPlan(x, 0.4)
+    plan.type1(torch.ones(50_000, dtype=torch.float64, device="cuda"), (21, 21), 1e-6)
+    rep = _lib.timing_report()
+    _lib.timing_enable(False)
+    assert rep["sort.bucket_hist_kernel"]["units"] == 50_000
+    assert any(k.startswith("spread2d_") and v["units"] == 50_000 for k, v in rep.items())
