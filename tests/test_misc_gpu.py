@@ -17,7 +17,11 @@ def test_predict_without_variance_returns_nan_vector_like_reference():
     g = torch.Generator(device="cuda").manual_seed(3)
     x = torch.rand(4000, 2, dtype=torch.float64, device="cuda", generator=g)
     y = torch.sin(4 * x[:, 0]) + 0.1 * torch.randn(4000, dtype=torch.float64, device="cuda", generator=g)
-    m = efgpnd.EFGPND(x, y, "SE", sigmasq=0.05, eps=1e-3, estimate_params=False)
+    from kernels import SquaredExponential
+    # (a kernel given by NAME has NaN hyperparameters until estimated, in the reference as here:
+    #  kernels/squared_exponential.py:23-24 default init_lengthscale / init_variance to NaN)
+    k = SquaredExponential(dimension=2, init_lengthscale=0.2, init_variance=1.0)
+    m = efgpnd.EFGPND(x, y, k, sigmasq=0.05, eps=1e-3, estimate_params=False)
     xn = x[:100]
     mean, var = m.predict(xn, return_variance=False)
     assert mean.shape == (100,) and var.shape == (100,)
