@@ -10,10 +10,10 @@
 // 4.2 ms for the scattered type-2 result), and an LSD radix sort on (key, index) needs three more passes.
 // Here the permutation is factored into two stages that are each sector-efficient:
 //
-//   level 1  original order -> <= 256 coarse buckets (contiguous cell ranges = bands of grid rows).
+//   level 1  original order -> 128 (<= 256) coarse buckets (contiguous cell ranges = bands of grid rows).
 //            One CTA bucket-sorts a tile of 2048 points in shared memory and writes each bucket's
 //            run contiguously, so DRAM sees full sectors.  A[i] = level-1 position of point i.
-//   level 2  inside a bucket (N/256 points: a few MB, L2 resident) a counting sort by cell places the
+//   level 2  inside a bucket (N/128 points: a few MB, L2 resident) a counting sort by cell places the
 //            points in their final slots.  Binv[slot] = level-1 position of the point in that slot.
 //
 // Later transforms move per-point data through the same two stages: strengths c[i] -> tmp[A[i]]
