@@ -18,6 +18,7 @@
 // partials of its row, so no separate scalar kernels and no atomics on the critical path.
 // Converged rows are skipped by all kernels via a double-buffered per-row flag.
 #include "toeplitz.cuh"
+#include <cstdlib>
 
 namespace efgp {
 
@@ -287,6 +288,231 @@ cg_C_kernel(typename cplx_of<T>::type* __restrict__ x, typename cplx_of<T>::type
   }
 }
 
+// ------------------------------------------------------------------ tiny 2-D blocks: matvec by direct DFTs
+// For the posterior-mean system the block is tiny (71 x 71 unknowns, 144 x 144 embedding at the headline size):
+// the cuFFT pair is 4 launches of ~3 us each and the iteration is bound by launch latency, not by work.  A
+// zero-padded, cropped 2-D transform written as plain DFT sums costs 2 n0 n1 F1 + 2 F0 F1 n0 complex MACs
+// (4.4e6 here: about a microsecond of FP64), needs no padded buffer, and fuses with the vector updates, so an
+// iteration is 4 launches (D1, D2, D3, C) instead of 8:
+//   D1  rows   : beta, p = M^-1 r + beta p,   U[j0, k1] = sum_j1 ws p[j0, j1] w1^(k1 j1)
+//   D2  columns: V[k0] = sum_j0 U[j0, k1] w0^(k0 j0);  V *= vhat[k0, k1];  X[i0, k1] = sum_k0 V[k0] w0^-(k0 (i0 + n0 - 1))
+//   D3  rows   : Y[i0, i1] = sum_k1 X[i0, k1] w1^-(k1 (i1 + n1 - 1));  Ap = c1 ws Y + c2 p,  partial <p, Ap>
+// with w = exp(-2 pi i / F): the same unnormalised transforms cuFFT computes, so the cached vhat (pre-scaled by
+// 1 / Ftot) is shared with the FFT path.  Chunks of the reductions are the block's rows (NC = n0, len = n1).
+template <typename C>
+__device__ __forceinline__ C cmul(C a, C b) {
+  C o;
+  o.x = a.x * b.x - a.y * b.y;
+  o.y = a.x * b.y + a.y * b.x;
+  return o;
+}
+template <typename C>
+__device__ __forceinline__ void cmac(C& acc, C a, C b) {   // acc += a * b
+  acc.x = fma(a.x, b.x, acc.x);
+  acc.x = fma(-a.y, b.y, acc.x);
+  acc.y = fma(a.x, b.y, acc.y);
+  acc.y = fma(a.y, b.x, acc.y);
+}
+template <typename C>
+__device__ __forceinline__ void cmac_conj(C& acc, C a, C b) {   // acc += a * conj(b)
+  acc.x = fma(a.x, b.x, acc.x);
+  acc.x = fma(a.y, b.y, acc.x);
+  acc.y = fma(a.y, b.x, acc.y);
+  acc.y = fma(-a.x, b.y, acc.y);
+}
+
+// One output of a DFT sum, split over G = 4 adjacent lanes (terms j = g, g + 4, ...) with two independent
+// accumulators per lane, then combined with two shuffles: sum_j data[j] * tw[(j * step) mod F] (or its conjugate
+// twiddle).  Every lane of the warp must call it (the shuffles are full-mask); lanes of one group get the sum.
+constexpr int kDftG = 4;
+template <typename C, bool CONJ>
+__device__ __forceinline__ C dft_sum4(const C* __restrict__ data, int nterms, const C* __restrict__ tw, int F, int step) {
+  const int g = threadIdx.x & (kDftG - 1);
+  C a0, a1;
+  a0.x = a0.y = a1.x = a1.y = 0;
+  int idx = (g * step) % F;
+  const int d1 = (kDftG * step) % F;
+  int j = g;
+  for (; j + kDftG < nterms; j += 2 * kDftG) {
+    int idx2 = idx + d1;
+    if (idx2 >= F) idx2 -= F;
+    if (CONJ) {
+      cmac_conj(a0, data[j], tw[idx]);
+      cmac_conj(a1, data[j + kDftG], tw[idx2]);
+    } else {
+      cmac(a0, data[j], tw[idx]);
+      cmac(a1, data[j + kDftG], tw[idx2]);
+    }
+    idx = idx2 + d1;
+    if (idx >= F) idx -= F;
+  }
+  if (j < nterms) {
+    if (CONJ) cmac_conj(a0, data[j], tw[idx]); else cmac(a0, data[j], tw[idx]);
+  }
+  a0.x += a1.x;
+  a0.y += a1.y;
+#pragma unroll
+  for (int o = 1; o < kDftG; o <<= 1) {
+    a0.x += __shfl_xor_sync(0xffffffffu, a0.x, o);
+    a0.y += __shfl_xor_sync(0xffffffffu, a0.y, o);
+  }
+  return a0;
+}
+
+template <typename T>
+__global__ void dft_twiddle_kernel(typename cplx_of<T>::type* tw, int F) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= F) return;
+  double sn, cs;
+  sincospi(-2.0 * (double)k / (double)F, &sn, &cs);
+  tw[k].x = (T)cs;
+  tw[k].y = (T)sn;
+}
+
+constexpr int kDftMaxF = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+cg_D1_kernel(typename cplx_of<T>::type* __restrict__ p, const typename cplx_of<T>::type* __restrict__ r,
+             const T* __restrict__ minv, const T* __restrict__ ws, int n1, int F1, int it, double tol, int early,
+             int batched, const typename cplx_of<T>::type* __restrict__ tw1g, typename cplx_of<T>::type* __restrict__ U,
+             CgScal s) {
+  using C = typename cplx_of<T>::type;
+  __shared__ C zrow[kDftMaxF];
+  __shared__ C tw1[kDftMaxF];
+  const int row = blockIdx.y, c = blockIdx.x, n0 = gridDim.x;
+  const int cur = it & 1, prev = cur ^ 1;
+  if (!s.act[prev * s.B + row]) {
+    if (c == 0 && threadIdx.x == 0) s.act[cur * s.B + row] = 0;
+    return;
+  }
+  double beta = 0;
+  if (it > 0) {
+    double rz_new;
+    bool conv = row_converged(s, row, tol, early, batched, rz_new);
+    if (conv) {
+      if (c == 0 && threadIdx.x == 0) {
+        s.act[cur * s.B + row] = 0;
+        s.conv_iter[row] = it - 1;
+        atomicSub(&s.counters[0], 1);
+        atomicMax(&s.counters[1], it - 1);
+      }
+      return;
+    }
+    beta = rz_new / (s.rz[prev * s.B + row] + 1e-16);
+    if (c == 0 && threadIdx.x == 0) {
+      s.rz[cur * s.B + row] = rz_new;
+      s.act[cur * s.B + row] = 1;
+    }
+  } else if (c == 0 && threadIdx.x == 0) {
+    s.rz[cur * s.B + row] = s.rz[prev * s.B + row];
+    s.act[cur * s.B + row] = 1;
+  }
+  const int64_t M = (int64_t)n0 * n1;
+  const T bt = (T)beta;
+  for (int j = threadIdx.x; j < F1; j += blockDim.x) tw1[j] = tw1g[j];
+  for (int j1 = threadIdx.x; j1 < n1; j1 += blockDim.x) {
+    const int64_t k = (int64_t)c * n1 + j1, i = (int64_t)row * M + k;
+    C pv = p[i];
+    if (it > 0) {
+      C rv = r[i];
+      T mi = minv ? minv[k] : T(1);
+      pv.x = rv.x * mi + bt * pv.x;
+      pv.y = rv.y * mi + bt * pv.y;
+      p[i] = pv;
+    }
+    T w = ws ? ws[k] : T(1);
+    C o;
+    o.x = pv.x * w;
+    o.y = pv.y * w;
+    zrow[j1] = o;
+  }
+  __syncthreads();
+  C* Urow = U + ((int64_t)row * n0 + c) * F1;
+  const int per_pass = blockDim.x / kDftG;
+  for (int base = 0; base < F1; base += per_pass) {          // uniform trip count: full-mask shuffles inside
+    const int k1 = base + (int)(threadIdx.x / kDftG);
+    const C acc = dft_sum4<C, false>(zrow, k1 < F1 ? n1 : 0, tw1, F1, k1 < F1 ? k1 : 0);
+    if (k1 < F1 && (threadIdx.x & (kDftG - 1)) == 0) Urow[k1] = acc;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+cg_D2_kernel(const typename cplx_of<T>::type* __restrict__ U, const typename cplx_of<T>::type* __restrict__ vhat,
+             int n0, int F0, int F1, const typename cplx_of<T>::type* __restrict__ tw0g,
+             typename cplx_of<T>::type* __restrict__ X, const int* __restrict__ act) {
+  using C = typename cplx_of<T>::type;
+  __shared__ C ucol[kDftMaxF];
+  __shared__ C vcol[kDftMaxF];
+  __shared__ C tw0[kDftMaxF];
+  const int row = blockIdx.y, k1 = blockIdx.x;
+  if (!act[row]) return;
+  for (int j = threadIdx.x; j < F0; j += blockDim.x) tw0[j] = tw0g[j];
+  for (int j0 = threadIdx.x; j0 < n0; j0 += blockDim.x) ucol[j0] = U[((int64_t)row * n0 + j0) * F1 + k1];
+  __syncthreads();
+  const int per_pass = blockDim.x / kDftG, og = threadIdx.x / kDftG;
+  const bool lead = (threadIdx.x & (kDftG - 1)) == 0;
+  for (int base = 0; base < F0; base += per_pass) {
+    const int k0 = base + og;
+    C h;
+    h.x = h.y = 0;
+    if (k0 < F0 && lead) h = vhat[(int64_t)k0 * F1 + k1];     // in flight during the sum
+    const C acc = dft_sum4<C, false>(ucol, k0 < F0 ? n0 : 0, tw0, F0, k0 < F0 ? k0 : 0);
+    if (k0 < F0 && lead) vcol[k0] = cmul(acc, h);
+  }
+  __syncthreads();
+  for (int base = 0; base < n0; base += per_pass) {
+    const int i0 = base + og;
+    const C acc = dft_sum4<C, true>(vcol, i0 < n0 ? F0 : 0, tw0, F0, i0 < n0 ? (i0 + n0 - 1) % F0 : 0);
+    if (i0 < n0 && lead) X[((int64_t)row * n0 + i0) * F1 + k1] = acc;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+cg_D3_kernel(const typename cplx_of<T>::type* __restrict__ X, const typename cplx_of<T>::type* __restrict__ p,
+             const T* __restrict__ ws, int n1, int F1, T c1, T c2, int it,
+             const typename cplx_of<T>::type* __restrict__ tw1g, typename cplx_of<T>::type* __restrict__ Ap, CgScal s) {
+  using C = typename cplx_of<T>::type;
+  __shared__ C xrow[kDftMaxF];
+  __shared__ C tw1[kDftMaxF];
+  __shared__ double sh[8];
+  const int row = blockIdx.y, c = blockIdx.x, n0 = gridDim.x;
+  if (!s.act[(it & 1) * s.B + row]) return;
+  const int64_t M = (int64_t)n0 * n1;
+  for (int j = threadIdx.x; j < F1; j += blockDim.x) {
+    tw1[j] = tw1g[j];
+    xrow[j] = X[((int64_t)row * n0 + c) * F1 + j];
+  }
+  __syncthreads();
+  double dot = 0;
+  const int per_pass = blockDim.x / kDftG, og = threadIdx.x / kDftG;
+  const bool lead = (threadIdx.x & (kDftG - 1)) == 0;
+  for (int base = 0; base < n1; base += per_pass) {
+    const int i1 = base + og;
+    const bool on = i1 < n1 && lead;
+    const int64_t k = (int64_t)c * n1 + (i1 < n1 ? i1 : 0), i = (int64_t)row * M + k;
+    C pv;
+    pv.x = pv.y = 0;
+    T w = c1;
+    if (on) {                                                  // in flight during the sum
+      pv = p[i];
+      if (ws) w = ws[k] * c1;
+    }
+    const C acc = dft_sum4<C, true>(xrow, i1 < n1 ? F1 : 0, tw1, F1, i1 < n1 ? (i1 + n1 - 1) % F1 : 0);
+    if (on) {
+      C o;
+      o.x = acc.x * w + c2 * pv.x;
+      o.y = acc.y * w + c2 * pv.y;
+      Ap[i] = o;
+      dot += (double)pv.x * o.x + (double)pv.y * o.y;
+    }
+  }
+  double tsum = block_sum(dot, sh);
+  if (threadIdx.x == 0) s.p_pAp[row * s.NC + c] = tsum;
+}
+
 // After `it` iterations: register rows that converged in iteration it-1.
 __global__ void __launch_bounds__(256) cg_final_kernel(int it, double tol, int early, int batched, CgScal s) {
   const int row = blockIdx.x;           // one block per row
@@ -333,6 +559,26 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   s.B = B;
   s.NC = (int)std::min<int64_t>(kMaxChunks, std::max<int64_t>(1, (M + kChunkLen - 1) / kChunkLen));
   s.len = (M + s.NC - 1) / s.NC;
+  // tiny 2-D blocks with few right-hand sides: direct-DFT matvec, 4 launches per iteration (see cg_D1_kernel)
+  static const bool dft_off = std::getenv("EFGP_CG_FFT") != nullptr;     // A/B switch: force the cuFFT path
+  const bool direct = !dft_off && t.dim == 2 && B <= 4 && t.F[0] <= kDftMaxF && t.F[1] <= kDftMaxF &&
+                      t.n[0] <= kMaxChunks;
+  const int n0 = (int)t.n[0], n1 = (int)t.n[1], F0 = (int)t.F[0], F1 = (int)t.F[1];
+  C *tw0 = nullptr, *tw1 = nullptr, *U = nullptr, *X = nullptr;
+  if (direct) {
+    s.NC = n0;            // reduction chunks = rows of the block
+    s.len = n1;
+    const bool fresh = t.dft_tw.p == nullptr;
+    tw0 = (C*)t.dft_tw.get(((size_t)F0 + F1) * sizeof(C));
+    tw1 = tw0 + F0;
+    U = (C*)t.dft.get((size_t)2 * B * n0 * F1 * sizeof(C));
+    X = U + (size_t)B * n0 * F1;
+    if (fresh || !t.dft_ready) {
+      dft_twiddle_kernel<T><<<div_up(F0, 128), 128, 0, st>>>(tw0, F0);
+      dft_twiddle_kernel<T><<<div_up(F1, 128), 128, 0, st>>>(tw1, F1);
+      t.dft_ready = true;
+    }
+  }
   size_t nd = (size_t)2 * B + B + (size_t)3 * B * s.NC;
   size_t ni = (size_t)2 * B + B + 4;
   char* sc = (char*)t.cg_scal.get(nd * sizeof(double) + ni * sizeof(int));
@@ -384,6 +630,12 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   while (it < max_iter) {
     int until = std::min(max_iter, it + check);
     stg.add_launches(4 * (until - it));
+    for (; direct && it < until; ++it) {
+      cg_D1_kernel<T><<<grid, 256, 0, st>>>(p, r, minv, w, n1, F1, it, tol, early, batched, tw1, U, s);
+      cg_D2_kernel<T><<<dim3(F1, B), 256, 0, st>>>(U, (const C*)t.vhat, n0, F0, F1, tw0, X, s.act + (it & 1) * B);
+      cg_D3_kernel<T><<<grid, 256, 0, st>>>(X, p, w, n1, F1, c1, c2, it, tw1, Ap, s);
+      cg_C_kernel<T><<<grid, 256, 0, st>>>(x, r, p, Ap, minv, M, it, s);
+    }
     for (; it < until; ++it) {
       cg_A_kernel<T><<<grid, 256, 0, st>>>(p, r, minv, w, g, it, tol, early, batched, P, s);
       fft_pair_begin<T>(t, B, P, Q, st);

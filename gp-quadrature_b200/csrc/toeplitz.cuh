@@ -15,6 +15,8 @@ struct Toeplitz {
   DevBuf P, Q;                      // padded input (zeros persist), spectrum / output
   int64_t P_rows = 0;               // rows of P known to be zero outside the block
   DevBuf cg_vec, cg_scal;
+  DevBuf dft_tw, dft;               // direct-DFT CG path (cg.cu): twiddle tables, U / X scratch
+  bool dft_ready = false;           // twiddles written
   ~Toeplitz();
 };
 

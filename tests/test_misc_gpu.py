@@ -40,3 +40,31 @@ def test_timing_report_counts_points():
     _lib.timing_enable(False)
     assert rep["sort.bucket_hist_kernel"]["units"] == 50_000
     assert any(k.startswith("spread2d_") and v["units"] == 50_000 for k, v in rep.items())
+
+
+@pytest.mark.parametrize("dt,tol", [(torch.float64, 1e-9), (torch.float32, 2e-3)])
+def test_direct_dft_cg_matches_fft_cg_on_rectangular_block(dt, tol):
+    """cg.cu solves tiny 2-D blocks with <= 4 right-hand sides through direct DFT sums (4 launches per iteration)
+    and everything else through cuFFT: the same rectangular system solved both ways (1 row vs the same row
+    repeated 5 times) must agree."""
+    from efgp_b200 import ops
+    cdt = torch.complex128 if dt == torch.float64 else torch.complex64
+    g = torch.Generator(device="cuda").manual_seed(11)
+    n0, n1 = 9, 14
+    x = torch.rand(3000, 2, dtype=dt, device="cuda", generator=g)
+    v = ops.NufftPlan(x, 0.7).type1(None, (2 * n0 - 1, 2 * n1 - 1), 1e-12 if dt == torch.float64 else 1e-6)
+    T = ops.ToeplitzPlan(v.to(cdt), force_pow2=False)
+    M = n0 * n1
+    ws = (0.02 + torch.rand(M, dtype=dt, device="cuda", generator=g)) / 30
+    b = torch.randn(M, dtype=dt, device="cuda", generator=g) + 1j * torch.randn(M, dtype=dt, device="cuda", generator=g)
+    b = b.to(cdt)
+    cg_tol = 1e-10 if dt == torch.float64 else 1e-5
+    x1, it1 = T.cg(b, torch.zeros_like(b), ops.MODE_A_MEAN, ws, 0.5, cg_tol, max_iter=500, batched=False)
+    b5 = b.repeat(5, 1)
+    x5, it5 = T.cg(b5, torch.zeros_like(b5), ops.MODE_A_MEAN, ws, 0.5, cg_tol, max_iter=500, batched=False)
+    assert it1 < 500 and it5 < 500
+    for r in range(5):
+        assert float(torch.linalg.norm(x5[r] - x1) / torch.linalg.norm(x1)) < tol
+    # and the solution really solves the system
+    res = T.apply(x1, ops.MODE_A_MEAN, ws, 0.5) - b
+    assert float(torch.linalg.norm(res) / torch.linalg.norm(b)) < 50 * cg_tol
