@@ -19,6 +19,7 @@
 // Converged rows are skipped by all kernels via a double-buffered per-row flag.
 #include "toeplitz.cuh"
 #include <cstdlib>
+#include <cooperative_groups.h>
 
 namespace efgp {
 
@@ -255,13 +256,12 @@ cg_B_kernel(const typename cplx_of<T>::type* __restrict__ Q, const typename cplx
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256)
-cg_C_kernel(typename cplx_of<T>::type* __restrict__ x, typename cplx_of<T>::type* __restrict__ r,
-            const typename cplx_of<T>::type* __restrict__ p, const typename cplx_of<T>::type* __restrict__ Ap,
-            const T* __restrict__ minv, int64_t M, int it, CgScal s) {
+__device__ __forceinline__ void cg_C_body(typename cplx_of<T>::type* __restrict__ x, typename cplx_of<T>::type* __restrict__ r,
+                                          const typename cplx_of<T>::type* __restrict__ p,
+                                          const typename cplx_of<T>::type* __restrict__ Ap, const T* __restrict__ minv,
+                                          int64_t M, int it, const CgScal& s, int row, int c) {
   using C = typename cplx_of<T>::type;
   __shared__ double sh[8];
-  int row = blockIdx.y, c = blockIdx.x;
   if (!s.act[(it & 1) * s.B + row]) return;
   double pAp = sum_partials(s.p_pAp + row * s.NC, s.NC) + 1e-16;
   const T alpha = (T)(s.rz[(it & 1) * s.B + row] / pAp);
@@ -286,6 +286,14 @@ cg_C_kernel(typename cplx_of<T>::type* __restrict__ x, typename cplx_of<T>::type
     s.p_rr[row * s.NC + c] = t1;
     s.p_rz[row * s.NC + c] = t2;
   }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+cg_C_kernel(typename cplx_of<T>::type* __restrict__ x, typename cplx_of<T>::type* __restrict__ r,
+            const typename cplx_of<T>::type* __restrict__ p, const typename cplx_of<T>::type* __restrict__ Ap,
+            const T* __restrict__ minv, int64_t M, int it, CgScal s) {
+  cg_C_body<T>(x, r, p, Ap, minv, M, it, s, blockIdx.y, blockIdx.x);
 }
 
 // ------------------------------------------------------------------ tiny 2-D blocks: matvec by direct DFTs
@@ -371,20 +379,22 @@ __global__ void dft_twiddle_kernel(typename cplx_of<T>::type* tw, int F) {
 
 constexpr int kDftMaxF = 256;
 
+// Returns whether `row` is still active in iteration `it` (the same answer in every CTA that asks: the decision
+// only reads the reduced scalars of iteration it - 1).  CTA c = 0 records the decision; CTAs with c >= n0 (the
+// persistent kernel has more CTAs than block rows) only decide.
 template <typename T>
-__global__ void __launch_bounds__(256)
-cg_D1_kernel(typename cplx_of<T>::type* __restrict__ p, const typename cplx_of<T>::type* __restrict__ r,
-             const T* __restrict__ minv, const T* __restrict__ ws, int n1, int F1, int it, double tol, int early,
-             int batched, const typename cplx_of<T>::type* __restrict__ tw1g, typename cplx_of<T>::type* __restrict__ U,
-             CgScal s) {
+__device__ __forceinline__ bool cg_D1_body(typename cplx_of<T>::type* __restrict__ p,
+                                           const typename cplx_of<T>::type* __restrict__ r, const T* __restrict__ minv,
+                                           const T* __restrict__ ws, int n0, int n1, int F1, int it, double tol, int early,
+                                           int batched, const typename cplx_of<T>::type* __restrict__ tw1g,
+                                           typename cplx_of<T>::type* __restrict__ U, const CgScal& s, int row, int c) {
   using C = typename cplx_of<T>::type;
   __shared__ C zrow[kDftMaxF];
   __shared__ C tw1[kDftMaxF];
-  const int row = blockIdx.y, c = blockIdx.x, n0 = gridDim.x;
   const int cur = it & 1, prev = cur ^ 1;
   if (!s.act[prev * s.B + row]) {
     if (c == 0 && threadIdx.x == 0) s.act[cur * s.B + row] = 0;
-    return;
+    return false;
   }
   double beta = 0;
   if (it > 0) {
@@ -397,7 +407,7 @@ cg_D1_kernel(typename cplx_of<T>::type* __restrict__ p, const typename cplx_of<T
         atomicSub(&s.counters[0], 1);
         atomicMax(&s.counters[1], it - 1);
       }
-      return;
+      return false;
     }
     beta = rz_new / (s.rz[prev * s.B + row] + 1e-16);
     if (c == 0 && threadIdx.x == 0) {
@@ -408,8 +418,10 @@ cg_D1_kernel(typename cplx_of<T>::type* __restrict__ p, const typename cplx_of<T
     s.rz[cur * s.B + row] = s.rz[prev * s.B + row];
     s.act[cur * s.B + row] = 1;
   }
+  if (c >= n0) return true;
   const int64_t M = (int64_t)n0 * n1;
   const T bt = (T)beta;
+  __syncthreads();            // (persistent kernel) the previous use of zrow / tw1 by this CTA is over
   for (int j = threadIdx.x; j < F1; j += blockDim.x) tw1[j] = tw1g[j];
   for (int j1 = threadIdx.x; j1 < n1; j1 += blockDim.x) {
     const int64_t k = (int64_t)c * n1 + j1, i = (int64_t)row * M + k;
@@ -435,19 +447,30 @@ cg_D1_kernel(typename cplx_of<T>::type* __restrict__ p, const typename cplx_of<T
     const C acc = dft_sum4<C, false>(zrow, k1 < F1 ? n1 : 0, tw1, F1, k1 < F1 ? k1 : 0);
     if (k1 < F1 && (threadIdx.x & (kDftG - 1)) == 0) Urow[k1] = acc;
   }
+  return true;
 }
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-cg_D2_kernel(const typename cplx_of<T>::type* __restrict__ U, const typename cplx_of<T>::type* __restrict__ vhat,
-             int n0, int F0, int F1, const typename cplx_of<T>::type* __restrict__ tw0g,
-             typename cplx_of<T>::type* __restrict__ X, const int* __restrict__ act) {
+cg_D1_kernel(typename cplx_of<T>::type* __restrict__ p, const typename cplx_of<T>::type* __restrict__ r,
+             const T* __restrict__ minv, const T* __restrict__ ws, int n1, int F1, int it, double tol, int early,
+             int batched, const typename cplx_of<T>::type* __restrict__ tw1g, typename cplx_of<T>::type* __restrict__ U,
+             CgScal s) {
+  cg_D1_body<T>(p, r, minv, ws, gridDim.x, n1, F1, it, tol, early, batched, tw1g, U, s, blockIdx.y, blockIdx.x);
+}
+
+template <typename T>
+__device__ __forceinline__ void cg_D2_body(const typename cplx_of<T>::type* __restrict__ U,
+                                           const typename cplx_of<T>::type* __restrict__ vhat, int n0, int F0, int F1,
+                                           const typename cplx_of<T>::type* __restrict__ tw0g,
+                                           typename cplx_of<T>::type* __restrict__ X, const int* __restrict__ act,
+                                           int row, int k1) {
   using C = typename cplx_of<T>::type;
   __shared__ C ucol[kDftMaxF];
   __shared__ C vcol[kDftMaxF];
   __shared__ C tw0[kDftMaxF];
-  const int row = blockIdx.y, k1 = blockIdx.x;
   if (!act[row]) return;
+  __syncthreads();            // (persistent kernel) the previous use of the shared columns by this CTA is over
   for (int j = threadIdx.x; j < F0; j += blockDim.x) tw0[j] = tw0g[j];
   for (int j0 = threadIdx.x; j0 < n0; j0 += blockDim.x) ucol[j0] = U[((int64_t)row * n0 + j0) * F1 + k1];
   __syncthreads();
@@ -471,16 +494,25 @@ cg_D2_kernel(const typename cplx_of<T>::type* __restrict__ U, const typename cpl
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-cg_D3_kernel(const typename cplx_of<T>::type* __restrict__ X, const typename cplx_of<T>::type* __restrict__ p,
-             const T* __restrict__ ws, int n1, int F1, T c1, T c2, int it,
-             const typename cplx_of<T>::type* __restrict__ tw1g, typename cplx_of<T>::type* __restrict__ Ap, CgScal s) {
+cg_D2_kernel(const typename cplx_of<T>::type* __restrict__ U, const typename cplx_of<T>::type* __restrict__ vhat,
+             int n0, int F0, int F1, const typename cplx_of<T>::type* __restrict__ tw0g,
+             typename cplx_of<T>::type* __restrict__ X, const int* __restrict__ act) {
+  cg_D2_body<T>(U, vhat, n0, F0, F1, tw0g, X, act, blockIdx.y, blockIdx.x);
+}
+
+template <typename T>
+__device__ __forceinline__ void cg_D3_body(const typename cplx_of<T>::type* __restrict__ X,
+                                           const typename cplx_of<T>::type* __restrict__ p, const T* __restrict__ ws,
+                                           int n0, int n1, int F1, T c1, T c2, int it,
+                                           const typename cplx_of<T>::type* __restrict__ tw1g,
+                                           typename cplx_of<T>::type* __restrict__ Ap, const CgScal& s, int row, int c) {
   using C = typename cplx_of<T>::type;
   __shared__ C xrow[kDftMaxF];
   __shared__ C tw1[kDftMaxF];
   __shared__ double sh[8];
-  const int row = blockIdx.y, c = blockIdx.x, n0 = gridDim.x;
   if (!s.act[(it & 1) * s.B + row]) return;
   const int64_t M = (int64_t)n0 * n1;
+  __syncthreads();            // (persistent kernel) the previous use of xrow / tw1 by this CTA is over
   for (int j = threadIdx.x; j < F1; j += blockDim.x) {
     tw1[j] = tw1g[j];
     xrow[j] = X[((int64_t)row * n0 + c) * F1 + j];
@@ -511,6 +543,71 @@ cg_D3_kernel(const typename cplx_of<T>::type* __restrict__ X, const typename cpl
   }
   double tsum = block_sum(dot, sh);
   if (threadIdx.x == 0) s.p_pAp[row * s.NC + c] = tsum;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+cg_D3_kernel(const typename cplx_of<T>::type* __restrict__ X, const typename cplx_of<T>::type* __restrict__ p,
+             const T* __restrict__ ws, int n1, int F1, T c1, T c2, int it,
+             const typename cplx_of<T>::type* __restrict__ tw1g, typename cplx_of<T>::type* __restrict__ Ap, CgScal s) {
+  cg_D3_body<T>(X, p, ws, gridDim.x, n1, F1, c1, c2, it, tw1g, Ap, s, blockIdx.y, blockIdx.x);
+}
+
+// The whole solve of a tiny block as ONE cooperative launch: the four phases of an iteration are separated by
+// grid-wide barriers instead of kernel boundaries, so an iteration costs four barriers (~1.5 us each on 144 CTAs)
+// instead of four launches with their dependent-launch latency, and the host neither launches per iteration nor
+// reads convergence counters in between.  Every CTA takes the same decisions from the same reduced scalars, so
+// all of them leave the loop in the same iteration (a barrier is never skipped by part of the grid).
+template <typename T>
+struct CgPersistArgs {
+  typename cplx_of<T>::type *x, *r, *p, *Ap, *U, *X;
+  const typename cplx_of<T>::type *vhat, *tw0, *tw1;
+  const T *minv, *ws;
+  int n0, n1, F0, F1;
+  T c1, c2;
+  double tol;
+  int early, batched, max_iter;
+  CgScal s;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) cg_persist_kernel(const CgPersistArgs<T> a) {
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  const int c = blockIdx.x, B = a.s.B;
+  const int64_t M = (int64_t)a.n0 * a.n1;
+  int it = 0;
+  for (; it < a.max_iter; ++it) {
+    bool any = false;
+    for (int row = 0; row < B; ++row)
+      any |= cg_D1_body<T>(a.p, a.r, a.minv, a.ws, a.n0, a.n1, a.F1, it, a.tol, a.early, a.batched, a.tw1, a.U, a.s,
+                           row, c);
+    if (!any) break;                     // identical in every CTA
+    grid.sync();
+    if (c < a.F1)
+      for (int row = 0; row < B; ++row)
+        cg_D2_body<T>(a.U, a.vhat, a.n0, a.F0, a.F1, a.tw0, a.X, a.s.act + (it & 1) * B, row, c);
+    grid.sync();
+    if (c < a.n0)
+      for (int row = 0; row < B; ++row)
+        cg_D3_body<T>(a.X, a.p, a.ws, a.n0, a.n1, a.F1, a.c1, a.c2, it, a.tw1, a.Ap, a.s, row, c);
+    grid.sync();
+    if (c < a.n0)
+      for (int row = 0; row < B; ++row) cg_C_body<T>(a.x, a.r, a.p, a.Ap, a.minv, M, it, a.s, row, c);
+    grid.sync();
+  }
+  if (c == 0 && it == a.max_iter && it > 0) {      // what cg_final_kernel does after the last iteration
+    const int prev = (it & 1) ^ 1;
+    for (int row = 0; row < B; ++row) {
+      if (!a.s.act[prev * B + row]) continue;
+      double rz_new;
+      if (row_converged(a.s, row, a.tol, a.early, a.batched, rz_new) && threadIdx.x == 0) {
+        a.s.act[prev * B + row] = 0;
+        a.s.conv_iter[row] = it - 1;
+        atomicSub(&a.s.counters[0], 1);
+        atomicMax(&a.s.counters[1], it - 1);
+      }
+    }
+  }
 }
 
 // After `it` iterations: register rows that converged in iteration it-1.
@@ -627,6 +724,37 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   int check = my_hint > 0 ? std::min(my_hint, 64) : 4;
   bool first = true;
   ScopedStage stg("cg.iterations", st, 0);
+  if (direct) {
+    static const bool persist_off = std::getenv("EFGP_CG_PERSIST") && std::atoi(std::getenv("EFGP_CG_PERSIST")) == 0;
+    static int sms = 0, coop = 0;
+    if (!sms) {
+      int dev = 0;
+      EFGP_CUDA(cudaGetDevice(&dev));
+      EFGP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      EFGP_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    }
+    int per_sm = 0;
+    EFGP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cg_persist_kernel<T>, 256, 0));
+    const int ctas = std::max(n0, F1);
+    if (!persist_off && coop && ctas <= per_sm * sms) {
+      CgPersistArgs<T> a;
+      a.x = x; a.r = r; a.p = p; a.Ap = Ap; a.U = U; a.X = X;
+      a.vhat = (const C*)t.vhat; a.tw0 = tw0; a.tw1 = tw1;
+      a.minv = minv; a.ws = w;
+      a.n0 = n0; a.n1 = n1; a.F0 = F0; a.F1 = F1;
+      a.c1 = c1; a.c2 = c2;
+      a.tol = tol; a.early = early; a.batched = batched; a.max_iter = max_iter;
+      a.s = s;
+      void* args[] = {(void*)&a};
+      stg.add_launches(1);
+      EFGP_CUDA(cudaLaunchCooperativeKernel((void*)cg_persist_kernel<T>, dim3(ctas), dim3(256), args, 0, st));
+      EFGP_CUDA(cudaMemcpyAsync(h_counters, s.counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+      EFGP_CUDA(cudaStreamSynchronize(st));
+      all_conv = early && h_counters[0] <= 0;
+      jmax = h_counters[1];
+      return;
+    }
+  }
   while (it < max_iter) {
     int until = std::min(max_iter, it + check);
     stg.add_launches(4 * (until - it));

@@ -54,4 +54,8 @@ def test_two_ranks_reproduce_one_rank(tmp_path):
         assert rel < 1e-7, rel          # bar: 1e-5 (BASELINE.json); CG tolerance of the run is 1e-9
         assert two["stats"]["trace_num_rhs"] == one["stats"]["trace_num_rhs"] == 2 * 7
         assert two["stats"]["trace_samples"] == 7
-        assert abs(two["stats"]["trace_cg_iters"] - one["stats"]["trace_cg_iters"]) <= 1
+        # iteration counts are statistics, not results: the fp64 atomics of the spread make the right-hand sides
+        # differ in the last bits from run to run, and a row that sits at the 1e-9 tolerance after ~460
+        # iterations may need a few more (460 and 474 both occur): allow 5 %
+        it1, it2 = one["stats"]["trace_cg_iters"], two["stats"]["trace_cg_iters"]
+        assert abs(it2 - it1) <= max(2, 0.05 * it1), (it1, it2)
