@@ -3,6 +3,7 @@
 PyTorch is used only for device memory and streams; all arithmetic on the O(N) and O(M log M)
 paths happens in libefgp_b200.so.
 """
+import contextlib
 import ctypes
 
 import torch
@@ -36,6 +37,16 @@ def _require_cuda(t, what):
         raise _lib.EfgpError(f"{what} must be a CUDA tensor: the EFGP hot path has no CPU fallback")
 
 
+_NULL = contextlib.nullcontext()
+
+
+def _on(dev):
+    """Device guard for the C calls; entering torch.cuda.device costs ~10 us of host time per call, which is on the
+    critical path of the small launch-bound sections, so it is skipped when `dev` is already current."""
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    return _NULL if torch.cuda.current_device() == idx else torch.cuda.device(idx)
+
+
 def _stream(dev):
     return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
 
@@ -60,7 +71,7 @@ class NufftPlan:
         xc = [0.0] * self.d if xcen is None else [float(v) for v in xcen]
         self._h = ctypes.c_void_p()
         check(_lib.lib().efgp_nufft_create(ctypes.byref(self._h), int(self.d), _dtype_code(self.rdtype)))
-        with torch.cuda.device(self.device):
+        with _on(self.device):
             check(_lib.lib().efgp_nufft_set_points(self._h, _ptr(self.x), int(self.N), self.h, dbl_array(xc),
                                                    _stream(self.device)))
 
@@ -104,7 +115,7 @@ class NufftPlan:
             v = vals.to(self.cdtype if is_c else self.rdtype).reshape(B, self.N).contiguous()
         sc = self._scale(scale, M)
         out = torch.empty((B,) + out_shape, dtype=self.cdtype, device=self.device)
-        with torch.cuda.device(self.device):
+        with _on(self.device):
             check(_lib.lib().efgp_nufft_type1(self._h, _ptr(v), is_c, B, i64_array(out_shape), float(eps),
                                               int(isign), int(bool(modeord)), _ptr(sc), _ptr(out),
                                               _stream(self.device)))
@@ -128,7 +139,7 @@ class NufftPlan:
         sc = self._scale(scale, M)
         out_gen = torch.empty(shape_gen, dtype=self.cdtype, device=self.device)
         out_rhs = torch.empty(shape_rhs, dtype=self.cdtype, device=self.device)
-        with torch.cuda.device(self.device):
+        with _on(self.device):
             check(_lib.lib().efgp_nufft_type1_pair(self._h, _ptr(yv), i64_array(shape_gen), float(eps_gen),
                                                    i64_array(shape_rhs), float(eps_rhs), _ptr(sc), _ptr(out_gen),
                                                    _ptr(out_rhs), _stream(self.device)))
@@ -151,7 +162,7 @@ class NufftPlan:
         f = f.reshape(B, M).contiguous()
         sc = self._scale(scale, M)
         out = torch.empty((B, self.N), dtype=self.rdtype if real_out else self.cdtype, device=self.device)
-        with torch.cuda.device(self.device):
+        with _on(self.device):
             check(_lib.lib().efgp_nufft_type2(self._h, _ptr(f), B, i64_array(shape), float(eps), int(isign),
                                               int(bool(modeord)), _ptr(sc), 1 if real_out else 0, _ptr(out),
                                               _stream(self.device)))
@@ -176,7 +187,7 @@ class ToeplitzPlan:
         for n in self.ns:
             self.size *= n
         self._h = ctypes.c_void_p()
-        with torch.cuda.device(self.device):
+        with _on(self.device):
             check(_lib.lib().efgp_toeplitz_create(ctypes.byref(self._h), _ptr(self.v), self.d, i64_array(self.Ls),
                                                   _dtype_code(self.rdtype), 1 if force_pow2 else 0,
                                                   _stream(self.device)))
@@ -205,7 +216,7 @@ class ToeplitzPlan:
         xs = x.to(self.cdtype).reshape(-1, self.size).contiguous()
         y = torch.empty_like(xs)
         w = self._ws(ws)
-        with torch.cuda.device(self.device):
+        with _on(self.device):
             check(_lib.lib().efgp_toeplitz_apply(self._h, _ptr(xs), xs.shape[0], _ptr(w), float(sigmasq), int(mode),
                                                  _ptr(y), _stream(self.device)))
         return y.reshape(x.shape)
@@ -220,7 +231,7 @@ class ToeplitzPlan:
         w = self._ws(ws)
         mi = self._ws(minv)
         iters = ctypes.c_int(0)
-        with torch.cuda.device(self.device):
+        with _on(self.device):
             check(_lib.lib().efgp_cg_solve(self._h, _ptr(w), float(sigmasq), int(mode), _ptr(mi), _ptr(bs), _ptr(x),
                                            bs.shape[0], float(tol), -1 if max_iter is None else int(max_iter),
                                            1 if early_stopping else 0, 1 if batched else 0, ctypes.byref(iters),

@@ -762,6 +762,12 @@ class EFGPND(nn.Module):
     def _current_params(self):
         # live values (exp of the log-parameters); the reference's iter_hypers() only echoes the
         # constructor values (kernel.py:141-153), which would hide optimizer updates
+        gp = self._gp_params
+        if getattr(self.kernel, "_gp_params_ref", None) is gp and all(n in gp.hypers_names for n in self.kernel.hypers):
+            vals = gp.raw.detach().exp().tolist()          # one host op for all hypers (same values as get_hyper)
+            cur = {name: vals[gp.hypers_names.index(name)] for name in self.kernel.hypers}
+            cur["sigmasq"] = vals[-1]
+            return cur
         cur = {name: float(self.kernel.get_hyper(name)) for name in self.kernel.hypers}
         cur["sigmasq"] = float(self.sigmasq.item())
         return cur
@@ -834,7 +840,7 @@ class EFGPND(nn.Module):
         now = self._current_params()
         stale = (not self._fitted or getattr(self, "_fit_params", None) is None
                  or any(abs(self._fit_params.get(k, float("inf")) - v) > 1e-8 for k, v in now.items()))
-        self._update_param_cache()
+        self._cached_params.update(now)
         if not stale and not force_recompute:
             return
         device = self.x.device
@@ -898,8 +904,8 @@ class EFGPND(nn.Module):
         self._ws_real = A_mean.ws_real          # contiguous real weights, reused by predict's fused type-2 scaling
         self._toeplitz = toeplitz
         self._fitted = True
-        self._fit_params = self._current_params()
-        self._update_param_cache()
+        self._fit_params = now            # the hypers do not change during a fit: no second read-out after the solve
+        self._cached_params.update(now)
 
     # ------------------------------------------------------------------ predict
     def predict(self, x_new, *, return_variance: bool = True, variance_method: str = "stochastic",
