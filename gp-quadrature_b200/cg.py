@@ -27,6 +27,8 @@ class ConjugateGradients:
             raise ValueError("A_apply_function must be a torch.Tensor or a callable")
         self.b = b.to(dtype=self.dtype, device=self.device)
         self.x0 = x0.to(dtype=self.dtype, device=self.device)
+        # efgpnd tags the cold-start guesses it creates with torch.zeros_like: the library then skips A x0
+        self._x0_zero = bool(getattr(x0, "_efgp_zero", False))
         self.is_batched = b.dim() > 1
         self.tol = tol
         self.div_eps = 1e-16
@@ -55,7 +57,8 @@ class ConjugateGradients:
             minv = self.M_inv_apply.inv_diag if self.M_inv_apply is not None else None
             x, it = op.toeplitz.plan.cg(self.b, self.x0, op.mode, op.ws_real, op.sigmasq, self.tol,
                                         max_iter=self.max_iter, early_stopping=self.early_stopping,
-                                        minv=minv, batched=self.is_batched)
+                                        minv=minv, batched=self.is_batched,
+                                        x0_zero=self._x0_zero)
             self.iters_completed = it
             return x
         return self._solve_batched() if self.is_batched else self._solve_single()

@@ -106,7 +106,13 @@ cg_init_kernel(const typename cplx_of<T>::type* __restrict__ b, const typename c
   double a_rz = 0, a_bb = 0;
   for (int64_t k = k0 + threadIdx.x; k < k1; k += blockDim.x) {
     int64_t i = (int64_t)row * M + k;
-    C bv = b[i], av = Ap[i];
+    C bv = b[i], av;
+    if (Ap) {
+      av = Ap[i];
+    } else {            // x0 == 0: A x0 = 0 was not computed
+      av.x = 0;
+      av.y = 0;
+    }
     C rv;
     rv.x = bv.x - av.x;
     rv.y = bv.y - av.y;
@@ -627,7 +633,7 @@ __global__ void __launch_bounds__(256) cg_final_kernel(int it, double tol, int e
 
 template <typename T>
 static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, const T* minv, const void* b_, void* x_,
-                        int B, double tol, int max_iter, int early, int batched, int& all_conv, int& jmax,
+                        int B, double tol, int max_iter, int early, int batched, int x0_zero, int& all_conv, int& jmax,
                         cudaStream_t st) {
   using C = typename cplx_of<T>::type;
   const int64_t M = t.M;
@@ -700,12 +706,12 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   }
   C* Q = (C*)t.Q.get(need);
 
-  // Ap = A x0  (generic apply writes through P/Q as well)
-  toeplitz_apply(t, x, B, ws, sigmasq, mode, Ap, st);
+  // Ap = A x0  (generic apply writes through P/Q as well); skipped for a cold start
+  if (!x0_zero) toeplitz_apply(t, x, B, ws, sigmasq, mode, Ap, st);
   dim3 grid(s.NC, B), gf(div_up(t.Ftot, 256), B);
   {
     ScopedStage stg_init("cg.init", st, 2);
-    cg_init_kernel<T><<<grid, 256, 0, st>>>(b, Ap, minv, r, p, M, s);
+    cg_init_kernel<T><<<grid, 256, 0, st>>>(b, x0_zero ? (const C*)nullptr : (const C*)Ap, minv, r, p, M, s);
     cg_init_scal_kernel<<<B, 256, 0, st>>>(s);
   }
   EFGP_CUDA(cudaGetLastError());
@@ -793,7 +799,7 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
 }
 
 void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void* minv, const void* b, void* x,
-              int batch, double tol, int max_iter, int early_stopping, int batched_semantics,
+              int batch, double tol, int max_iter, int early_stopping, int batched_semantics, int x0_is_zero,
               int* iters_completed, cudaStream_t st) {
   EFGP_CHECK(batch >= 1, "batch must be >= 1");
   EFGP_CHECK(mode >= 0 && mode <= 3, "unknown operator mode");
@@ -810,10 +816,10 @@ void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void*
     char* xx = (char*)x + (size_t)b0 * t.M * esz;
     if (t.dtype == 0)
       solve_group<float>(t, (const float*)ws, sigmasq, mode, (const float*)minv, bb, xx, nb, tol, max_iter,
-                         early_stopping, batched_semantics, all_conv, jmax, st);
+                         early_stopping, batched_semantics, x0_is_zero, all_conv, jmax, st);
     else
       solve_group<double>(t, (const double*)ws, sigmasq, mode, (const double*)minv, bb, xx, nb, tol, max_iter,
-                          early_stopping, batched_semantics, all_conv, jmax, st);
+                          early_stopping, batched_semantics, x0_is_zero, all_conv, jmax, st);
     int it_g = max_iter;
     if (all_conv) it_g = batched_semantics ? std::min(jmax + 2, max_iter) : jmax + 1;
     iters = std::max(iters, it_g);

@@ -27,7 +27,7 @@ void toeplitz_create(Toeplitz& t, const void* v, int dim, const int64_t* Ls, int
 void toeplitz_apply(Toeplitz& t, const void* x, int batch, const void* ws, double sigmasq, int mode, void* y,
                     cudaStream_t st);
 void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void* minv, const void* b, void* x,
-              int batch, double tol, int max_iter, int early_stopping, int batched_semantics,
+              int batch, double tol, int max_iter, int early_stopping, int batched_semantics, int x0_is_zero,
               int* iters_completed, cudaStream_t st);
 
 }  // namespace efgp

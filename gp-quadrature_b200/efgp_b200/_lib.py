@@ -38,7 +38,8 @@ _SIGNATURES = {
     "efgp_toeplitz_fft_shape": (ctypes.c_int, [vp, c_i64p]),
     "efgp_toeplitz_apply": (ctypes.c_int, [vp, vp, ctypes.c_int, vp, ctypes.c_double, ctypes.c_int, vp, vp]),
     "efgp_cg_solve": (ctypes.c_int, [vp, vp, ctypes.c_double, ctypes.c_int, vp, vp, vp, ctypes.c_int,
-                                     ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_intp, vp]),
+                                     ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, c_intp,
+                                     vp]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

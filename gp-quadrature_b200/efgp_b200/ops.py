@@ -221,19 +221,25 @@ class ToeplitzPlan:
                                                  _ptr(y), _stream(self.device)))
         return y.reshape(x.shape)
 
-    def cg(self, b, x0, mode, ws, sigmasq, tol, max_iter=None, early_stopping=True, minv=None, batched=None):
-        """Solve A x = b for the fused operator `mode`; returns (x, iters_completed)."""
+    def cg(self, b, x0, mode, ws, sigmasq, tol, max_iter=None, early_stopping=True, minv=None, batched=None,
+           x0_zero=False):
+        """Solve A x = b for the fused operator `mode`; returns (x, iters_completed).  x0_zero=True promises that
+        x0 is all zeros (x0 may then be None): the library skips the matvec A x0."""
         _require_cuda(b, "b")
         if batched is None:
             batched = b.ndim > 1
         bs = b.to(self.cdtype).reshape(-1, self.size).contiguous()
-        x = x0.to(self.cdtype).reshape(-1, self.size).clone().contiguous()
+        if x0_zero:
+            x = torch.zeros_like(bs)
+        else:
+            x = x0.to(self.cdtype).reshape(-1, self.size).clone().contiguous()
         w = self._ws(ws)
         mi = self._ws(minv)
         iters = ctypes.c_int(0)
         with _on(self.device):
             check(_lib.lib().efgp_cg_solve(self._h, _ptr(w), float(sigmasq), int(mode), _ptr(mi), _ptr(bs), _ptr(x),
                                            bs.shape[0], float(tol), -1 if max_iter is None else int(max_iter),
-                                           1 if early_stopping else 0, 1 if batched else 0, ctypes.byref(iters),
+                                           1 if early_stopping else 0, 1 if batched else 0, 1 if x0_zero else 0,
+                                           ctypes.byref(iters),
                                            _stream(self.device)))
         return x.reshape(b.shape), int(iters.value)

@@ -279,7 +279,8 @@ class _FusedOperator:
         # EFGP weights are sqrt(S h^d) >= 0 stored as complex (efgpnd.py:98, 779-780).  Tensors built by this
         # module are tagged so the zero-imaginary test (a device->host sync) only runs for foreign weights.
         self._real_ws = (not w.is_complex()) or getattr(ws, "_efgp_real", False) or bool((w.imag == 0).all())
-        self.ws_real = (w.real if w.is_complex() else w).to(device=toeplitz.device).contiguous()
+        wr = getattr(ws, "_efgp_real_part", None)
+        self.ws_real = wr if wr is not None else (w.real if w.is_complex() else w).to(device=toeplitz.device).contiguous()
 
     def __call__(self, v):
         v = v.to(dtype=self.cdtype)
@@ -331,10 +332,19 @@ def create_jacobi_precond(ws, sigmasq_scalar, diag_scale=1.0):
     """M^-1 v = v / (diag_scale |ws|^2 + sigma^2) (efgpnd.py:1619-1631)."""
     ss = sigmasq_scalar.detach() if isinstance(sigmasq_scalar, torch.Tensor) else sigmasq_scalar
     ds = diag_scale.detach() if isinstance(diag_scale, torch.Tensor) else diag_scale
-    return _JacobiPrecond(ds * ws.detach().abs().pow(2).real + ss)
+    wr = getattr(ws, "_efgp_real_part", None)      # weights built by EFGPND: |ws|^2 = Re(ws)^2 without the complex abs
+    w2 = (wr * wr) if wr is not None else ws.detach().abs().pow(2).real
+    return _JacobiPrecond(ds * w2 + ss)
 
 
 # ----------------------------------------------------------------------------- probes
+def _zero_guess(like, dtype=None):
+    """torch.zeros_like(like), tagged so that ConjugateGradients can tell the library that A x0 = 0."""
+    z = torch.zeros_like(like, dtype=dtype) if dtype is not None else torch.zeros_like(like)
+    z._efgp_zero = True
+    return z
+
+
 def _rademacher_like_reference(shape, rdtype, device):
     """+-1 probes drawn with the reference's calls `empty(shape).bernoulli_(0.5).mul_(2).sub_(1)`
     (efgpnd.py:179-181, 199-201), on PROBE_DEVICE if set, else on `device`."""
@@ -366,7 +376,7 @@ def diag_sums_nd(A_apply, J, xis_flat, max_cg_iter, cg_tol, ws):
     draw_dev = torch.device(PROBE_DEVICE) if PROBE_DEVICE is not None else dev
     etas = (torch.randint(0, 2, (J, N), device=draw_dev) * 2 - 1).to(xis_flat.dtype).to(dev)
     rhs = ws[None, :] * etas
-    us = ConjugateGradients(A_apply, rhs, x0=torch.zeros_like(rhs), tol=cg_tol, max_iter=max_cg_iter,
+    us = ConjugateGradients(A_apply, rhs, x0=_zero_guess(rhs), tol=cg_tol, max_iter=max_cg_iter,
                             early_stopping=True).solve()
     gammas = ws[None, :] * us
     s_size = (2 * M_loc - 1,) * d_loc
@@ -402,7 +412,7 @@ def compute_prediction_variance(x_new, xis, ws, A_var, cg_tol, max_cg_iter, vari
         for xb in torch.split(x_new, 8192, dim=0):
             fx = torch.exp(2 * math.pi * 1j * (xb @ xis.T)).to(cdtype)
             rhs = ws * fx.conj()
-            gamma = ConjugateGradients(A_var, rhs, x0=torch.zeros_like(rhs, dtype=cdtype), tol=cg_tol,
+            gamma = ConjugateGradients(A_var, rhs, x0=_zero_guess(rhs, cdtype), tol=cg_tol,
                                        max_iter=max_cg_iter, early_stopping=True).solve()
             out.append(torch.real((fx * (ws * gamma)).sum(dim=-1)).clamp_min(0.0))
             del fx, rhs, gamma
@@ -547,7 +557,7 @@ def efgpnd_gradient_batched(
             Fy = nufft_op.type1(y, OUT).reshape(-1)
             rhs = ws * Fy
             warm = mean_cg_init is not None and mean_cg_init.shape == rhs.shape
-            mean_x0 = mean_cg_init.to(device=device, dtype=cdtype).clone() if warm else torch.zeros_like(rhs)
+            mean_x0 = mean_cg_init.to(device=device, dtype=cdtype).clone() if warm else _zero_guess(rhs)
             cg_mean = ConjugateGradients(A_apply, rhs, mean_x0, tol=cg_tol, early_stopping=early_stopping,
                                          M_inv_apply=mean_M_inv)
             beta = cg_mean.solve()
@@ -593,7 +603,7 @@ def efgpnd_gradient_batched(
             B_noise = (ws * toeplitz(ws * Vl)).reshape(Tl, -1)
             B_all = torch.cat((B_all_kernel, B_noise.unsqueeze(0)), dim=0).reshape((nk + 1) * Tl, -1)
             with rf("7_batch_cg_solve"):
-                cg_trace = ConjugateGradients(A_apply, B_all, torch.zeros_like(B_all), tol=cg_tol,
+                cg_trace = ConjugateGradients(A_apply, B_all, _zero_guess(B_all), tol=cg_tol,
                                               early_stopping=early_stopping, M_inv_apply=trace_M_inv)
                 Beta_all = cg_trace.solve()
             with rf("7.5_compute_alpha"):
@@ -878,8 +888,13 @@ class EFGPND(nn.Module):
         xis = torch.stack(torch.meshgrid(*(xis_1d for _ in range(d)), indexing="ij"), dim=-1).view(-1, d)
         xis.h_float = h_float
         hd = torch.tensor(h_float, dtype=rdtype) ** d          # CPU scalar, same arithmetic as the reference's h ** d
-        ws = torch.sqrt(self.kernel.spectral_density(xis).to(dtype=cdtype) * float(hd)).to(dtype=cdtype)
+        # ws = sqrt(S h^d) stored as complex like the reference's (efgpnd.py:779-780).  S >= 0, so the square root is
+        # taken in real arithmetic (the complex sqrt of (a, 0), a >= 0 is (sqrt a, 0) exactly, at five times the
+        # kernel time) and the real part stays attached for the fused operators and the Jacobi diagonal.
+        ws_r = torch.sqrt(self.kernel.spectral_density(xis).to(dtype=rdtype) * float(hd))
+        ws = ws_r.to(dtype=cdtype)
         ws._efgp_real = True
+        ws._efgp_real_part = ws_r
         rhs = ws * Fy.reshape(-1)                                                # ws * F^* y
         v_kernel, rhs = _sum_over_shards(v_kernel, rhs, group)
         toeplitz = ToeplitzND(v_kernel, force_pow2=_TOEPLITZ_POW2)
@@ -892,7 +907,7 @@ class EFGPND(nn.Module):
         if self.opts.get("mean_cg_warm_start", True) and self._beta is not None and self._beta.shape == rhs.shape:
             beta_x0 = self._beta.to(device=device, dtype=cdtype).clone()
         else:
-            beta_x0 = torch.zeros_like(rhs, dtype=cdtype)
+            beta_x0 = _zero_guess(rhs, cdtype)
         solver = ConjugateGradients(A_mean, rhs, x0=beta_x0, tol=cg_tol, early_stopping=True, M_inv_apply=mean_M_inv)
         beta = solver.solve()
         self.last_fit_stats = {"mean_cg_iters": int(solver.iters_completed), "mtot": int(mtot), "h": h_float,

@@ -93,10 +93,11 @@ int efgp_toeplitz_apply(efgp_toeplitz* t, const void* x, int batch, const void* 
  * b: (batch, M) complex; x: (batch, M) complex, holds x0 on entry and the solution on exit;
  * minv: optional (M,) real Jacobi diagonal M^-1 (create_jacobi_precond, efgpnd.py:1619-1631);
  * max_iter < 0 means 2*M (cg.py:60-65); batched_semantics selects _solve_batched (1) or
- * _solve_single (0) stopping rules and iteration counting.  Synchronises the stream. */
+ * _solve_single (0) stopping rules and iteration counting; x0_is_zero = 1 is the caller's promise that x holds
+ * zeros on entry (the cold start of every fit, efgpnd.py:805), which saves the matvec A x0.  Synchronises the stream. */
 int efgp_cg_solve(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, const void* minv,
                   const void* b, void* x, int batch, double tol, int max_iter, int early_stopping,
-                  int batched_semantics, int* iters_completed, void* stream);
+                  int batched_semantics, int x0_is_zero, int* iters_completed, void* stream);
 
 #ifdef __cplusplus
 }
