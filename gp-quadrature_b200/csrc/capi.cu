@@ -215,4 +215,13 @@ int efgp_cg_solve(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, co
   })
 }
 
+int efgp_lanczos(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, void* q, int batch, int steps,
+                 double breakdown_tol, double* alphas, double* betas, void* stream) {
+  EFGP_TRY({
+    EFGP_CHECK(t != nullptr && q != nullptr && alphas != nullptr && betas != nullptr, "null argument");
+    efgp::lanczos_tridiag(t->t, ws, sigmasq, mode, q, batch, steps, breakdown_tol, alphas, betas,
+                          (cudaStream_t)stream);
+  })
+}
+
 }  // extern "C"

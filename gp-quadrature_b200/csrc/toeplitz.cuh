@@ -29,5 +29,9 @@ void toeplitz_apply(Toeplitz& t, const void* x, int batch, const void* ws, doubl
 void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void* minv, const void* b, void* x,
               int batch, double tol, int max_iter, int early_stopping, int batched_semantics, int x0_is_zero,
               int* iters_completed, cudaStream_t st);
+// lanczos.cu: `steps` lockstep Lanczos steps from the normalised start block q0 (overwritten); alphas / betas are
+// (batch, steps) doubles on the device.  Enqueues only (no synchronisation).
+void lanczos_tridiag(Toeplitz& t, const void* ws, double sigmasq, int mode, void* q0, int batch, int steps,
+                     double breakdown, double* alphas, double* betas, cudaStream_t st);
 
 }  // namespace efgp

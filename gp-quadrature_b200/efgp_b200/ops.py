@@ -243,3 +243,17 @@ class ToeplitzPlan:
                                            ctypes.byref(iters),
                                            _stream(self.device)))
         return x.reshape(b.shape), int(iters.value)
+
+    def lanczos(self, q, steps, mode, ws, sigmasq, breakdown_tol=1e-12):
+        """`steps` lockstep Lanczos steps of the fused operator `mode` from the unit-norm rows of q (P, M);
+        returns (alphas, betas), each (P, steps) float64 on the device.  No host synchronisation."""
+        _require_cuda(q, "q")
+        qs = q.to(self.cdtype).reshape(-1, self.size).clone().contiguous()   # the library uses it as work space
+        P = qs.shape[0]
+        alphas = torch.empty((P, int(steps)), dtype=torch.float64, device=self.device)
+        betas = torch.empty_like(alphas)
+        w = self._ws(ws)
+        with _on(self.device):
+            check(_lib.lib().efgp_lanczos(self._h, _ptr(w), float(sigmasq), int(mode), _ptr(qs), P, int(steps),
+                                          float(breakdown_tol), _ptr(alphas), _ptr(betas), _stream(self.device)))
+        return alphas, betas

@@ -153,8 +153,14 @@ class NUFFT:
         x = x.to(self.device)
         if not x.is_cuda:
             raise EfgpError("NUFFT needs CUDA tensors: the EFGP hot path has no CPU fallback")
-        self._x, self._xcen, self._h = x, xcen, h
         self.d = x.shape[1]
+        if isinstance(xcen, torch.Tensor) and xcen.ndim == 2 and xcen.shape[0] > 1:
+            # pg_classifier.py:347-354 passes zeros_like(X): a per-point centre only broadcasts like the reference's
+            # (x - xcen) when its rows agree, and then it is a d-vector
+            if tuple(xcen.shape) != tuple(x.shape) or not bool((xcen == xcen[:1]).all()):
+                raise ValueError("xcen must be a d-vector (or an (N, d) tensor with identical rows)")
+            xcen = xcen[0]
+        self._x, self._xcen, self._h = x, xcen, h
         self._plan = _shared_plan(x, _as_float(h), xcen if xcen is not None else [0.0] * self.d)
         self._phi = None
 
@@ -438,38 +444,24 @@ def logdet_slq(ws, sigma2, toeplitz, *, probes=1000, steps=100, dtype=torch.floa
     wr = (ws.real if ws.is_complex() else ws).to(dtype=dtype, device=dev)
     m = wr.numel()
     s2 = _as_float(sigma2)
-    cd = _cmplx(dtype)
-    A = _FusedOperator(wr.to(cd), toeplitz, s2, _ops.MODE_A_VAR, cd)   # v + Gv(v)/sigma^2
-    z = _rademacher_like_reference((probes, m), dtype, dev)
-    znorm = z.norm(dim=1)
-    q = (z / znorm[:, None]).to(cd)
-    q_prev = torch.zeros_like(q)
-    beta_prev = torch.zeros(probes, dtype=dtype, device=dev)
-    alphas, betas = [], []
-    alive = torch.ones(probes, dtype=torch.bool, device=dev)
-    for _ in range(steps):
-        v = A(q) - beta_prev[:, None] * q_prev
-        alpha = torch.sum(q.conj() * v, dim=1).real
-        v = v - alpha[:, None] * q
-        beta = torch.linalg.norm(v, dim=1).real
-        alphas.append(torch.where(alive, alpha, torch.ones_like(alpha)))
-        betas.append(torch.where(alive, beta, torch.zeros_like(beta)))
-        alive = alive & (beta >= 1e-12)
-        q_prev, beta_prev = q, torch.where(alive, beta, torch.zeros_like(beta))
-        q = torch.where(alive[:, None], v / beta.clamp_min(1e-300)[:, None], q)
-        if not bool(alive.any()):
-            break
-    k = len(alphas)
-    a = torch.stack(alphas, 1)
-    b = torch.stack(betas, 1)
-    T = torch.diag_embed(a)
-    if k > 1:
-        T = T + torch.diag_embed(b[:, :-1], offset=1) + torch.diag_embed(b[:, :-1], offset=-1)
-    evals, evecs = torch.linalg.eigh(T)
-    evals = evals.clamp_min(eps)
-    # rows that broke down early carry decoupled unit blocks (eigenvalue 1 -> log 0), so they add nothing
-    quad = (evecs[:, 0, :] ** 2 * torch.log(evals)).sum(1) * znorm ** 2
-    return float(quad.mean().item()) + n * math.log(s2)
+    quad_sum = 0.0
+    # probe blocks bound the three (P, M) work vectors and the padded FFT grids of the matvec
+    per = max(1, min(probes, 65535, int((1 << 27) // max(1, prod(toeplitz.fft_shape)))))
+    for p0 in range(0, probes, per):
+        z = _rademacher_like_reference((min(per, probes - p0), m), dtype, dev)
+        znorm = z.norm(dim=1)
+        q = (z / znorm[:, None]).to(_cmplx(dtype))
+        # A = I + Gv / sigma^2 (efgpnd.py:1713-1715); the whole recurrence runs in the library (lanczos.cu)
+        a, b = toeplitz.plan.lanczos(q, steps, _ops.MODE_A_VAR, wr, s2, breakdown_tol=1e-12)
+        a, b = a.to(dtype), b.to(dtype)
+        T = torch.diag_embed(a)
+        if steps > 1:
+            T = T + torch.diag_embed(b[:, :-1], offset=1) + torch.diag_embed(b[:, :-1], offset=-1)
+        evals, evecs = torch.linalg.eigh(T)
+        evals = evals.clamp_min(eps)
+        # rows that broke down early carry decoupled unit blocks (eigenvalue 1 -> log 0), so they add nothing
+        quad_sum = quad_sum + (evecs[:, 0, :] ** 2 * torch.log(evals)).sum(1).mul(znorm ** 2).sum()
+    return float((quad_sum / probes).item()) + n * math.log(s2)
 
 
 # ----------------------------------------------------------------------------- gradient

@@ -99,6 +99,16 @@ int efgp_cg_solve(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, co
                   const void* b, void* x, int batch, double tol, int max_iter, int early_stopping,
                   int batched_semantics, int x0_is_zero, int* iters_completed, void* stream);
 
+/* ---- Lanczos: replaces the probe loop of logdet_slq (efgpnd.py:1719-1746), all probes in lockstep, for
+ * operators of the four modes above (the reference uses A = I + Gv / sigma^2, mode 3).
+ * q: (batch, M) complex start vectors z / ||z|| (efgpnd.py:1723), OVERWRITTEN (used as work space);
+ * alphas, betas: (batch, steps) float64 device arrays = the diagonal and the off-diagonal (betas[:, j] couples
+ * rows j and j+1; the last column is unused, as in the reference's T, efgpnd.py:1748-1753).  A row whose beta falls
+ * below breakdown_tol (1e-12, efgpnd.py:1742) stops: its remaining entries are alpha = 1, beta = 0, decoupled unit
+ * blocks that add log 1 = 0 to the quadrature.  Enqueues on the stream, does not synchronise. */
+int efgp_lanczos(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, void* q, int batch, int steps,
+                 double breakdown_tol, double* alphas, double* betas, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

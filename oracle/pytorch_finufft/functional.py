@@ -67,12 +67,15 @@ def finufft_type1(points, values, output_shape, eps=1e-6, isign=-1, modeord=Fals
     M = 1
     for s in output_shape:
         M *= s
-    out = torch.zeros(v.shape[0], M, dtype=torch.complex128)
-    step = max(1, _CHUNK_ELEMS // max(M, 1))
+    out = None     # accumulated functionally (no in-place ops) so the stand-in also runs under torch.vmap,
+    step = max(1, _CHUNK_ELEMS // max(M, 1))   # which pg_classifier.py:357-358 wraps around type1 / type2
     for s0 in range(0, N, step):
         sl = slice(s0, min(N, s0 + step))
         F = _dense_rows(_axis_phases(points[:, sl], output_shape, isign, modeord))
-        out += v[:, sl] @ F
+        part = v[:, sl] @ F
+        out = part if out is None else out + part
+    if out is None:
+        out = torch.zeros(v.shape[0], M, dtype=torch.complex128)
     return out.reshape(*batch, *output_shape).to(cd)
 
 
@@ -87,10 +90,11 @@ def finufft_type2(points, targets, eps=1e-6, isign=+1, modeord=False, **_):
     for s in shape:
         M *= s
     f = targets.reshape(-1, M).to(torch.complex128)
-    out = torch.empty(f.shape[0], N, dtype=torch.complex128)
+    parts = []
     step = max(1, _CHUNK_ELEMS // max(M, 1))
     for s0 in range(0, N, step):
         sl = slice(s0, min(N, s0 + step))
         F = _dense_rows(_axis_phases(points[:, sl], shape, isign, modeord))
-        out[:, sl] = f @ F.T
+        parts.append(f @ F.T)
+    out = torch.cat(parts, dim=1) if parts else torch.empty(f.shape[0], 0, dtype=torch.complex128)
     return out.reshape(*batch, N).to(cd)
