@@ -58,7 +58,8 @@ class ConjugateGradients:
             x, it = op.toeplitz.plan.cg(self.b, self.x0, op.mode, op.ws_real, op.sigmasq, self.tol,
                                         max_iter=self.max_iter, early_stopping=self.early_stopping,
                                         minv=minv, batched=self.is_batched,
-                                        x0_zero=self._x0_zero)
+                                        x0_zero=self._x0_zero,
+                                        hermitian=bool(getattr(self.b, "_efgp_hermitian", False)))
             self.iters_completed = it
             return x
         return self._solve_batched() if self.is_batched else self._solve_single()

@@ -34,6 +34,9 @@ struct TzGeomC {
   int n[kMaxDim];
   int F[kMaxDim];
   int64_t M, Ftot;
+  int mc[kMaxDim];     // centre of the block per axis, (n - 1) / 2   (Hermitian path)
+  int Fh;              // F[last] / 2 + 1: last extent of the half spectrum
+  int64_t Htot;        // elements of the half spectrum per row
 };
 
 __device__ __forceinline__ void tzc_offsets(const TzGeomC& g, int64_t k64, int64_t& pad_off, int64_t& crop_off) {
@@ -49,6 +52,29 @@ __device__ __forceinline__ void tzc_offsets(const TzGeomC& g, int64_t k64, int64
   for (int a = 0; a < g.dim; ++a) {
     pad_off = pad_off * g.F[a] + id[a];
     crop_off = crop_off * g.F[a] + (id[a] + g.n[a] - 1);
+  }
+}
+
+// Hermitian path: position of mode k (neg = false) or of -k (neg = true, taken when k lies in the half that the
+// half spectrum does not store: centred last index < 0) inside the (F_0, .., F_last/2+1) half-spectrum array.
+__device__ __forceinline__ void tzc_sym_offset(const TzGeomC& g, int64_t k64, int64_t& hoff, bool& neg) {
+  int id[kMaxDim] = {0, 0, 0};
+  uint32_t k = (uint32_t)k64;
+  for (int a = g.dim - 1; a >= 0; --a) {
+    const uint32_t q = k / (uint32_t)g.n[a];
+    id[a] = (int)(k - q * (uint32_t)g.n[a]);
+    k = q;
+  }
+  const int last = g.dim - 1;
+  neg = id[last] < g.mc[last];
+  hoff = 0;
+  for (int a = 0; a < g.dim; ++a) {
+    int ka = id[a] - g.mc[a];
+    if (neg) ka = -ka;
+    if (a < last)
+      hoff = hoff * g.F[a] + (ka < 0 ? ka + g.F[a] : ka);
+    else
+      hoff = hoff * g.Fh + ka;
   }
 }
 
@@ -160,7 +186,7 @@ __device__ __forceinline__ bool row_converged(const CgScal& s, int row, double t
   return conv;
 }
 
-template <typename T>
+template <typename T, bool SYM>
 __global__ void __launch_bounds__(256)
 cg_A_kernel(typename cplx_of<T>::type* __restrict__ p, const typename cplx_of<T>::type* __restrict__ r,
             const T* __restrict__ minv, const T* __restrict__ ws, TzGeomC g, int it, double tol, int early,
@@ -212,8 +238,51 @@ cg_A_kernel(typename cplx_of<T>::type* __restrict__ p, const typename cplx_of<T>
     C o;
     o.x = pv.x * w;
     o.y = pv.y * w;
-    P[(int64_t)row * g.Ftot + po] = o;
+    if (SYM) {        // half spectrum of the real array X(f): conj(ws p) at the modes with centred last index >= 0
+      int64_t ho;
+      bool neg;
+      tzc_sym_offset(g, k, ho, neg);
+      if (!neg) {
+        o.y = -o.y;
+        P[(int64_t)row * g.Htot + ho] = o;
+      }
+    } else {
+      P[(int64_t)row * g.Ftot + po] = o;
+    }
   }
+}
+
+// Hermitian path: v <- (v + conj(mirror v)) / 2 per row.  On an odd centred grid the mirror of flat index k is M-1-k.
+// The real-FFT matvec reads only half of p and returns an exactly symmetric Ap, so an asymmetric component of the
+// start (rounding-level in a warm start) would never be reduced and would leak into x through p: project it out once.
+template <typename T>
+__global__ void __launch_bounds__(256)
+cg_symmetrize_kernel(typename cplx_of<T>::type* __restrict__ v, int64_t M) {
+  using C = typename cplx_of<T>::type;
+  const int row = blockIdx.y;
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t km = M - 1 - k;
+  if (k > km) return;
+  C* base = v + (int64_t)row * M;
+  C a = base[k], b = base[km];
+  C sm;
+  sm.x = T(0.5) * (a.x + b.x);
+  sm.y = T(0.5) * (a.y - b.y);
+  if (k == km) sm.y = 0;
+  base[k] = sm;
+  sm.y = -sm.y;
+  base[km] = sm;
+}
+
+// Hermitian path: X(f) *= V(f), both real
+template <typename T>
+__global__ void __launch_bounds__(256)
+cg_Mr_kernel(T* __restrict__ R, const T* __restrict__ vr, int64_t Ftot, const int* __restrict__ act) {
+  int row = blockIdx.y;
+  if (!act[row]) return;
+  int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= Ftot) return;
+  R[(int64_t)row * Ftot + f] *= vr[f];
 }
 
 template <typename T>
@@ -233,7 +302,7 @@ cg_M_kernel(typename cplx_of<T>::type* __restrict__ Q, const typename cplx_of<T>
   Q[(int64_t)row * Ftot + f] = o;
 }
 
-template <typename T>
+template <typename T, bool SYM>
 __global__ void __launch_bounds__(256)
 cg_B_kernel(const typename cplx_of<T>::type* __restrict__ Q, const typename cplx_of<T>::type* __restrict__ p,
             const T* __restrict__ ws, TzGeomC g, T c1, T c2, int it,
@@ -248,7 +317,16 @@ cg_B_kernel(const typename cplx_of<T>::type* __restrict__ Q, const typename cplx
     int64_t i = (int64_t)row * g.M + k;
     int64_t po, co;
     tzc_offsets(g, k, po, co);
-    C q = Q[(int64_t)row * g.Ftot + co];
+    C q;
+    if (SYM) {        // y[k] = conj(out[k]) for stored modes, y[k] = conj(y[-k]) = out[-k] for the other half
+      int64_t ho;
+      bool neg;
+      tzc_sym_offset(g, k, ho, neg);
+      q = Q[(int64_t)row * g.Htot + ho];
+      if (!neg) q.y = -q.y;
+    } else {
+      q = Q[(int64_t)row * g.Ftot + co];
+    }
     C pv = p[i];
     T w = ws ? ws[k] * c1 : c1;
     C o;
@@ -634,7 +712,7 @@ __global__ void __launch_bounds__(256) cg_final_kernel(int it, double tol, int e
 template <typename T>
 static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, const T* minv, const void* b_, void* x_,
                         int B, double tol, int max_iter, int early, int batched, int x0_zero, int& all_conv, int& jmax,
-                        cudaStream_t st) {
+                        cudaStream_t st, int hermitian) {
   using C = typename cplx_of<T>::type;
   const int64_t M = t.M;
   TzGeomC g;
@@ -645,6 +723,16 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   }
   g.M = M;
   g.Ftot = t.Ftot;
+  bool odd = true;
+  g.Htot = 1;
+  for (int a = 0; a < kMaxDim; ++a) {
+    g.mc[a] = (g.n[a] - 1) / 2;
+    if (a < t.dim) {
+      odd = odd && (g.n[a] & 1);
+      g.Htot *= (a == t.dim - 1) ? g.F[a] / 2 + 1 : g.F[a];
+    }
+  }
+  g.Fh = g.F[t.dim - 1] / 2 + 1;
   const C* b = (const C*)b_;
   C* x = (C*)x_;
   T c1 = 1, c2 = 0;
@@ -705,14 +793,24 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
     t.P_rows = B;
   }
   C* Q = (C*)t.Q.get(need);
+  // Hermitian right-hand sides (caller's promise) on odd blocks: real-FFT matvec in the cuFFT loop below
+  static const bool sym_off = std::getenv("EFGP_CG_NO_HERMITIAN") != nullptr;     // A/B switch
+  const bool sym = hermitian && odd && !direct && !sym_off;
+  const T* vreal = sym ? (const T*)toeplitz_real_spectrum(t, st) : nullptr;
 
   // Ap = A x0  (generic apply writes through P/Q as well); skipped for a cold start
+  const dim3 gsym(div_up((M + 1) / 2, 256), B);
+  if (sym && !x0_zero) cg_symmetrize_kernel<T><<<gsym, 256, 0, st>>>(x, M);
   if (!x0_zero) toeplitz_apply(t, x, B, ws, sigmasq, mode, Ap, st);
   dim3 grid(s.NC, B), gf(div_up(t.Ftot, 256), B);
   {
     ScopedStage stg_init("cg.init", st, 2);
     cg_init_kernel<T><<<grid, 256, 0, st>>>(b, x0_zero ? (const C*)nullptr : (const C*)Ap, minv, r, p, M, s);
     cg_init_scal_kernel<<<B, 256, 0, st>>>(s);
+    if (sym) {
+      cg_symmetrize_kernel<T><<<gsym, 256, 0, st>>>(r, M);
+      cg_symmetrize_kernel<T><<<gsym, 256, 0, st>>>(p, M);
+    }
   }
   EFGP_CUDA(cudaGetLastError());
 
@@ -770,12 +868,37 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
       cg_D3_kernel<T><<<grid, 256, 0, st>>>(X, p, w, n1, F1, c1, c2, it, tw1, Ap, s);
       cg_C_kernel<T><<<grid, 256, 0, st>>>(x, r, p, Ap, minv, M, it, s);
     }
+    for (; sym && it < until; ++it) {
+      // half-size matvec: H = conj(ws p) on the stored half of the modes (C2R input, clobbered by cuFFT -> zeroed
+      // every iteration), X = Z2D(H) real, X *= V, H = D2Z(X), Ap from conj(H)
+      C* H = P;
+      T* R = (T*)Q;
+      EFGP_CUDA(cudaMemsetAsync(H, 0, (size_t)B * g.Htot * sizeof(C), st));
+      cg_A_kernel<T, true><<<grid, 256, 0, st>>>(p, r, minv, w, g, it, tol, early, batched, H, s);
+      {
+        cufftHandle pl = global_fft().get(t.dim, t.F, sizeof(T) == 4 ? CUFFT_C2R : CUFFT_Z2D, B, st);
+        if (sizeof(T) == 4)
+          EFGP_CUFFT(cufftExecC2R(pl, (cufftComplex*)H, (cufftReal*)R));
+        else
+          EFGP_CUFFT(cufftExecZ2D(pl, (cufftDoubleComplex*)H, (cufftDoubleReal*)R));
+      }
+      cg_Mr_kernel<T><<<gf, 256, 0, st>>>(R, vreal, t.Ftot, s.act + (it & 1) * B);
+      {
+        cufftHandle pl = global_fft().get(t.dim, t.F, sizeof(T) == 4 ? CUFFT_R2C : CUFFT_D2Z, B, st);
+        if (sizeof(T) == 4)
+          EFGP_CUFFT(cufftExecR2C(pl, (cufftReal*)R, (cufftComplex*)H));
+        else
+          EFGP_CUFFT(cufftExecD2Z(pl, (cufftDoubleReal*)R, (cufftDoubleComplex*)H));
+      }
+      cg_B_kernel<T, true><<<grid, 256, 0, st>>>(H, p, w, g, c1, c2, it, Ap, s);
+      cg_C_kernel<T><<<grid, 256, 0, st>>>(x, r, p, Ap, minv, M, it, s);
+    }
     for (; it < until; ++it) {
-      cg_A_kernel<T><<<grid, 256, 0, st>>>(p, r, minv, w, g, it, tol, early, batched, P, s);
+      cg_A_kernel<T, false><<<grid, 256, 0, st>>>(p, r, minv, w, g, it, tol, early, batched, P, s);
       fft_pair_begin<T>(t, B, P, Q, st);
       cg_M_kernel<T><<<gf, 256, 0, st>>>(Q, (const C*)t.vhat, t.Ftot, s.act + (it & 1) * B);
       fft_pair_end<T>(t, B, Q, st);
-      cg_B_kernel<T><<<grid, 256, 0, st>>>(Q, p, w, g, c1, c2, it, Ap, s);
+      cg_B_kernel<T, false><<<grid, 256, 0, st>>>(Q, p, w, g, c1, c2, it, Ap, s);
       cg_C_kernel<T><<<grid, 256, 0, st>>>(x, r, p, Ap, minv, M, it, s);
     }
     EFGP_CUDA(cudaGetLastError());
@@ -793,6 +916,7 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
     }
   }
   if (!early) EFGP_CUDA(cudaStreamSynchronize(st));
+  if (sym) t.P_rows = 0;                 // P was used as the half spectrum: its zero padding is gone
   all_conv = early && h_counters[0] <= 0;
   jmax = h_counters[1];
   if (all_conv) my_hint = jmax + 1;      // iterations 0..jmax: the final kernel then sees every row converged
@@ -800,7 +924,7 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
 
 void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void* minv, const void* b, void* x,
               int batch, double tol, int max_iter, int early_stopping, int batched_semantics, int x0_is_zero,
-              int* iters_completed, cudaStream_t st) {
+              int* iters_completed, cudaStream_t st, int hermitian) {
   EFGP_CHECK(batch >= 1, "batch must be >= 1");
   EFGP_CHECK(mode >= 0 && mode <= 3, "unknown operator mode");
   EFGP_CHECK(mode == kModeT || ws != nullptr, "ws is required for Gv / A_mean / A_var");
@@ -816,10 +940,10 @@ void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void*
     char* xx = (char*)x + (size_t)b0 * t.M * esz;
     if (t.dtype == 0)
       solve_group<float>(t, (const float*)ws, sigmasq, mode, (const float*)minv, bb, xx, nb, tol, max_iter,
-                         early_stopping, batched_semantics, x0_is_zero, all_conv, jmax, st);
+                         early_stopping, batched_semantics, x0_is_zero, all_conv, jmax, st, hermitian);
     else
       solve_group<double>(t, (const double*)ws, sigmasq, mode, (const double*)minv, bb, xx, nb, tol, max_iter,
-                          early_stopping, batched_semantics, x0_is_zero, all_conv, jmax, st);
+                          early_stopping, batched_semantics, x0_is_zero, all_conv, jmax, st, hermitian);
     int it_g = max_iter;
     if (all_conv) it_g = batched_semantics ? std::min(jmax + 2, max_iter) : jmax + 1;
     iters = std::max(iters, it_g);

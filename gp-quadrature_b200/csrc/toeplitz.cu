@@ -16,6 +16,7 @@ namespace efgp {
 
 Toeplitz::~Toeplitz() {
   if (vhat) pool_free(vhat);
+  if (vhat_real) pool_free(vhat_real);
 }
 
 struct TzGeom {
@@ -162,6 +163,43 @@ static void create_t(Toeplitz& t, const void* v, cudaStream_t st) {
     EFGP_CUFFT(cufftExecZ2Z(plan, (cufftDoubleComplex*)t.vhat, (cufftDoubleComplex*)t.vhat, CUFFT_FORWARD));
   tz_scale_kernel<C, T><<<div_up(t.Ftot, 256), 256, 0, st>>>((C*)t.vhat, t.Ftot, (T)(1.0 / (double)t.Ftot));
   EFGP_CUDA(cudaGetLastError());
+}
+
+// vhat holds the spectrum of the generator stored from index 0 (centre at c_a = n_a - 1); multiplying by
+// exp(+2 pi i f.c / F) moves the centre to the origin, where a Hermitian generator has a real spectrum.
+template <typename T>
+__global__ void tz_real_spectrum_kernel(const typename cplx_of<T>::type* __restrict__ vhat, TzGeom g,
+                                        T* __restrict__ out) {
+  int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= g.Ftot) return;
+  int64_t rem = f;
+  double re = 1.0, im = 0.0;
+  for (int a = g.dim - 1; a >= 0; --a) {
+    const int fa = (int)(rem % g.F[a]);
+    rem /= g.F[a];
+    const int64_t num = ((int64_t)fa * (g.n[a] - 1)) % g.F[a];      // exact phase index
+    double s, c;
+    sincospi(2.0 * (double)num / (double)g.F[a], &s, &c);
+    const double r2 = re * c - im * s;
+    im = re * s + im * c;
+    re = r2;
+  }
+  const typename cplx_of<T>::type h = vhat[f];
+  out[f] = (T)((double)h.x * re - (double)h.y * im);
+}
+
+const void* toeplitz_real_spectrum(Toeplitz& t, cudaStream_t st) {
+  if (t.vhat_real) return t.vhat_real;
+  TzGeom g = make_tz_geom(t);
+  const size_t esz = t.dtype == 0 ? 4 : 8;
+  t.vhat_real = pool_alloc(esz * (size_t)t.Ftot);
+  if (t.dtype == 0)
+    tz_real_spectrum_kernel<float><<<div_up(t.Ftot, 256), 256, 0, st>>>((const float2*)t.vhat, g, (float*)t.vhat_real);
+  else
+    tz_real_spectrum_kernel<double><<<div_up(t.Ftot, 256), 256, 0, st>>>((const double2*)t.vhat, g,
+                                                                         (double*)t.vhat_real);
+  EFGP_CUDA(cudaGetLastError());
+  return t.vhat_real;
 }
 
 void toeplitz_create(Toeplitz& t, const void* v, int dim, const int64_t* Ls, int dtype, int force_pow2,

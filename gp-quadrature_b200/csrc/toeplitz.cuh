@@ -12,6 +12,7 @@ struct Toeplitz {
   int64_t F[kMaxDim] = {1, 1, 1};   // FFT extents
   int64_t M = 1, Ftot = 1;
   void* vhat = nullptr;             // FFT of the zero-padded generator, pre-scaled by 1/Ftot
+  void* vhat_real = nullptr;        // real spectrum of the CENTRED generator (Hermitian v), built on first use
   DevBuf P, Q;                      // padded input (zeros persist), spectrum / output
   int64_t P_rows = 0;               // rows of P known to be zero outside the block
   DevBuf cg_vec, cg_scal;
@@ -26,9 +27,14 @@ void toeplitz_create(Toeplitz& t, const void* v, int dim, const int64_t* Ls, int
                      cudaStream_t st);
 void toeplitz_apply(Toeplitz& t, const void* x, int batch, const void* ws, double sigmasq, int mode, void* y,
                     cudaStream_t st);
+// hermitian != 0: the caller promises b[-k] = conj(b[k]) in the centred mode index for every row of b and x0 and
+// a Hermitian generator v (both hold for D F^* c with real c and an even real diagonal D): the cuFFT matvec then
+// runs as Z2D -> real multiply -> D2Z on half-size arrays.
 void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void* minv, const void* b, void* x,
               int batch, double tol, int max_iter, int early_stopping, int batched_semantics, int x0_is_zero,
-              int* iters_completed, cudaStream_t st);
+              int* iters_completed, cudaStream_t st, int hermitian = 0);
+// V[f] = (1 / Ftot) sum_j v[j] exp(-2 pi i f.j / F) over the centred generator index j: real when v[-j] = conj v[j].
+const void* toeplitz_real_spectrum(Toeplitz& t, cudaStream_t st);
 // lanczos.cu: `steps` lockstep Lanczos steps from the normalised start block q0 (overwritten); alphas / betas are
 // (batch, steps) doubles on the device.  Enqueues only (no synchronisation).
 void lanczos_tridiag(Toeplitz& t, const void* ws, double sigmasq, int mode, void* q0, int batch, int steps,

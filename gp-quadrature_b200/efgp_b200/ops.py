@@ -222,9 +222,10 @@ class ToeplitzPlan:
         return y.reshape(x.shape)
 
     def cg(self, b, x0, mode, ws, sigmasq, tol, max_iter=None, early_stopping=True, minv=None, batched=None,
-           x0_zero=False):
+           x0_zero=False, hermitian=False):
         """Solve A x = b for the fused operator `mode`; returns (x, iters_completed).  x0_zero=True promises that
-        x0 is all zeros (x0 may then be None): the library skips the matvec A x0."""
+        x0 is all zeros (x0 may then be None): the library skips the matvec A x0.  hermitian=True promises
+        b[-k] = conj(b[k]) (and the same for x0): the matvec then runs on real FFTs of half the size."""
         _require_cuda(b, "b")
         if batched is None:
             batched = b.ndim > 1
@@ -237,11 +238,11 @@ class ToeplitzPlan:
         mi = self._ws(minv)
         iters = ctypes.c_int(0)
         with _on(self.device):
-            check(_lib.lib().efgp_cg_solve(self._h, _ptr(w), float(sigmasq), int(mode), _ptr(mi), _ptr(bs), _ptr(x),
-                                           bs.shape[0], float(tol), -1 if max_iter is None else int(max_iter),
-                                           1 if early_stopping else 0, 1 if batched else 0, 1 if x0_zero else 0,
-                                           ctypes.byref(iters),
-                                           _stream(self.device)))
+            solve = _lib.lib().efgp_cg_solve_hermitian if hermitian else _lib.lib().efgp_cg_solve
+            check(solve(self._h, _ptr(w), float(sigmasq), int(mode), _ptr(mi), _ptr(bs), _ptr(x),
+                        bs.shape[0], float(tol), -1 if max_iter is None else int(max_iter),
+                        1 if early_stopping else 0, 1 if batched else 0, 1 if x0_zero else 0,
+                        ctypes.byref(iters), _stream(self.device)))
         return x.reshape(b.shape), int(iters.value)
 
     def lanczos(self, q, steps, mode, ws, sigmasq, breakdown_tol=1e-12):

@@ -351,6 +351,13 @@ def _zero_guess(like, dtype=None):
     return z
 
 
+def _hermitian(t):
+    """Tag a right-hand side D F^* c (c real, D an even real diagonal): b[-k] = conj b[k] in the centred mode index,
+    so ConjugateGradients may ask the library for the real-FFT matvec (efgp_cg_solve_hermitian)."""
+    t._efgp_hermitian = True
+    return t
+
+
 def _rademacher_like_reference(shape, rdtype, device):
     """+-1 probes drawn with the reference's calls `empty(shape).bernoulli_(0.5).mul_(2).sub_(1)`
     (efgpnd.py:179-181, 199-201), on PROBE_DEVICE if set, else on `device`."""
@@ -417,7 +424,7 @@ def compute_prediction_variance(x_new, xis, ws, A_var, cg_tol, max_cg_iter, vari
         out = []
         for xb in torch.split(x_new, 8192, dim=0):
             fx = torch.exp(2 * math.pi * 1j * (xb @ xis.T)).to(cdtype)
-            rhs = ws * fx.conj()
+            rhs = _hermitian(ws * fx.conj())            # conj(fx)[-k] = fx[k]: symmetric rows
             gamma = ConjugateGradients(A_var, rhs, x0=_zero_guess(rhs, cdtype), tol=cg_tol,
                                        max_iter=max_cg_iter, early_stopping=True).solve()
             out.append(torch.real((fx * (ws * gamma)).sum(dim=-1)).clamp_min(0.0))
@@ -549,11 +556,15 @@ def efgpnd_gradient_batched(
             Fy = nufft_op.type1(y, OUT).reshape(-1)
             rhs = ws * Fy
             warm = mean_cg_init is not None and mean_cg_init.shape == rhs.shape
+            if not y.is_complex() and (not warm or getattr(mean_cg_init, "_efgp_hermitian", False)):
+                _hermitian(rhs)                     # y real; a warm start from one of our own solutions is symmetric too
             mean_x0 = mean_cg_init.to(device=device, dtype=cdtype).clone() if warm else _zero_guess(rhs)
             cg_mean = ConjugateGradients(A_apply, rhs, mean_x0, tol=cg_tol, early_stopping=early_stopping,
                                          M_inv_apply=mean_M_inv)
             beta = cg_mean.solve()
             beta_raw = beta.detach().clone()
+            if getattr(rhs, "_efgp_hermitian", False):
+                beta_raw._efgp_hermitian = True
             z = nufft_op.type2(beta, OUT, scale=ws_r, real_out=True)          # Re F(ws beta)
             alpha = (y - z) / s2
 
@@ -593,15 +604,26 @@ def efgpnd_gradient_batched(
             else:
                 B_all_kernel = torch.empty((0, Tl, M), device=device, dtype=cdtype)
             B_noise = (ws * toeplitz(ws * Vl)).reshape(Tl, -1)
-            B_all = torch.cat((B_all_kernel, B_noise.unsqueeze(0)), dim=0).reshape((nk + 1) * Tl, -1)
+            rows_k = nk * Tl
             with rf("7_batch_cg_solve"):
-                cg_trace = ConjugateGradients(A_apply, B_all, _zero_guess(B_all), tol=cg_tol,
+                # The reference solves all (nk + 1) Tl rows in one batched call (efgpnd.py:203-212); rows are
+                # independent there (per-row alpha, beta and stopping), so the split below changes no row's iterates.
+                # The kernel-derivative rows ws T D' F^* Z (Z real) are Hermitian-symmetric in the mode index and take
+                # the real-FFT matvec; the noise rows (+-1 per MODE) are not and take the general one.
+                trace_iters_l = 0
+                if rows_k > 0:
+                    Bk = _hermitian(B_all_kernel.reshape(rows_k, -1))
+                    cg_k = ConjugateGradients(A_apply, Bk, _zero_guess(Bk), tol=cg_tol,
                                               early_stopping=early_stopping, M_inv_apply=trace_M_inv)
-                Beta_all = cg_trace.solve()
+                    Beta_kernel = cg_k.solve()
+                    trace_iters_l = int(cg_k.iters_completed)
+                else:
+                    Beta_kernel = B_all_kernel.reshape(0, M)
+                cg_n = ConjugateGradients(A_apply, B_noise, _zero_guess(B_noise), tol=cg_tol,
+                                          early_stopping=early_stopping, M_inv_apply=trace_M_inv)
+                Beta_noise = cg_n.solve()
+                trace_iters_l = max(trace_iters_l, int(cg_n.iters_completed))
             with rf("7.5_compute_alpha"):
-                rows_k = nk * Tl
-                Beta_kernel = Beta_all[:rows_k]
-                Beta_noise = Beta_all[rows_k:]
                 sums = torch.zeros(nk, Tl, device=device, dtype=rdtype)
                 if nk > 0:
                     # Alpha = (F(D'F*Z) - F(ws beta_k)) / sigma^2 = F(D'F*Z - ws beta_k) / sigma^2, real part only
@@ -613,7 +635,7 @@ def efgpnd_gradient_batched(
                             a_chunk = nufft_op.type2(rm, OUT, real_out=True).reshape(-1, N)
                             sums[slot, t0:t0 + a_chunk.shape[0]] = (Zl[t0:t0 + a_chunk.shape[0]] * a_chunk).sum(dim=1)
                 noise_sum = (Vl.conj() * Beta_noise).sum(dim=1).real.sum()
-            return sums.sum(dim=1), noise_sum, int(cg_trace.iters_completed), int(B_all.shape[0])
+            return sums.sum(dim=1), noise_sum, trace_iters_l, (nk + 1) * Tl
 
         with rf("6_monte_carlo_trace"):
             T = trace_samples
@@ -889,6 +911,8 @@ class EFGPND(nn.Module):
         ws._efgp_real_part = ws_r
         rhs = ws * Fy.reshape(-1)                                                # ws * F^* y
         v_kernel, rhs = _sum_over_shards(v_kernel, rhs, group)
+        if not y.is_complex():
+            _hermitian(rhs)                      # y real: symmetric system (a warm start from self._beta is one too)
         toeplitz = ToeplitzND(v_kernel, force_pow2=_TOEPLITZ_POW2)
         A_mean = create_A_mean(ws, toeplitz, s2, cdtype)
         center = tuple((s - 1) // 2 for s in v_kernel.shape)

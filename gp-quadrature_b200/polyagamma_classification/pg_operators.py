@@ -25,7 +25,7 @@ from typing import Callable
 import torch
 
 from cg import ConjugateGradients
-from efgpnd import NUFFT, ToeplitzND, compute_convolution_vector_vectorized_dD, _FusedOperator, _zero_guess
+from efgpnd import NUFFT, ToeplitzND, compute_convolution_vector_vectorized_dD, _FusedOperator, _hermitian, _zero_guess
 from efgp_b200 import ops as _ops
 from utils.kernels import get_xis
 
@@ -108,7 +108,7 @@ def _make_sigma_apply(spectral, delta, *, cg_tol, use_exact_weighted_toeplitz_op
         if vector_input:
             z = z.unsqueeze(0)
         zr = z.real if z.is_complex() else z
-        rhs = spectral.nufft_op.type1(zr, out_shape=spectral.out_shape, scale=ws_r).reshape(z.shape[0], -1)
+        rhs = _hermitian(spectral.nufft_op.type1(zr, out_shape=spectral.out_shape, scale=ws_r).reshape(z.shape[0], -1))
         cg = ConjugateGradients(A_feat, rhs, x0=_zero_guess(rhs), tol=cg_tol, max_iter=2000, early_stopping=True)
         x = cg.solve()
         info["cg_iters"] = int(cg.iters_completed)

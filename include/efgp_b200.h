@@ -99,6 +99,17 @@ int efgp_cg_solve(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, co
                   const void* b, void* x, int batch, double tol, int max_iter, int early_stopping,
                   int batched_semantics, int x0_is_zero, int* iters_completed, void* stream);
 
+/* efgp_cg_solve for right-hand sides that are Hermitian-symmetric in the centred mode index, b[-k] = conj(b[k]) for
+ * every row of b (and of x when x0_is_zero = 0), with a Hermitian generator v.  That is the case for every system the
+ * reference builds as D F^* c with real point values c and an even real diagonal D: the posterior-mean solve
+ * (efgpnd.py:786-812), the kernel-derivative probe rows of the gradient (efgpnd.py:183-197), the 'regular' variance rows
+ * (efgpnd.py:1805-1820).  The operator preserves the symmetry, the transform of the padded iterate is then real, and the
+ * matvec runs as C2R -> real multiply -> R2C on half-size arrays (blocks with odd extents; otherwise, and for the tiny
+ * blocks solved without cuFFT, this is efgp_cg_solve).  Same arguments, semantics and iteration counting. */
+int efgp_cg_solve_hermitian(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, const void* minv,
+                            const void* b, void* x, int batch, double tol, int max_iter, int early_stopping,
+                            int batched_semantics, int x0_is_zero, int* iters_completed, void* stream);
+
 /* ---- Lanczos: replaces the probe loop of logdet_slq (efgpnd.py:1719-1746), all probes in lockstep, for
  * operators of the four modes above (the reference uses A = I + Gv / sigma^2, mode 3).
  * q: (batch, M) complex start vectors z / ||z|| (efgpnd.py:1723), OVERWRITTEN (used as work space);

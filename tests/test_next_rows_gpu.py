@@ -170,3 +170,51 @@ def test_sample_gp_spectral_approx(tag, ns, cpu_probes):
     assert rel(s, g[f"sample_{tag}"]) < 1e-9
     with pytest.raises(ValueError):
         vs.sample_gp_spectral_approx(x, num_samples=0)
+
+
+# ----------------------------------------------------------------------------- real-FFT (Hermitian) CG path
+@pytest.mark.parametrize("d,m,rows,dt", [(1, 40, 6, torch.float64), (2, 12, 7, torch.float64), (3, 5, 9, torch.float64),
+                                         (2, 9, 1, torch.float64), (3, 4, 5, torch.float32), (2, 30, 6, torch.float32)])
+def test_cg_hermitian_path_matches_general_path(d, m, rows, dt):
+    """efgp_cg_solve_hermitian (C2R -> real multiply -> R2C on half-size arrays) against efgp_cg_solve on the same
+    Hermitian-symmetric right-hand sides: same iterates to rounding, same iteration counts, cold and warm start."""
+    import efgpnd
+    from efgp_b200 import ops
+    torch.manual_seed(d * 100 + m)
+    cdt = torch.complex128 if dt == torch.float64 else torch.complex64
+    N = 4000
+    x = (torch.rand(N, d, dtype=dt, device="cuda") * 2 - 1)
+    h = 0.4
+    v = efgpnd.compute_convolution_vector_vectorized_dD(m, x, h)
+    toep = efgpnd.ToeplitzND(v, force_pow2=False)
+    mt = 2 * m + 1
+    M = mt ** d
+    grid = torch.stack(torch.meshgrid(*([torch.arange(-m, m + 1, device="cuda", dtype=dt)] * d), indexing="ij"), -1)
+    ws = torch.exp(-0.02 * (grid ** 2).sum(-1)).reshape(-1)                    # even, real, positive
+    c = torch.randn(rows, N, dtype=dt, device="cuda")
+    b = efgpnd.NUFFT(x, torch.zeros(d, dtype=dt, device="cuda"), h, 1e-9 if dt == torch.float64 else 1e-5).type1(
+        c, (mt,) * d).reshape(rows, M) * ws
+    flip = torch.flip(b.reshape((rows,) + (mt,) * d), dims=tuple(range(1, d + 1))).reshape(rows, M)
+    assert rel(flip.conj(), b) < (1e-7 if dt == torch.float64 else 1e-3)       # the premise: b[-k] = conj b[k]
+    tol = 1e-9 if dt == torch.float64 else 1e-4
+    for mode, s2 in ((ops.MODE_A_MEAN, 0.3), (ops.MODE_A_VAR, 0.3)):
+        minv = 1.0 / (N * ws * ws + s2)
+        xg, itg = toep.plan.cg(b, None, mode, ws, s2, tol, minv=minv, x0_zero=True, hermitian=False)
+        xh, ith = toep.plan.cg(b, None, mode, ws, s2, tol, minv=minv, x0_zero=True, hermitian=True)
+        slack = 1 if dt == torch.float64 else max(1, itg // 50)      # fp32 rounding moves long solves by a few iterations
+        assert abs(itg - ith) <= slack
+        # fp32: two rounding-different trajectories agree to ~eps32 x condition number (~1e4 here)
+        assert rel(xh, xg) < (1e-8 if dt == torch.float64 else 1e-2)
+        op = efgpnd._FusedOperator(ws.to(cdt), toep, s2, mode, cdt)
+        assert rel(op(xh), b) < 10 * tol                                        # it solves the system
+        # warm start from a (symmetric) nearby point: same trajectory on both paths
+        x0 = xg * 0.9
+        xw, itw = toep.plan.cg(b, x0, mode, ws, s2, tol, minv=minv, hermitian=True)
+        xv, itv = toep.plan.cg(b, x0, mode, ws, s2, tol, minv=minv, hermitian=False)
+        assert abs(itw - itv) <= slack
+        assert rel(xw, xv) < (1e-8 if dt == torch.float64 else 1e-2)
+    # the general path still works on the same plan afterwards (the padded buffer is re-zeroed)
+    u = torch.randn(3, M, dtype=cdt, device="cuda")
+    y1 = toep(u)
+    dense = efgpnd.ToeplitzND(v, force_pow2=True)(u)
+    assert rel(y1, dense) < (1e-11 if dt == torch.float64 else 1e-4)
