@@ -822,8 +822,8 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   // which the remaining iterations are launch-bound.  Solves of the same kind (operator mode, single/batched)
   // repeat with nearly the same iteration count in the EFGP loop, so the first check is scheduled where the
   // previous such solve stopped; iterations past convergence are no-ops (rows are frozen on the device).
-  static int hint[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
-  int& my_hint = hint[mode][batched ? 1 : 0];
+  static int hint[4][2][2] = {};         // per operator mode, single/batched, general/Hermitian matvec
+  int& my_hint = hint[mode][batched ? 1 : 0][sym ? 1 : 0];
   int it = 0;
   int check = my_hint > 0 ? std::min(my_hint, 64) : 4;
   bool first = true;
