@@ -48,5 +48,8 @@ def run(tag, N, d, kernel, eps, rows, s2, tol):
 
 
 if __name__ == "__main__":
-    run("config2_grid", 100_000, 2, Matern(dimension=2, init_lengthscale=0.2, init_variance=1.0, nu=1.5), 1e-4, 256, 0.04, 1e-5)
-    run("config4_grid", 10_000_000, 3, SquaredExponential(dimension=3, init_lengthscale=0.1, init_variance=1.0), 1e-4, 64, 0.04, 1e-5)
+    which = sys.argv[1:] or ["2", "4"]
+    if "2" in which:
+        run("config2_grid", 100_000, 2, Matern(dimension=2, init_lengthscale=0.2, init_variance=1.0, nu=1.5), 1e-4, 256, 0.04, 1e-5)
+    if "4" in which:
+        run("config4_grid", 10_000_000, 3, SquaredExponential(dimension=3, init_lengthscale=0.1, init_variance=1.0), 1e-4, 64, 0.04, 1e-5)
