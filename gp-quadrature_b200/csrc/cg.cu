@@ -278,11 +278,22 @@ cg_symmetrize_kernel(typename cplx_of<T>::type* __restrict__ v, int64_t M) {
 template <typename T>
 __global__ void __launch_bounds__(256)
 cg_Mr_kernel(T* __restrict__ R, const T* __restrict__ vr, int64_t Ftot, const int* __restrict__ act) {
+  using V2 = typename cplx_of<T>::type;      // two reals per access (rows start 16-byte aligned when Ftot is even)
   int row = blockIdx.y;
   if (!act[row]) return;
-  int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t f = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 2;
   if (f >= Ftot) return;
-  R[(int64_t)row * Ftot + f] *= vr[f];
+  T* base = R + (int64_t)row * Ftot;
+  if ((Ftot & 1) == 0) {
+    V2 a = *reinterpret_cast<V2*>(base + f);
+    const V2 h = *reinterpret_cast<const V2*>(vr + f);
+    a.x *= h.x;
+    a.y *= h.y;
+    *reinterpret_cast<V2*>(base + f) = a;
+  } else {
+    base[f] *= vr[f];
+    if (f + 1 < Ftot) base[f + 1] *= vr[f + 1];
+  }
 }
 
 template <typename T>
@@ -882,7 +893,7 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
         else
           EFGP_CUFFT(cufftExecZ2D(pl, (cufftDoubleComplex*)H, (cufftDoubleReal*)R));
       }
-      cg_Mr_kernel<T><<<gf, 256, 0, st>>>(R, vreal, t.Ftot, s.act + (it & 1) * B);
+      cg_Mr_kernel<T><<<dim3(div_up((t.Ftot + 1) / 2, 256), B), 256, 0, st>>>(R, vreal, t.Ftot, s.act + (it & 1) * B);
       {
         cufftHandle pl = global_fft().get(t.dim, t.F, sizeof(T) == 4 ? CUFFT_R2C : CUFFT_D2Z, B, st);
         if (sizeof(T) == 4)

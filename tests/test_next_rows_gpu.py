@@ -174,7 +174,8 @@ def test_sample_gp_spectral_approx(tag, ns, cpu_probes):
 
 # ----------------------------------------------------------------------------- real-FFT (Hermitian) CG path
 @pytest.mark.parametrize("d,m,rows,dt", [(1, 40, 6, torch.float64), (2, 12, 7, torch.float64), (3, 5, 9, torch.float64),
-                                         (2, 9, 1, torch.float64), (3, 4, 5, torch.float32), (2, 30, 6, torch.float32)])
+                                         (2, 9, 1, torch.float64), (3, 4, 5, torch.float32), (2, 30, 6, torch.float32),
+                                         (2, 6, 6, torch.float64)])       # 4m+1 = 25: odd FFT extents
 def test_cg_hermitian_path_matches_general_path(d, m, rows, dt):
     """efgp_cg_solve_hermitian (C2R -> real multiply -> R2C on half-size arrays) against efgp_cg_solve on the same
     Hermitian-symmetric right-hand sides: same iterates to rounding, same iteration counts, cold and warm start."""
