@@ -37,7 +37,19 @@ class ConjugateGradients:
         self.max_iter = max_iter
         self.early_stopping = early_stopping
         self.M_inv_apply = M_inv_apply
-        self.iters_completed = 0
+        self._iters = 0
+
+    @property
+    def iters_completed(self):
+        """Iterations of the last solve (cg.py:152, 243).  A solve that the library only enqueued (one cooperative
+        kernel, no host decisions) reports it lazily: reading the attribute waits for that solve."""
+        if not isinstance(self._iters, int):
+            self._iters = int(self._iters)
+        return self._iters
+
+    @iters_completed.setter
+    def iters_completed(self, value):
+        self._iters = value
 
     # ------------------------------------------------------------------ dispatch
     def _fused(self):
@@ -59,8 +71,8 @@ class ConjugateGradients:
                                         max_iter=self.max_iter, early_stopping=self.early_stopping,
                                         minv=minv, batched=self.is_batched,
                                         x0_zero=self._x0_zero,
-                                        hermitian=bool(getattr(self.b, "_efgp_hermitian", False)))
-            self.iters_completed = it
+                                        hermitian=bool(getattr(self.b, "_efgp_hermitian", False)), lazy_iters=True)
+            self._iters = it                    # a LazyIters: resolved when iters_completed is read
             return x
         return self._solve_batched() if self.is_batched else self._solve_single()
 

@@ -225,6 +225,16 @@ int efgp_cg_solve_hermitian(efgp_toeplitz* t, const void* ws, double sigmasq, in
   })
 }
 
+int efgp_cg_solve_async(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, const void* minv, const void* b,
+                        void* x, int batch, double tol, int max_iter, int early_stopping, int batched_semantics,
+                        int x0_is_zero, int hermitian, int* counters_pinned, int* iters_completed, void* stream) {
+  EFGP_TRY({
+    EFGP_CHECK(t != nullptr && b != nullptr && x != nullptr && counters_pinned != nullptr, "null argument");
+    efgp::cg_solve(t->t, ws, sigmasq, mode, minv, b, x, batch, tol, max_iter, early_stopping,
+                   batched_semantics, x0_is_zero, iters_completed, (cudaStream_t)stream, hermitian, counters_pinned);
+  })
+}
+
 int efgp_lanczos(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, void* q, int batch, int steps,
                  double breakdown_tol, double* alphas, double* betas, void* stream) {
   EFGP_TRY({

@@ -723,7 +723,7 @@ __global__ void __launch_bounds__(256) cg_final_kernel(int it, double tol, int e
 template <typename T>
 static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, const T* minv, const void* b_, void* x_,
                         int B, double tol, int max_iter, int early, int batched, int x0_zero, int& all_conv, int& jmax,
-                        cudaStream_t st, int hermitian) {
+                        cudaStream_t st, int hermitian, int* async_counters) {
   using C = typename cplx_of<T>::type;
   const int64_t M = t.M;
   TzGeomC g;
@@ -863,6 +863,11 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
       void* args[] = {(void*)&a};
       stg.add_launches(1);
       EFGP_CUDA(cudaLaunchCooperativeKernel((void*)cg_persist_kernel<T>, dim3(ctas), dim3(256), args, 0, st));
+      if (async_counters) {      // the whole solve is on the stream: hand the counters over without waiting for it
+        EFGP_CUDA(cudaMemcpyAsync(async_counters, s.counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+        all_conv = -1;
+        return;
+      }
       EFGP_CUDA(cudaMemcpyAsync(h_counters, s.counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
       EFGP_CUDA(cudaStreamSynchronize(st));
       all_conv = early && h_counters[0] <= 0;
@@ -935,7 +940,7 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
 
 void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void* minv, const void* b, void* x,
               int batch, double tol, int max_iter, int early_stopping, int batched_semantics, int x0_is_zero,
-              int* iters_completed, cudaStream_t st, int hermitian) {
+              int* iters_completed, cudaStream_t st, int hermitian, int* async_counters) {
   EFGP_CHECK(batch >= 1, "batch must be >= 1");
   EFGP_CHECK(mode >= 0 && mode <= 3, "unknown operator mode");
   EFGP_CHECK(mode == kModeT || ws != nullptr, "ws is required for Gv / A_mean / A_var");
@@ -944,6 +949,9 @@ void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void*
   size_t esz = t.dtype == 0 ? 8 : 16;
   int group = (int)std::max<int64_t>(1, std::min<int64_t>(batch, (int64_t)((12ull << 30) / ((size_t)t.Ftot * esz))));
   int iters = 0;
+  bool all_conv_all = true;
+  int jmax_all = -1;
+  int* async_one = (async_counters && batch <= group) ? async_counters : nullptr;   // one group: may stay asynchronous
   for (int b0 = 0; b0 < batch; b0 += group) {
     int nb = std::min(group, batch - b0);
     int all_conv = 0, jmax = -1;
@@ -951,15 +959,25 @@ void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void*
     char* xx = (char*)x + (size_t)b0 * t.M * esz;
     if (t.dtype == 0)
       solve_group<float>(t, (const float*)ws, sigmasq, mode, (const float*)minv, bb, xx, nb, tol, max_iter,
-                         early_stopping, batched_semantics, x0_is_zero, all_conv, jmax, st, hermitian);
+                         early_stopping, batched_semantics, x0_is_zero, all_conv, jmax, st, hermitian, async_one);
     else
       solve_group<double>(t, (const double*)ws, sigmasq, mode, (const double*)minv, bb, xx, nb, tol, max_iter,
-                          early_stopping, batched_semantics, x0_is_zero, all_conv, jmax, st, hermitian);
+                          early_stopping, batched_semantics, x0_is_zero, all_conv, jmax, st, hermitian, async_one);
+    if (all_conv < 0) {                  // enqueued only: the counters arrive in async_counters with the stream
+      if (iters_completed) *iters_completed = -1;
+      return;
+    }
+    all_conv_all = all_conv_all && all_conv;
+    jmax_all = std::max(jmax_all, jmax);
     int it_g = max_iter;
     if (all_conv) it_g = batched_semantics ? std::min(jmax + 2, max_iter) : jmax + 1;
     iters = std::max(iters, it_g);
   }
   if (iters_completed) *iters_completed = iters;
+  if (async_counters) {                  // the solve ran synchronously: same hand-over format
+    async_counters[0] = all_conv_all ? 0 : 1;
+    async_counters[1] = jmax_all;
+  }
 }
 
 }  // namespace efgp

@@ -32,7 +32,10 @@ void toeplitz_apply(Toeplitz& t, const void* x, int batch, const void* ws, doubl
 // runs as Z2D -> real multiply -> D2Z on half-size arrays.
 void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void* minv, const void* b, void* x,
               int batch, double tol, int max_iter, int early_stopping, int batched_semantics, int x0_is_zero,
-              int* iters_completed, cudaStream_t st, int hermitian = 0);
+              int* iters_completed, cudaStream_t st, int hermitian = 0, int* async_counters = nullptr);
+// async_counters (pinned host int[2], optional): when the solve runs as ONE cooperative kernel the call returns without
+// synchronising, *iters_completed = -1, and the stream delivers {rows still active, last converging iteration}
+// there; otherwise the call is synchronous and fills the same two ints itself.
 // V[f] = (1 / Ftot) sum_j v[j] exp(-2 pi i f.j / F) over the centred generator index j: real when v[-j] = conj v[j].
 const void* toeplitz_real_spectrum(Toeplitz& t, cudaStream_t st);
 // lanczos.cu: `steps` lockstep Lanczos steps from the normalised start block q0 (overwritten); alphas / betas are

@@ -43,6 +43,9 @@ _SIGNATURES = {
     "efgp_cg_solve_hermitian": (ctypes.c_int, [vp, vp, ctypes.c_double, ctypes.c_int, vp, vp, vp, ctypes.c_int,
                                                ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                                c_intp, vp]),
+    "efgp_cg_solve_async": (ctypes.c_int, [vp, vp, ctypes.c_double, ctypes.c_int, vp, vp, vp, ctypes.c_int,
+                                           ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                           ctypes.c_int, vp, c_intp, vp]),
     "efgp_lanczos": (ctypes.c_int, [vp, vp, ctypes.c_double, ctypes.c_int, vp, ctypes.c_int, ctypes.c_int,
                                     ctypes.c_double, vp, vp, vp]),
 }

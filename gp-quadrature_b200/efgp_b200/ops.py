@@ -169,6 +169,65 @@ class NufftPlan:
         return out if batched else out.reshape(self.N)
 
 
+class LazyIters:
+    """Iteration count of a solve that was only enqueued (efgp_cg_solve_async): int(obj) waits for the stream to
+    deliver the two convergence counters into pinned host memory and applies the reference's counting rule."""
+    _ring, _owners, _next = None, [None] * 64, 0
+
+    def __init__(self, device, max_iter, batched, early):
+        cls = LazyIters
+        if cls._ring is None:
+            cls._ring = torch.zeros((64, 2), dtype=torch.int32).pin_memory()
+        slot = cls._next
+        cls._next = (slot + 1) % 64
+        prev = cls._owners[slot]
+        if prev is not None:
+            prev.resolve()                       # the slot is about to be reused
+        cls._owners[slot] = self
+        self._buf = cls._ring[slot]
+        self._slot = slot
+        self._device, self._max_iter, self._batched, self._early = device, int(max_iter), bool(batched), bool(early)
+        self._event = None
+        self._value = None
+
+    @property
+    def ptr(self):
+        return ctypes.c_void_p(self._buf.data_ptr())
+
+    def enqueued(self):
+        self._event = torch.cuda.Event()
+        self._event.record(torch.cuda.current_stream(self._device))
+
+    def set(self, value):
+        self._value = int(value)
+        LazyIters._owners[self._slot] = None
+
+    def resolve(self):
+        if self._value is None:
+            self._event.synchronize()
+            active, jmax = int(self._buf[0]), int(self._buf[1])
+            if self._early and active <= 0:
+                v = min(jmax + 2, self._max_iter) if self._batched else jmax + 1
+            else:
+                v = self._max_iter
+            self.set(v)
+        return self._value
+
+    def __int__(self):
+        return self.resolve()
+
+    __index__ = __int__
+
+    def __eq__(self, other):
+        return int(self) == other
+
+    def __hash__(self):
+        return hash(int(self))
+
+    def __repr__(self):
+        return str(int(self))
+
+
 class ToeplitzPlan:
     """Cached spectrum of the zero-padded F^H F generator v ((4m+1)^d complex)."""
 
@@ -222,10 +281,12 @@ class ToeplitzPlan:
         return y.reshape(x.shape)
 
     def cg(self, b, x0, mode, ws, sigmasq, tol, max_iter=None, early_stopping=True, minv=None, batched=None,
-           x0_zero=False, hermitian=False):
+           x0_zero=False, hermitian=False, lazy_iters=False):
         """Solve A x = b for the fused operator `mode`; returns (x, iters_completed).  x0_zero=True promises that
         x0 is all zeros (x0 may then be None): the library skips the matvec A x0.  hermitian=True promises
-        b[-k] = conj(b[k]) (and the same for x0): the matvec then runs on real FFTs of half the size."""
+        b[-k] = conj(b[k]) (and the same for x0): the matvec then runs on real FFTs of half the size.
+        lazy_iters=True: the second result is a LazyIters; when the solve runs as one cooperative kernel the call
+        does not synchronise and the count is read only when somebody asks for it."""
         _require_cuda(b, "b")
         if batched is None:
             batched = b.ndim > 1
@@ -237,6 +298,20 @@ class ToeplitzPlan:
         w = self._ws(ws)
         mi = self._ws(minv)
         iters = ctypes.c_int(0)
+        if lazy_iters:
+            mi_host = 2 * self.size if max_iter is None else int(max_iter)
+            lz = LazyIters(self.device, mi_host, batched, early_stopping)
+            with _on(self.device):
+                check(_lib.lib().efgp_cg_solve_async(self._h, _ptr(w), float(sigmasq), int(mode), _ptr(mi), _ptr(bs),
+                                                     _ptr(x), bs.shape[0], float(tol), mi_host,
+                                                     1 if early_stopping else 0, 1 if batched else 0,
+                                                     1 if x0_zero else 0, 1 if hermitian else 0, lz.ptr,
+                                                     ctypes.byref(iters), _stream(self.device)))
+                if iters.value < 0:
+                    lz.enqueued()
+                else:
+                    lz.set(iters.value)
+            return x.reshape(b.shape), lz
         with _on(self.device):
             solve = _lib.lib().efgp_cg_solve_hermitian if hermitian else _lib.lib().efgp_cg_solve
             check(solve(self._h, _ptr(w), float(sigmasq), int(mode), _ptr(mi), _ptr(bs), _ptr(x),

@@ -351,6 +351,44 @@ def _zero_guess(like, dtype=None):
     return z
 
 
+class _LazyStats(dict):
+    """Statistics dict whose values may still be on their way from the device (ops.LazyIters): they turn into plain
+    ints the first time anybody looks."""
+
+    def _settle(self):
+        for k, v in list(dict.items(self)):
+            if isinstance(v, _ops.LazyIters):
+                dict.__setitem__(self, k, int(v))
+
+    def __getitem__(self, k):
+        self._settle()
+        return dict.__getitem__(self, k)
+
+    def get(self, k, default=None):
+        self._settle()
+        return dict.get(self, k, default)
+
+    def __iter__(self):                 # also keeps dict.update(stats) off CPython's raw-copy fast path
+        self._settle()
+        return dict.__iter__(self)
+
+    def items(self):
+        self._settle()
+        return dict.items(self)
+
+    def values(self):
+        self._settle()
+        return dict.values(self)
+
+    def copy(self):
+        self._settle()
+        return dict(self)
+
+    def __repr__(self):
+        self._settle()
+        return dict.__repr__(self)
+
+
 def _hermitian(t):
     """Tag a right-hand side D F^* c (c real, D an even real diagonal): b[-k] = conj b[k] in the centred mode index,
     so ConjugateGradients may ask the library for the real-FFT matvec (efgp_cg_solve_hermitian)."""
@@ -926,8 +964,9 @@ class EFGPND(nn.Module):
             beta_x0 = _zero_guess(rhs, cdtype)
         solver = ConjugateGradients(A_mean, rhs, x0=beta_x0, tol=cg_tol, early_stopping=True, M_inv_apply=mean_M_inv)
         beta = solver.solve()
-        self.last_fit_stats = {"mean_cg_iters": int(solver.iters_completed), "mtot": int(mtot), "h": h_float,
-                               "feature_count": int(ws.numel())}
+        # the iteration count stays lazy: predict() can enqueue its type-2 behind the solve instead of waiting for it
+        self.last_fit_stats = _LazyStats({"mean_cg_iters": solver._iters, "mtot": int(mtot), "h": h_float,
+                                          "feature_count": int(ws.numel())})
         ws._efgp_real = True
         self._beta = beta
         self._xis = xis

@@ -110,6 +110,19 @@ int efgp_cg_solve_hermitian(efgp_toeplitz* t, const void* ws, double sigmasq, in
                             const void* b, void* x, int batch, double tol, int max_iter, int early_stopping,
                             int batched_semantics, int x0_is_zero, int* iters_completed, void* stream);
 
+/* efgp_cg_solve without the host synchronisation where the solve does not need the host: small 2-D blocks with <= 4
+ * right-hand sides (the posterior-mean system of a fit) run as ONE cooperative kernel that takes every convergence
+ * decision on the device; the call then returns at once with *iters_completed = -1 and the stream later writes
+ * counters_pinned[0] = rows still active (<= 0: all converged) and counters_pinned[1] = index j of the last converging
+ * iteration into the caller's PINNED host ints, from which iters_completed = all converged ? (batched_semantics ?
+ * min(j + 2, max_iter) : j + 1) : max_iter (cg.py:132-153, 198-244).  x is valid in stream order.  Every other solve
+ * runs synchronously exactly like efgp_cg_solve / efgp_cg_solve_hermitian (hermitian != 0), sets *iters_completed
+ * and fills the two ints itself.  This lets the caller enqueue the type-2 transform of predict() behind the solve
+ * instead of idling the GPU while the host learns an iteration count it only reports (efgpnd.py:805-812, 922). */
+int efgp_cg_solve_async(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, const void* minv, const void* b,
+                        void* x, int batch, double tol, int max_iter, int early_stopping, int batched_semantics,
+                        int x0_is_zero, int hermitian, int* counters_pinned, int* iters_completed, void* stream);
+
 /* ---- Lanczos: replaces the probe loop of logdet_slq (efgpnd.py:1719-1746), all probes in lockstep, for
  * operators of the four modes above (the reference uses A = I + Gv / sigma^2, mode 3).
  * q: (batch, M) complex start vectors z / ||z|| (efgpnd.py:1723), OVERWRITTEN (used as work space);
