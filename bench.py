@@ -144,6 +144,64 @@ def workload_config(args, world, mtot=None):
 
 
 # ----------------------------------------------------------------------------- clocks
+class NvmlClockSampler:
+    """SM clock / throttle reasons sampled through NVML every 5 ms from a thread: the timed region of a sharded run is
+    only tens of milliseconds, shorter than the start-up of an `nvidia-smi -lms` process (ClockSampler below, kept as
+    the fallback when pynvml is missing)."""
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
+
+    def __init__(self, gpu_index):
+        import threading
+        import pynvml
+        pynvml.nvmlInit()
+        self.nv = pynvml
+        self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        self.sm, self.pw, self.reasons = [], [], set()
+        self._stop = threading.Event()
+        self._sample()
+        self.sm.clear()                   # the probe sample above is outside the timed region
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+
+    def _sample(self):
+        nv = self.nv
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        try:
+            self.pw.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+        except Exception:
+            pass
+        try:
+            get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            mask = int(get(self.h))
+            for bit, name in self.REASONS:
+                if mask & bit:
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def _run(self):
+        while not self._stop.is_set():
+            self._sample()
+            self._stop.wait(0.005)
+
+    def stop(self):
+        self._stop.set()
+        self.t.join(timeout=2)
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.mx, "reasons": ["no samples"]}
+        hi = sorted(self.sm)[len(self.sm) // 2:]            # samples under load = the upper half
+        return {"sm_mhz": sorted(hi)[len(hi) // 2], "sm_max_mhz": self.mx, "reasons": sorted(self.reasons),
+                "samples": len(self.sm), "power_w_max": max(self.pw) if self.pw else None, "source": "nvml"}
+
+
+def make_clock_sampler(gpu_index):
+    try:
+        return NvmlClockSampler(gpu_index)
+    except Exception:
+        return ClockSampler(gpu_index)
+
+
 class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
@@ -303,7 +361,7 @@ def main():
     barrier()
 
     # ---- device-resident timing (value) with per-stage timing inside the library
-    sampler = ClockSampler(local) if rank == 0 else None
+    sampler = make_clock_sampler(local) if rank == 0 else None
     _lib.timing_enable(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
