@@ -749,12 +749,10 @@ class EFGPND(nn.Module):
         super().__init__()
         if not x.is_cuda:
             raise EfgpError("EFGPND needs CUDA tensors: the EFGP hot path has no CPU fallback")
-        self.x = x
-        self.y = y
-        self.device = x.device
-        self.eps = eps
-        self.nufft_eps = nufft_eps
-        self.opts = {} if opts is None else opts.copy()
+        # plain (non-Parameter, non-Module) attributes go straight into __dict__, which is where nn.Module.__setattr__
+        # would put them after ~5 us of isinstance checks each: the constructor sits on the step's critical path
+        self.__dict__.update(x=x, y=y, device=x.device, eps=eps, nufft_eps=nufft_eps,
+                             opts={} if opts is None else opts.copy())
         dimension = 1 if x.ndim == 1 else x.shape[1]
         if isinstance(kernel, str):
             from kernels.squared_exponential import SquaredExponential
@@ -790,16 +788,9 @@ class EFGPND(nn.Module):
                 self.kernel._gp_params_ref = self._gp_params
         finally:
             torch.set_default_dtype(prev)
-        self._beta = None
-        self._xis = None
-        self._ws = None
-        self._ws_real = None
-        self._toeplitz = None
-        self._fitted = False
-        self._cached_params = {}
-        self._registered_optimizers = []
-        self.last_gradient_stats = {}
-        self._last_gradient_beta = None
+        self.__dict__.update(_beta=None, _xis=None, _ws=None, _ws_real=None, _toeplitz=None, _fitted=False,
+                             _cached_params={}, _registered_optimizers=[], last_gradient_stats={},
+                             _last_gradient_beta=None)
         self._update_param_cache()
 
     # ------------------------------------------------------------------ parameter bookkeeping
@@ -968,13 +959,10 @@ class EFGPND(nn.Module):
         self.last_fit_stats = _LazyStats({"mean_cg_iters": solver._iters, "mtot": int(mtot), "h": h_float,
                                           "feature_count": int(ws.numel())})
         ws._efgp_real = True
-        self._beta = beta
-        self._xis = xis
-        self._ws = ws
-        self._ws_real = A_mean.ws_real          # contiguous real weights, reused by predict's fused type-2 scaling
-        self._toeplitz = toeplitz
-        self._fitted = True
-        self._fit_params = now            # the hypers do not change during a fit: no second read-out after the solve
+        # _ws_real: contiguous real weights, reused by predict's fused type-2 scaling; _fit_params: the hypers do not
+        # change during a fit, so there is no second read-out after the solve
+        self.__dict__.update(_beta=beta, _xis=xis, _ws=ws, _ws_real=A_mean.ws_real, _toeplitz=toeplitz, _fitted=True,
+                             _fit_params=now)
         self._cached_params.update(now)
 
     # ------------------------------------------------------------------ predict
