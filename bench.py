@@ -13,9 +13,13 @@ Multi-GPU (torchrun, one rank per GPU): the N points are sharded over the ranks 
 total N fixed), each rank spreads its shard, ONE NCCL all-reduce sums the two mode grids, every
 rank solves the same M x M system and interpolates at its own points.
 
-`--impl reference` times the reference's CPU path (the oracle's restatement of efgpnd.py with the
-C/OpenMP NUFFT of oracle/cnufft.c standing in for FINUFFT, which is not installable here) on a
-bounded sample of the same workload, on all host cores.
+`--impl reference` times the reference's CPU path on a bounded sample of the same workload, on all host
+cores: the UNMODIFIED reference modules (oracle/_ref, copied there by oracle/make_ref.sh) with the C/OpenMP
+ES-kernel NUFFT of oracle/cnufft.c under the `pytorch_finufft` name (FINUFFT is not installable here); if
+oracle/_ref is missing it falls back to the oracle's restatement of efgpnd.py (kind "port").
+
+`--workload config4` times BASELINE.json configs[3] instead: one 3-D SE hyperparameter-gradient step at N = 1e7
+with 64 Hutchinson probes, the probes sharded over the GPUs (scalar all-reduce).
 """
 import argparse
 import json
@@ -43,9 +47,12 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--npts", type=float, default=1e8, help="total number of points (all ranks)")
-    ap.add_argument("--cpu-sample", type=float, default=4e6, help="points in the CPU-baseline sample")
+    ap.add_argument("--cpu-sample", type=float, default=1e7, help="points in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the full-size oracle comparison after the timing")
+    ap.add_argument("--workload", default="config3", choices=["config3", "config4"])
+    ap.add_argument("--probes", type=int, default=64, help="config4: Hutchinson probes per gradient step")
     return ap.parse_args()
 
 
@@ -62,6 +69,22 @@ def synth(n, d, seed, device, dtype):
     return x, y
 
 
+CHUNK = 1 << 20
+
+
+def synth_range(lo, hi, d, device, dtype, seed=1000):
+    """Points [lo, hi) of ONE seeded data set (chunk c of 2^20 points comes from seed + c), so that every rank of
+    an N-GPU run holds a slice of the data the 1-GPU run solves and the results can be compared."""
+    import torch
+    xs, ys = [], []
+    for c in range(lo // CHUNK, (max(hi, lo + 1) - 1) // CHUNK + 1):
+        x, y = synth(CHUNK, d, seed + c, device, dtype)
+        a, b = max(lo, c * CHUNK) - c * CHUNK, min(hi, (c + 1) * CHUNK) - c * CHUNK
+        xs.append(x[a:b])
+        ys.append(y[a:b])
+    return torch.cat(xs), torch.cat(ys)
+
+
 # ----------------------------------------------------------------------------- CPU reference arm
 def _host_threads():
     try:
@@ -70,67 +93,114 @@ def _host_threads():
         return os.cpu_count() or 1
 
 
-def cpu_solve_step(x, y):
-    """One posterior-mean solve with the oracle's restatement of the reference + the fast CPU NUFFT."""
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
+
+
+def _cpu_arm_setup():
+    """Returns (kind, solve) for the CPU arm.  kind "reference": the UNMODIFIED reference modules in oracle/_ref
+    (EFGPND(...).predict, efgpnd.py:824-972) with the C/OpenMP NUFFT under the pytorch_finufft name; kind "port": the
+    oracle's restatement of the same algebra when oracle/_ref is absent.  Must run in a process that has NOT imported
+    the product package (same module names)."""
     import torch
+    threads = _host_threads()
+    torch.set_num_threads(threads)            # also under torchrun, which exports OMP_NUM_THREADS=1
+    oracle_dir = os.path.join(ROOT, "oracle")
+    if os.path.exists(os.path.join(REF_DIR, "efgpnd.py")):
+        for mod in ("efgpnd", "cg", "kernels", "utils"):
+            assert mod not in sys.modules, f"{mod} already imported: the reference arm needs its own process"
+        sys.path[:] = [pth for pth in sys.path if os.path.abspath(pth or ".") not in (PKG, ROOT)]
+        sys.path.insert(0, REF_DIR)
+        sys.path.insert(0, os.path.join(oracle_dir, "fast_shim"))
+        sys.path.append(oracle_dir)
+        import fast_nufft as F
+        F.NTHREADS = threads
+        import io
+        import contextlib
+        import warnings
+        warnings.filterwarnings("ignore")
+        import efgpnd as R
+        from kernels.squared_exponential import SquaredExponential
+
+        def solve(x, y):
+            kern = SquaredExponential(dimension=2, init_lengthscale=ELL, init_variance=VAR)
+            with contextlib.redirect_stdout(io.StringIO()):
+                m = R.EFGPND(x, y, kern, sigmasq=SIG2, eps=EPS, nufft_eps=NUFFT_EPS, opts={"cg_tolerance": CG_TOL},
+                             estimate_params=False)
+                mean, _ = m.predict(x, return_variance=False)
+            return int(round(m._xis.shape[0] ** 0.5)), mean
+
+        return "reference", solve
+    sys.path.insert(0, oracle_dir)
     import efgp_oracle as O
     import fast_nufft as F
-    # all host cores, also under torchrun (which exports OMP_NUM_THREADS=1)
-    F.NTHREADS = _host_threads()
-    torch.set_num_threads(_host_threads())
-    kern = O.OracleKernel("se", 2, ELL, VAR)
-    f = O.fit(x, y, kern, SIG2, EPS, NUFFT_EPS, cg_tol=CG_TOL, backend=F)
-    mean = O.predict_mean(f, x, NUFFT_EPS, backend=F)
-    return f, mean
+    F.NTHREADS = threads
 
+    def solve(x, y):
+        kern = O.OracleKernel("se", 2, ELL, VAR)
+        f = O.fit(x, y, kern, SIG2, EPS, NUFFT_EPS, cg_tol=CG_TOL, backend=F)
+        return f.mtot, O.predict_mean(f, x, NUFFT_EPS, backend=F)
 
-def cpu_baseline(n_sample, reps):
-    import torch
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import fast_nufft as F
-    x, y = synth(int(n_sample), 2, 1234, "cpu", torch.float64)
-    cpu_solve_step(x[:20000], y[:20000])  # warm the libraries
-    best = float("inf")
-    for _ in range(reps):
-        t0 = time.perf_counter()
-        f, _ = cpu_solve_step(x, y)
-        best = min(best, time.perf_counter() - t0)
-    cores = _host_threads()
-    return {"value": n_sample / best / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{int(n_sample)} of the workload's points, full solve (2 type-1, CG {f.iters} its, 1 type-2), "
-                      f"best of {reps}; oracle restatement of efgpnd.py + C/OpenMP ES-kernel NUFFT (FINUFFT absent)",
-            "seconds": best, "os_cpu_count": os.cpu_count()}
+    return "port", solve
 
 
 def run_reference(args):
+    """CPU arm: K timed posterior-mean solves of a bounded sample of the workload on all host cores, preceded by a
+    size sweep (1e6 / 4e6 / sample) that shows the metric (Mpts/s) is size-independent for N >> M, which is what lets a
+    sample stand in for N = 1e8."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    reps = max(1, args.steps)
-    n_s = args.cpu_sample
     import torch
-    x, y = synth(int(n_s), 2, 1234, "cpu", torch.float64)
-    for _ in range(min(args.warmup, 1)):
-        cpu_solve_step(x[:200000], y[:200000])
+    kind, solve = _cpu_arm_setup()
+    reps = max(1, args.steps)
+    n_s = int(args.cpu_sample)
+    x, y = synth(n_s, 2, 1234, "cpu", torch.float64)
+    for _ in range(max(1, min(args.warmup, 2))):
+        mtot, _ = solve(x[:200000], y[:200000])
+    sweep = {}
+    for n in sorted({min(n_s, 1000000), min(n_s, 4000000)}):
+        if n < n_s:
+            t0 = time.perf_counter()
+            solve(x[:n], y[:n])
+            sweep[str(n)] = n / (time.perf_counter() - t0) / 1e6
     t0 = time.perf_counter()
     for _ in range(reps):
-        f, _ = cpu_solve_step(x, y)
+        mtot, _ = solve(x, y)
     dt = (time.perf_counter() - t0) / reps
-    sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import fast_nufft as F
     v = n_s / dt / 1e6
+    sweep[str(n_s)] = v
     cores = _host_threads()
+    what = ("UNMODIFIED reference EFGPND.predict (oracle/_ref) + C/OpenMP ES-kernel NUFFT as pytorch_finufft"
+            if kind == "reference" else "oracle restatement of efgpnd.py + C/OpenMP ES-kernel NUFFT")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": reps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args, 1, f.mtot),
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"{int(n_s)} points per step (bounded sample of the N={int(args.npts)} workload)",
-                             "os_cpu_count": os.cpu_count()},
+            "config": workload_config(args, 1, mtot),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+                             "sample": f"{n_s} points per step (bounded sample of the N={int(args.npts)} workload); "
+                                       f"{what}; FINUFFT itself is not installable here",
+                             "mpts_per_s_by_sample_size": sweep, "os_cpu_count": os.cpu_count()},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def cpu_baseline(args):
+    """The CPU arm in its own process (the reference's modules share their names with the product package)."""
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "2", "--warmup", "1",
+           "--cpu-sample", str(args.cpu_sample), "--npts", str(args.npts)]
+    env = dict(os.environ)
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "OMP_NUM_THREADS"):
+        env.pop(k, None)
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=900)
+    for ln in reversed(r.stdout.splitlines()):
+        if ln.startswith("{"):
+            d = json.loads(ln)
+            cb = d["cpu_baseline"]
+            cb["seconds_per_step"] = d["ms_per_step"] / 1e3
+            return cb
+    return {"value": None, "unit": UNIT, "cores": _host_threads(), "kind": "failed",
+            "sample": (r.stderr or r.stdout)[-400:]}
 
 
 def workload_config(args, world, mtot=None):
@@ -159,9 +229,14 @@ class NvmlClockSampler:
         self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
         self.sm, self.pw, self.reasons = [], [], set()
         self._stop = threading.Event()
-        self._sample()
-        self.sm.clear()                   # the probe sample above is outside the timed region
+        self._sample()                    # probe that the queries work; not part of the statistics
+        self.sm.clear()
+        self.pw.clear()
+        self.reasons.clear()
         self.t = threading.Thread(target=self._run, daemon=True)
+
+    def start(self):
+        """Called right before the first timed launch: every sample lies inside the timed region."""
         self.t.start()
 
     def _sample(self):
@@ -190,9 +265,9 @@ class NvmlClockSampler:
         self.t.join(timeout=2)
         if not self.sm:
             return {"sm_mhz": None, "sm_max_mhz": self.mx, "reasons": ["no samples"]}
-        hi = sorted(self.sm)[len(self.sm) // 2:]            # samples under load = the upper half
-        return {"sm_mhz": sorted(hi)[len(hi) // 2], "sm_max_mhz": self.mx, "reasons": sorted(self.reasons),
-                "samples": len(self.sm), "power_w_max": max(self.pw) if self.pw else None, "source": "nvml"}
+        sm = sorted(self.sm)                      # every sample taken between start and stop (the timed region)
+        return {"sm_mhz": sm[len(sm) // 2], "sm_mhz_min": sm[0], "sm_max_mhz": self.mx, "reasons": sorted(self.reasons),
+                "samples": len(sm), "power_w_max": max(self.pw) if self.pw else None, "source": "nvml"}
 
 
 def make_clock_sampler(gpu_index):
@@ -210,8 +285,11 @@ class ClockSampler:
     def __init__(self, gpu_index):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
+        self.gpu_index = gpu_index
+
+    def start(self):
         try:
-            self.p = subprocess.Popen(["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.Q}",
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={self.gpu_index}", f"--query-gpu={self.Q}",
                                        "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except Exception:
@@ -247,8 +325,8 @@ class ClockSampler:
             pass
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        hi = sorted(sm)[len(sm) // 2:]            # samples under load = the upper half
-        return {"sm_mhz": sorted(hi)[len(hi) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+        sm = sorted(sm)                           # every sample of the sampling window
+        return {"sm_mhz": sm[len(sm) // 2], "sm_mhz_min": sm[0], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
                 "samples": len(sm), "power_w_max": max(pw)}
 
 
@@ -290,6 +368,56 @@ def algorithmic_flops(stage, n, d=2):
     return n * (d * horner + 2 * W ** d + W)
 
 
+def parity_check(x_loc, beta_timed, mean_timed, beta_tight, mean_tight, n_total, world, dev):
+    """Rank 0, after the timing: the CPU oracle (oracle/efgp_oracle.py restating efgpnd.py:745-822, on the C/OpenMP
+    ES-kernel NUFFT) solves the SAME full-size problem; beta is compared directly and the posterior mean at 10^4
+    sampled points against the exact NUDFT of the oracle's beta.  Two configurations: the timed one (nufft_eps 1e-4 on
+    both sides: bar 10 * nufft_eps, BASELINE.json) and a tight one (nufft_eps 1e-9, CG 1e-10: bar 1e-6)."""
+    import math
+    import torch
+    odir = os.path.join(ROOT, "oracle")
+    if odir not in sys.path:
+        sys.path.append(odir)
+    import efgp_oracle as O
+    import fast_nufft as F
+    from pytorch_finufft import functional as exact
+    F.NTHREADS = _host_threads()
+    torch.set_num_threads(_host_threads())
+    t_start = time.perf_counter()
+    if world > 1:
+        xa, ya = synth_range(0, n_total, 2, dev, torch.float64)
+        x_all, y_all = xa.cpu(), ya.cpu()
+        del xa, ya
+    else:
+        x_all, y_all = x_loc.cpu(), None
+    if y_all is None:
+        _, ya = synth_range(0, n_total, 2, dev, torch.float64)
+        y_all = ya.cpu()
+        del ya
+    kern = O.OracleKernel("se", 2, ELL, VAR, param_dtype=torch.float64)
+    s2 = float(torch.exp(torch.log(torch.tensor(SIG2, dtype=torch.float64))))
+    g = torch.Generator().manual_seed(7)
+    idx = torch.randint(0, x_loc.shape[0], (10000,), generator=g)
+    xs = x_loc[idx.to(dev)].cpu()
+
+    def rel(a, b):
+        return float(torch.linalg.norm((a - b).reshape(-1)) / torch.linalg.norm(b.reshape(-1)))
+
+    out = {"n_checked_points": int(n_total), "n_checked_means": int(idx.numel()),
+           "oracle": "oracle/efgp_oracle.fit on oracle/cnufft.c (CPU, all host cores) at the full N; means against the "
+                     "exact NUDFT of the oracle's beta at sampled points"}
+    for tag, neps, ctol, beta, mean, bar in (("timed_config", NUFFT_EPS, CG_TOL, beta_timed, mean_timed, 10 * NUFFT_EPS),
+                                             ("tight", 1e-9, 1e-10, beta_tight, mean_tight, 1e-6)):
+        f = O.fit(x_all, y_all, kern, s2, EPS, neps, cg_tol=ctol, backend=F)
+        phi = (2 * math.pi * f.h * xs).T.contiguous()
+        mean_ref = exact.finufft_type2(phi, (f.ws * f.beta).reshape(f.mtot, f.mtot), isign=+1, modeord=False).real
+        out[tag] = {"nufft_eps": neps, "cg_tol": ctol, "beta_rel": rel(beta.cpu().reshape(-1), f.beta.reshape(-1)),
+                    "mean_rel": rel(mean[idx.to(dev)].cpu(), mean_ref), "bar": bar, "oracle_cg_iters": int(f.iters)}
+        out[tag]["ok"] = bool(out[tag]["beta_rel"] <= bar and out[tag]["mean_rel"] <= bar)
+    out["seconds"] = time.perf_counter() - t_start
+    return out
+
+
 def bind_to_gpu_numa_node(local):
     """Pin this rank to the CPUs next to its GPU so that its pinned staging buffers (first touch) and the
     H2D / D2H DMA stay on the GPU's own NUMA node; 8 ranks otherwise share one node's memory controllers."""
@@ -315,10 +443,184 @@ def bind_to_gpu_numa_node(local):
     return None
 
 
+# ----------------------------------------------------------------------------- config 4: probe-sharded gradient step
+C4 = {"N": 1e7, "d": 3, "ell": 0.1, "var": 1.0, "sig2": 0.04, "eps": 1e-4, "cg_tol": 1e-5, "nufft_eps": 1e-5}
+C4_METRIC, C4_UNIT = "efgp_gradient_step_probe_throughput", "Mprobe-pts/s"
+
+
+def c4_data(n, device, dtype):
+    import torch
+    g = torch.Generator(device=device).manual_seed(0)                 # the same points on every rank
+    x = torch.rand(n, 3, dtype=dtype, device=device, generator=g) * 2 - 1
+    y = (torch.sin(3 * x[:, 0]) * torch.cos(4 * x[:, 1]) + 0.3 * torch.sin(5 * x[:, 2])
+         + 0.2 * torch.randn(n, dtype=dtype, device=device, generator=g))
+    return x, y
+
+
+def c4_config(args, n, world):
+    return {"workload": "BASELINE.json configs[3]: 3-D squared-exponential hyperparameter-gradient step "
+                        "(EFGPND.compute_gradients: mean solve + Hutchinson trace with batched NUFFTs and batched PCG)",
+            "N_total": int(n), "d": 3, "probes": int(args.probes), "lengthscale": C4["ell"], "variance": C4["var"],
+            "sigmasq": C4["sig2"], "eps": C4["eps"], "nufft_eps": C4["nufft_eps"], "cg_tolerance": C4["cg_tol"],
+            "parallelism": f"probes sharded over {world} GPU(s), every rank holds all points, scalar all-reduce"
+            if world > 1 else "single GPU",
+            "l2_policy": "inputs (320 MB of points, 5.8M-cell fine grids per probe) exceed the 126 MB L2"}
+
+
+def run_config4_reference(args):
+    """CPU arm of config 4: the reference's compute_gradients on a bounded sample (N = 2e5 points, 4 probes)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import torch
+    kind, _ = _cpu_arm_setup()
+    n_s, T = 200000, 4
+    x, y = c4_data(n_s, "cpu", torch.float64)
+    if kind == "reference":
+        import io
+        import contextlib
+        import efgpnd as R
+        from kernels.squared_exponential import SquaredExponential
+
+        def step():
+            k = SquaredExponential(dimension=3, init_lengthscale=C4["ell"], init_variance=C4["var"])
+            with contextlib.redirect_stdout(io.StringIO()):
+                m = R.EFGPND(x, y, k, sigmasq=C4["sig2"], eps=C4["eps"], estimate_params=False)
+                torch.manual_seed(1234)
+                m.compute_gradients(trace_samples=T, cg_tol=C4["cg_tol"], nufft_eps=C4["nufft_eps"], apply_gradients=False)
+    else:
+        import efgp_oracle as O
+        import fast_nufft as F
+
+        def step():
+            k = O.OracleKernel("se", 3, C4["ell"], C4["var"])
+            torch.manual_seed(1234)
+            O.gradient(x, y, k, C4["sig2"], C4["eps"], T, C4["nufft_eps"], C4["cg_tol"], backend=F)
+    step()
+    reps = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        step()
+    dt = (time.perf_counter() - t0) / reps
+    v = n_s * T / dt / 1e6
+    print(json.dumps({"impl": "reference", "metric": C4_METRIC, "value": v, "unit": C4_UNIT, "n_gpus": args.gpus,
+                      "steps": reps, "warmup": 1, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
+                      "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": c4_config(args, C4["N"], 1),
+                      "cpu_baseline": {"value": v, "unit": C4_UNIT, "cores": _host_threads(), "kind": kind,
+                                       "sample": f"{n_s} points x {T} probes per step (bounded sample of N=1e7 x 64)"},
+                      "e2e": {"value": v, "unit": C4_UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                      "gpu_launches": 0}), flush=True)
+
+
+def run_config4(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback for the product path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import efgpnd
+    from efgp_b200 import _lib
+    from kernels.squared_exponential import SquaredExponential
+    n = int(C4["N"]) if args.npts == 1e8 else int(args.npts)
+    T = int(args.probes)
+    x, y = c4_data(n, dev, torch.float64)
+    opts = {"shard_probes": world > 1}
+    state = {}
+
+    def step(xd, yd):
+        k = SquaredExponential(dimension=3, init_lengthscale=C4["ell"], init_variance=C4["var"])
+        m = efgpnd.EFGPND(xd, yd, k, sigmasq=C4["sig2"], eps=C4["eps"], estimate_params=False, opts=opts)
+        torch.manual_seed(1234)                       # identical probe seeds on every rank and repeat
+        g = m.compute_gradients(trace_samples=T, cg_tol=C4["cg_tol"], nufft_eps=C4["nufft_eps"], apply_gradients=False)
+        state["stats"] = m.last_gradient_stats
+        return g
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        grads = step(x, y)
+    barrier()
+    sampler = make_clock_sampler(local) if rank == 0 else None
+    _lib.timing_enable(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.reset_peak_memory_stats()
+    barrier()
+    if sampler:
+        sampler.start()
+    e0.record()
+    for _ in range(args.steps):
+        grads = step(x, y)
+    e1.record()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    stages = _lib.timing_report()
+    _lib.timing_enable(False)
+    tt = torch.tensor([e0.elapsed_time(e1) / args.steps], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms = float(tt.item())
+    # end to end: points and targets come from pinned host memory every step, the gradient goes back to the host
+    xh = torch.empty(x.shape, dtype=x.dtype, pin_memory=True).copy_(x)
+    yh = torch.empty(y.shape, dtype=y.dtype, pin_memory=True).copy_(y)
+    gh = torch.empty(3, dtype=torch.float64, pin_memory=True)
+    xd, yd = torch.empty_like(x), torch.empty_like(y)
+
+    def e2e_step():
+        xd.copy_(xh, non_blocking=True)
+        yd.copy_(yh, non_blocking=True)
+        gh.copy_(step(xd, yd).to(torch.float64), non_blocking=True)
+
+    e2e_step()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e1.record()
+    barrier()
+    tt = torch.tensor([e0.elapsed_time(e1) / args.steps], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_e2e = float(tt.item())
+    if rank == 0:
+        st = state["stats"]
+        per_stage = {k: {"ms_per_step": v["ms"] / args.steps, "launches_per_step": v["launches"] / args.steps}
+                     for k, v in stages.items()}
+        n_side = sum(v["ms"] for k, v in stages.items() if k.split(".")[0] in ("sort", "permute", "unpermute", "type1", "type2")
+                     or k.startswith("spread") or k.startswith("interp")) / args.steps
+        cg_side = sum(v["ms"] for k, v in stages.items() if k.startswith("cg.") or k.startswith("toeplitz.")) / args.steps
+        line = {"metric": C4_METRIC, "value": n * T / ms / 1e3, "unit": C4_UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": c4_config(args, n, world),
+                "clocks": clocks,
+                "e2e": {"value": n * T / ms_e2e / 1e3, "unit": C4_UNIT, "ms_per_step": ms_e2e,
+                        "h2d_bytes_per_step": (xh.numel() + yh.numel()) * 8 * world, "d2h_bytes_per_step": 24 * world,
+                        "api": "EFGPND(x, y, SquaredExponential).compute_gradients(trace_samples=64) on buffers copied "
+                               "from pinned host memory; the 3 gradient entries copied back"},
+                "gpu_launches": int(sum(v["launches"] for v in stages.values())),
+                "split_ms_per_step": {"O(N) stages (sort, permutes, spread, interp, fine-grid FFTs)": n_side,
+                                      "M-grid stages (Toeplitz, batched CG)": cg_side},
+                "stages": per_stage, "mean_cg_iters": int(st["mean_cg_iters"]), "trace_cg_iters": int(st["trace_cg_iters"]),
+                "mtot": int(st["mtot"]), "grad": [float(v) for v in grads],
+                "peak_mem_GB": torch.cuda.max_memory_allocated() / 1e9}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     args = parse()
     if args.impl == "reference":
-        return run_reference(args)
+        return run_config4_reference(args) if args.workload == "config4" else run_reference(args)
+    if args.workload == "config4":
+        return run_config4(args)
     import torch
     import torch.distributed as dist
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -338,17 +640,19 @@ def main():
     n_total = int(args.npts)
     lo_pt, hi_pt = efgpnd.shard_bounds(n_total, world, rank)
     n_loc = hi_pt - lo_pt
-    x, y = synth(n_loc, 2, 1000 + rank, dev, torch.float64)
+    x, y = synth_range(lo_pt, hi_pt, 2, dev, torch.float64)      # this rank's slice of ONE seeded data set
     opts = {"cg_tolerance": CG_TOL, "shard_points": world > 1}
     stats = {}
+    last = {}
 
-    def solve(xd, yd):
+    def solve(xd, yd, nufft_eps=NUFFT_EPS, cg_tol=CG_TOL):
         efgpnd._PLAN_CACHE.clear()                 # a step starts from raw points: sort included
         kern = SquaredExponential(dimension=2, init_lengthscale=ELL, init_variance=VAR)
-        model = efgpnd.EFGPND(xd, yd, kern, sigmasq=SIG2, eps=EPS, nufft_eps=NUFFT_EPS, opts=opts,
-                              estimate_params=False)
+        model = efgpnd.EFGPND(xd, yd, kern, sigmasq=SIG2, eps=EPS, nufft_eps=nufft_eps,
+                              opts=dict(opts, cg_tolerance=cg_tol), estimate_params=False)
         mean, _ = model.predict(xd, return_variance=False)
         stats.update(model.last_fit_stats)
+        last["model"] = model
         return mean
 
     def barrier():
@@ -365,15 +669,17 @@ def main():
     _lib.timing_enable(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    if sampler:
+        sampler.start()
     e0.record()
     for _ in range(args.steps):
         mean = solve(x, y)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1) / args.steps
+    clocks = sampler.stop() if sampler else None      # stopped right after the closing synchronize
     stages = _lib.timing_report()
     _lib.timing_enable(False)
-    clocks = sampler.stop() if sampler else None
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -458,6 +764,22 @@ def main():
                "api": "EFGPND(x, y, SquaredExponential, ...).predict(x, return_variance=False) on buffers copied "
                       "from pinned host memory; posterior mean copied back"}
 
+    # ---- parity at the full size: every rank runs the two solves (collectives), rank 0 compares with the oracle
+    parity = None
+    if not args.no_parity:
+        mean_timed = solve(x, y)
+        beta_timed = last["model"]._beta.detach().clone()
+        mean_tight = solve(x, y, nufft_eps=1e-9, cg_tol=1e-10)
+        beta_tight = last["model"]._beta.detach().clone()
+        barrier()
+        if rank == 0:
+            parity = parity_check(x, beta_timed, mean_timed, beta_tight, mean_tight, n_total, world, dev)
+    beta_now = last["model"]._beta.detach()
+    gprobe = torch.Generator(device="cpu").manual_seed(99)
+    wprobe = torch.randn(beta_now.numel(), dtype=torch.float64, generator=gprobe).to(dev)
+    beta_fingerprint = {"l2": float(beta_now.abs().square().sum().sqrt().item()),
+                        "probe": float((beta_now.real * wprobe).sum().item())}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -517,9 +839,10 @@ def main():
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": workload_config(args, world, stats.get("mtot")),
             "numa_cpulist": numa, "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-            "stages": per_stage, "mean_cg_iters": stats.get("mean_cg_iters"), "result_rms": check}
+            "stages": per_stage, "mean_cg_iters": stats.get("mean_cg_iters"), "result_rms": check,
+            "beta_fingerprint": beta_fingerprint, "parity": parity}
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(args.cpu_sample, 2)
+        line["cpu_baseline"] = cpu_baseline(args)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

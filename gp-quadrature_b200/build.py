@@ -11,8 +11,8 @@ OUT_DIR = os.path.join(HERE, "efgp_b200")
 LIB = os.path.join(OUT_DIR, "libefgp_b200.so")
 OBJ_DIR = os.path.join(HERE, "build")
 
-SOURCES = ["es_kernel.cpp", "pool.cpp", "timing.cpp", "points.cu", "spread.cu", "interp.cu", "nufft.cu", "toeplitz.cu", "cg.cu", "lanczos.cu", "capi.cu"]
-HEADERS = ["common.cuh", "nufft.cuh", "toeplitz.cuh", "stream_ring.cuh", os.path.join("..", "..", "include", "efgp_b200.h")]
+SOURCES = ["es_kernel.cpp", "pool.cpp", "timing.cpp", "points.cu", "spread.cu", "interp.cu", "nufft.cu", "toeplitz.cu", "cg.cu", "lanczos.cu", "fit.cu", "comm.cpp", "capi.cu"]
+HEADERS = ["common.cuh", "nufft.cuh", "toeplitz.cuh", "stream_ring.cuh", "fit.cuh", os.path.join("..", "..", "include", "efgp_b200.h")]
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -50,7 +50,7 @@ def build(force=False, verbose=True):
         list(ex.map(run, jobs))
     if jobs or force or _newer(objs, LIB):
         run([NVCC, "-shared", "-o", LIB] + objs +
-            ["-L/usr/local/cuda/lib64", "-lcufft", "-lcudart", "-Xlinker", "-rpath=/usr/local/cuda/lib64"])
+            ["-L/usr/local/cuda/lib64", "-lcufft", "-lcudart", "-ldl", "-Xlinker", "-rpath=/usr/local/cuda/lib64"])
     return LIB
 
 

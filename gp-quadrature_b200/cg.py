@@ -61,6 +61,8 @@ class ConjugateGradients:
             return None
         if self.b.dim() > 2 or not self.b.is_complex():
             return None
+        if not getattr(op, "_real_ws", False):
+            return None      # complex weights: the library solve would drop Im(ws); use the operator's own __call__
         return op
 
     def solve(self):

@@ -1,6 +1,8 @@
 // extern "C" boundary of libefgp_b200 (see include/efgp_b200.h).
 #include "../../include/efgp_b200.h"
 #include "toeplitz.cuh"
+#include "fit.cuh"
+#include <memory>
 
 namespace efgp {
 static thread_local std::string g_last_error;
@@ -9,10 +11,17 @@ void set_last_error(const std::string& msg) { g_last_error = msg; }
 
 struct efgp_nufft {
   efgp::Nufft nu;
+  cudaStream_t last_stream = nullptr;     // blocks released by the destructor are tagged with it (pool.cpp)
 };
 struct efgp_toeplitz {
   efgp::Toeplitz t;
+  cudaStream_t last_stream = nullptr;
 };
+
+// Every entry point that touches the device: refuse a second GPU in this process and publish the stream to the pool.
+#define EFGP_ENTER(stream)                               \
+  efgp::check_device();                                  \
+  efgp::set_current_stream((cudaStream_t)(stream))
 
 #define EFGP_TRY(body)                                  \
   try {                                                 \
@@ -100,6 +109,7 @@ static double measure_fp64_peak(cudaStream_t st) {
 
 int efgp_measure_fp64_peak(double* tflops, void* stream) {
   EFGP_TRY({
+    EFGP_ENTER(stream);
     EFGP_CHECK(tflops != nullptr, "null output");
     *tflops = measure_fp64_peak((cudaStream_t)stream);
   })
@@ -119,8 +129,9 @@ int efgp_nufft_create(efgp_nufft** out, int dim, int dtype) {
 
 int efgp_nufft_set_points(efgp_nufft* nu, const void* x, int64_t npts, double h, const double* xcen,
                           void* stream) {
-  (void)stream;
   EFGP_TRY({
+    EFGP_ENTER(stream);
+    if (nu) nu->last_stream = (cudaStream_t)stream;
     EFGP_CHECK(nu != nullptr, "null handle");
     EFGP_CHECK(npts >= 0, "npts must be >= 0");
     EFGP_CHECK(npts == 0 || x != nullptr, "null points");
@@ -132,12 +143,32 @@ int efgp_nufft_set_points(efgp_nufft* nu, const void* x, int64_t npts, double h,
   })
 }
 
-void efgp_nufft_destroy(efgp_nufft* nu) { delete nu; }
+int efgp_nufft_rescale(efgp_nufft* nu, double h, const double* xcen) {
+  EFGP_TRY({
+    EFGP_CHECK(nu != nullptr, "null handle");
+    bool same = h == nu->nu.h;
+    for (int a = 0; a < nu->nu.dim; ++a) same = same && (xcen ? xcen[a] : 0.0) == nu->nu.xcen[a];
+    if (!same) {
+      nu->nu.h = h;
+      for (int a = 0; a < efgp::kMaxDim; ++a) nu->nu.xcen[a] = (xcen && a < nu->nu.dim) ? xcen[a] : 0.0;
+      efgp::set_current_stream(nu->last_stream);
+      nu->nu.sorted.clear();      // the cell order depends on h: rebuilt by the next transform
+    }
+  })
+}
+
+void efgp_nufft_destroy(efgp_nufft* nu) {
+  if (!nu) return;
+  efgp::set_current_stream(nu->last_stream);
+  delete nu;
+}
 
 int efgp_nufft_type1(efgp_nufft* nu, const void* strengths, int is_complex, int batch,
                      const int64_t* out_shape, double eps, int isign, int modeord, const void* scale,
                      void* out, void* stream) {
   EFGP_TRY({
+    EFGP_ENTER(stream);
+    if (nu) nu->last_stream = (cudaStream_t)stream;
     EFGP_CHECK(nu != nullptr && out != nullptr && out_shape != nullptr, "null argument");
     efgp::nufft_type1(nu->nu, strengths, is_complex, batch, out_shape, eps, isign, modeord, scale, out,
                       (cudaStream_t)stream);
@@ -148,6 +179,8 @@ int efgp_nufft_type1_pair(efgp_nufft* nu, const void* y, const int64_t* shape_ge
                           const int64_t* shape_rhs, double eps_rhs, const void* scale, void* out_gen, void* out_rhs,
                           void* stream) {
   EFGP_TRY({
+    EFGP_ENTER(stream);
+    if (nu) nu->last_stream = (cudaStream_t)stream;
     EFGP_CHECK(nu != nullptr && y != nullptr && shape_gen != nullptr && shape_rhs != nullptr && out_gen != nullptr &&
                    out_rhs != nullptr,
                "null argument");
@@ -159,6 +192,8 @@ int efgp_nufft_type1_pair(efgp_nufft* nu, const void* y, const int64_t* shape_ge
 int efgp_nufft_type2(efgp_nufft* nu, const void* modes, int batch, const int64_t* shape, double eps,
                      int isign, int modeord, const void* scale, int real_out, void* out, void* stream) {
   EFGP_TRY({
+    EFGP_ENTER(stream);
+    if (nu) nu->last_stream = (cudaStream_t)stream;
     EFGP_CHECK(nu != nullptr && modes != nullptr && shape != nullptr, "null argument");
     EFGP_CHECK(nu->nu.N == 0 || out != nullptr, "null output");
     efgp::nufft_type2(nu->nu, modes, batch, shape, eps, isign, modeord, scale, real_out, out,
@@ -182,13 +217,19 @@ int efgp_toeplitz_create(efgp_toeplitz** out, const void* v, int dim, const int6
   EFGP_TRY({
     EFGP_CHECK(out != nullptr && v != nullptr && Ls != nullptr, "null argument");
     EFGP_CHECK(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    EFGP_ENTER(stream);
     std::unique_ptr<efgp_toeplitz> h(new efgp_toeplitz());
+    h->last_stream = (cudaStream_t)stream;
     efgp::toeplitz_create(h->t, v, dim, Ls, dtype, force_pow2, (cudaStream_t)stream);
     *out = h.release();
   })
 }
 
-void efgp_toeplitz_destroy(efgp_toeplitz* t) { delete t; }
+void efgp_toeplitz_destroy(efgp_toeplitz* t) {
+  if (!t) return;
+  efgp::set_current_stream(t->last_stream);
+  delete t;
+}
 
 int efgp_toeplitz_fft_shape(efgp_toeplitz* t, int64_t* shape_out) {
   EFGP_TRY({
@@ -200,6 +241,8 @@ int efgp_toeplitz_fft_shape(efgp_toeplitz* t, int64_t* shape_out) {
 int efgp_toeplitz_apply(efgp_toeplitz* t, const void* x, int batch, const void* ws, double sigmasq,
                         int mode, void* y, void* stream) {
   EFGP_TRY({
+    EFGP_ENTER(stream);
+    if (t) t->last_stream = (cudaStream_t)stream;
     EFGP_CHECK(t != nullptr && x != nullptr && y != nullptr, "null argument");
     efgp::toeplitz_apply(t->t, x, batch, ws, sigmasq, mode, y, (cudaStream_t)stream);
   })
@@ -209,6 +252,8 @@ int efgp_cg_solve(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, co
                   const void* b, void* x, int batch, double tol, int max_iter, int early_stopping,
                   int batched_semantics, int x0_is_zero, int* iters_completed, void* stream) {
   EFGP_TRY({
+    EFGP_ENTER(stream);
+    if (t) t->last_stream = (cudaStream_t)stream;
     EFGP_CHECK(t != nullptr && b != nullptr && x != nullptr, "null argument");
     efgp::cg_solve(t->t, ws, sigmasq, mode, minv, b, x, batch, tol, max_iter, early_stopping,
                    batched_semantics, x0_is_zero, iters_completed, (cudaStream_t)stream);
@@ -219,6 +264,8 @@ int efgp_cg_solve_hermitian(efgp_toeplitz* t, const void* ws, double sigmasq, in
                             const void* b, void* x, int batch, double tol, int max_iter, int early_stopping,
                             int batched_semantics, int x0_is_zero, int* iters_completed, void* stream) {
   EFGP_TRY({
+    EFGP_ENTER(stream);
+    if (t) t->last_stream = (cudaStream_t)stream;
     EFGP_CHECK(t != nullptr && b != nullptr && x != nullptr, "null argument");
     efgp::cg_solve(t->t, ws, sigmasq, mode, minv, b, x, batch, tol, max_iter, early_stopping,
                    batched_semantics, x0_is_zero, iters_completed, (cudaStream_t)stream, 1);
@@ -229,6 +276,8 @@ int efgp_cg_solve_async(efgp_toeplitz* t, const void* ws, double sigmasq, int mo
                         void* x, int batch, double tol, int max_iter, int early_stopping, int batched_semantics,
                         int x0_is_zero, int hermitian, int* counters_pinned, int* iters_completed, void* stream) {
   EFGP_TRY({
+    EFGP_ENTER(stream);
+    if (t) t->last_stream = (cudaStream_t)stream;
     EFGP_CHECK(t != nullptr && b != nullptr && x != nullptr && counters_pinned != nullptr, "null argument");
     efgp::cg_solve(t->t, ws, sigmasq, mode, minv, b, x, batch, tol, max_iter, early_stopping,
                    batched_semantics, x0_is_zero, iters_completed, (cudaStream_t)stream, hermitian, counters_pinned);
@@ -238,9 +287,89 @@ int efgp_cg_solve_async(efgp_toeplitz* t, const void* ws, double sigmasq, int mo
 int efgp_lanczos(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, void* q, int batch, int steps,
                  double breakdown_tol, double* alphas, double* betas, void* stream) {
   EFGP_TRY({
+    EFGP_ENTER(stream);
+    if (t) t->last_stream = (cudaStream_t)stream;
     EFGP_CHECK(t != nullptr && q != nullptr && alphas != nullptr && betas != nullptr, "null argument");
     efgp::lanczos_tridiag(t->t, ws, sigmasq, mode, q, batch, steps, breakdown_tol, alphas, betas,
                           (cudaStream_t)stream);
+  })
+}
+
+/* ---- library communicator */
+int efgp_comm_unique_id(void* id128) {
+  EFGP_TRY({
+    EFGP_CHECK(id128 != nullptr, "null argument");
+    efgp::comm_unique_id(id128);
+  })
+}
+
+int efgp_comm_init(int rank, int world, const void* id128) {
+  EFGP_TRY({
+    EFGP_CHECK(id128 != nullptr, "null argument");
+    efgp::check_device();
+    efgp::comm_init(rank, world, id128);
+  })
+}
+
+int efgp_comm_destroy(void) {
+  EFGP_TRY({ efgp::comm_destroy(); })
+}
+
+int efgp_comm_world(void) { return efgp::comm_world(); }
+
+int efgp_allreduce(void* buf, int64_t count, int dtype, int op, void* stream) {
+  EFGP_TRY({
+    EFGP_ENTER(stream);
+    EFGP_CHECK(buf != nullptr && count >= 0, "bad argument");
+    efgp::comm_allreduce(buf, count, dtype, op, (cudaStream_t)stream);
+  })
+}
+
+/* ---- fused fit */
+int efgp_bbox_async(const void* x, int64_t npts, int dim, int dtype, int sharded, double* ext_pinned, void* stream) {
+  EFGP_TRY({
+    EFGP_ENTER(stream);
+    EFGP_CHECK(x != nullptr && ext_pinned != nullptr, "null argument");
+    EFGP_CHECK(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    efgp::bbox_async(x, npts, dim, dtype, sharded, ext_pinned, (cudaStream_t)stream);
+  })
+}
+
+int efgp_fit(efgp_nufft* nu, const void* y, const efgp_fit_args* args, void* ws, void* vr, void* minv, void* beta,
+             efgp_toeplitz** toep_out, int* counters_pinned, int* iters_completed, void* stream) {
+  EFGP_TRY({
+    EFGP_ENTER(stream);
+    EFGP_CHECK(nu != nullptr && y != nullptr && args != nullptr && toep_out != nullptr && counters_pinned != nullptr,
+               "null argument");
+    EFGP_CHECK(nu->nu.N >= 1, "fit needs at least one point");
+    nu->last_stream = (cudaStream_t)stream;
+    efgp::FitArgs a;
+    a.family = args->family;
+    a.c = args->c;
+    a.a = args->a;
+    a.b = args->b;
+    a.p = args->p;
+    a.h = args->h;
+    a.hd = args->hd;
+    a.mtot = args->mtot;
+    a.sigmasq = args->sigmasq;
+    a.nufft_eps = args->nufft_eps;
+    a.gen_eps = args->gen_eps;
+    a.cg_tol = args->cg_tol;
+    a.max_iter = args->max_iter;
+    a.precondition = args->precondition;
+    a.force_pow2 = args->force_pow2;
+    a.sharded = args->sharded;
+    a.warm_start = args->warm_start;
+    EFGP_CHECK(a.family == 0 || a.family == 1, "unknown spectral-density family");
+    if (a.h != nu->nu.h) {           // same points, new spacing: the cell order of the sorted sets is stale
+      nu->nu.h = a.h;
+      nu->nu.sorted.clear();
+    }
+    std::unique_ptr<efgp_toeplitz> h(new efgp_toeplitz());
+    h->last_stream = (cudaStream_t)stream;
+    efgp::fit_run(nu->nu, h->t, y, a, ws, vr, minv, beta, counters_pinned, iters_completed, (cudaStream_t)stream);
+    *toep_out = h.release();
   })
 }
 

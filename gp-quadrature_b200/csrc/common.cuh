@@ -44,6 +44,12 @@ struct Error : std::runtime_error {
 constexpr int kMaxW = 16;      // widest spreading kernel (eps ~ 1e-14)
 constexpr int kMaxDeg = 20;    // highest Horner degree
 constexpr int kMaxDim = 3;
+constexpr double kMaxSigma = 16.0;   // beta keeps growing with the upsampling factor up to here
+// Degree of the piecewise polynomials, a function of the width only (the device Horner loops are unrolled at compile
+// time).  Measured with scripts/es_study.py against the exact NUDFT: for every width 2..16 and sigma in [2, 8] the
+// transform error at degree W - 1 is within 10 % of the error at degree W + 2 (W >= 5; W for the narrow kernels),
+// because the aliasing error exp(-pi W sqrt(1 - 1/sigma)) of the kernel itself is the floor.
+__host__ __device__ constexpr int es_degree(int W) { return W <= 4 ? W : W - 1; }
 
 // Piecewise-polynomial "exponential of semicircle" kernel phi(z)=exp(beta(sqrt(1-z^2)-1)).
 // For a point with in-cell offset u in [-1/2,1/2) the W weights are
@@ -59,6 +65,7 @@ struct ESKernel {
 
 // Width and beta for a requested tolerance and effective upsampling factor sigma = nf/nmodes.
 int es_width_for(double eps, double sigma, int max_w);
+double es_error_model(int W, double sigma);   // modelled relative l2 error of a transform with this kernel
 void es_build(ESKernel& k, int W, double sigma, double target_err);
 double es_eval_exact(const ESKernel& k, double z);  // z in [-1,1]
 // psi_hat(k/nf) for k = 0..kmax, psi(z)=phi(2z/W): deconvolution factors.
@@ -115,5 +122,10 @@ struct ScopedStage {
 void* pool_alloc(size_t bytes);
 void pool_free(void* p);
 void pool_trim();
+// stream of the C-ABI call in progress on this thread (pool.cpp: blocks released on one stream are not handed to
+// another without waiting), and the one-GPU-per-process check
+void set_current_stream(cudaStream_t st);
+cudaStream_t current_stream();
+void check_device();
 
 }  // namespace efgp

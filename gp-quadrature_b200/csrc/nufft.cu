@@ -15,6 +15,7 @@
 #include <utility>
 #include <cmath>
 #include <algorithm>
+#include <cstdlib>
 
 namespace efgp {
 
@@ -312,50 +313,111 @@ static void es_build_cached(ESKernel& k, int W, double sigma) {
   k = it->second;
 }
 
+// Modelled cost of one transform in units of one FP64 FMA on the points' side: per point W^d footprint FMAs (the 3-D
+// shared-memory tile kernels run ~3x below the FP64 rate of the 2-D register kernels) plus d even/odd Horner
+// evaluations; per fine-grid cell the memset, the flushes, the cuFFT passes and the deconvolution (~200 FMA-times of
+// HBM traffic, profiles/ncu_r01_traffic.json).  Only used to rank candidate upsampling factors.
+static double transform_cost(int dim, double npts, int W, double cells) {
+  const double foot = std::pow((double)W, dim) * (dim == 3 ? 3.0 : 1.0);
+  const double horner = dim * 0.5 * W * (es_degree(W) + 3);
+  return npts * (foot + horner) + 200.0 * cells;
+}
+
+// Fine grid of a transform that builds its OWN sorted set: EFGP grids are tiny next to N, so a larger upsampling
+// factor (narrower kernel: fewer FMAs per point) is nearly free -- e.g. the Toeplitz generator of the headline
+// solve (141^2 modes, eps 6e-8, 1e8 points) takes W = 7 on a 720^2 grid instead of W = 9 on 288^2 (measured
+// 1.6 -> see DESIGN.md section 4).  EFGP_SIGMA pins the factor (A/B measurements).
+static double pick_sigma(const Nufft& nu, const int64_t* n, double eps, int64_t* nf_out, int* w_out) {
+  static const double sigma_env = [] {
+    const char* e = std::getenv("EFGP_SIGMA");
+    double v = e ? std::atof(e) : 0.0;
+    return v >= 1.25 ? v : 0.0;
+  }();
+  const double cands[] = {2.0, 2.5, 3.0, 4.0, 5.0, 6.0, 8.0};
+  double best_cost = 0, best_sigma = 0;
+  for (double sg : cands) {
+    if (sigma_env > 0) sg = sigma_env;
+    int64_t nf[kMaxDim] = {1, 1, 1};
+    // the width depends on the achieved factor, which depends on the rounded-up grid: two passes settle it
+    int w = es_width_for(eps, sg, kMaxW);
+    double cells = 1, sig_eff = 1e30;
+    for (int pass = 0; pass < 2; ++pass) {
+      cells = 1;
+      sig_eff = 1e30;
+      for (int a = 0; a < nu.dim; ++a) {
+        nf[a] = next_smooth_even(std::max<int64_t>((int64_t)std::ceil(sg * (double)n[a]), 2 * w));
+        cells *= (double)nf[a];
+        sig_eff = std::min(sig_eff, (double)nf[a] / (double)n[a]);
+      }
+      w = es_width_for(eps, sig_eff, kMaxW);
+    }
+    const size_t esz = nu.dtype == 0 ? 4 : 8;
+    const bool fits = cells < 3.9e9 && cells * esz <= (double)((size_t)2 << 30);
+    if (!fits && best_sigma > 0) break;
+    const double cost = transform_cost(nu.dim, (double)nu.N, w, cells);
+    if (best_sigma == 0 || cost < best_cost) {
+      best_cost = cost;
+      best_sigma = sg;
+      for (int a = 0; a < kMaxDim; ++a) nf_out[a] = a < nu.dim ? nf[a] : 1;
+      *w_out = w;
+    }
+    if (sigma_env > 0) break;
+  }
+  return best_sigma;
+}
+
 static GridChoice choose_grid(Nufft& nu, const int64_t* n, double eps, cudaStream_t st) {
   GridChoice gc;
   const int max_w = kMaxW;
   if (nu.dtype == 0 && eps < 1e-7) eps = 1e-7;  // single precision floor
-  int w0 = es_width_for(eps, 2.0, max_w);
   int64_t own[kMaxDim] = {1, 1, 1};
+  int w_own = 2;
+  pick_sigma(nu, n, eps, own, &w_own);
   double own_cells = 1;
-  for (int a = 0; a < nu.dim; ++a) {
-    own[a] = next_smooth_even(std::max<int64_t>(2 * n[a], 2 * w0));
-    own_cells *= (double)own[a];
-  }
+  for (int a = 0; a < nu.dim; ++a) own_cells *= (double)own[a];
+  const double own_cost = transform_cost(nu.dim, (double)nu.N, w_own, own_cells);
+  // An existing sorted set on a grid at least 2x the mode count can serve this transform without another sort
+  // (larger effective upsampling -> narrower kernel): this is how F*y and the type-2 share the generator's grid.
   SortedPoints* best = nullptr;
+  int best_w = 0;
+  double best_cost = 0;
   for (auto& sp : nu.sorted) {
     bool ok = true;
-    double cells = 1;
+    double cells = 1, sigma = 1e30;
     for (int a = 0; a < nu.dim; ++a) {
-      ok = ok && sp->nf[a] >= own[a];
+      ok = ok && sp->nf[a] >= 2 * n[a];
       cells *= (double)sp->nf[a];
+      sigma = std::min(sigma, (double)sp->nf[a] / (double)n[a]);
     }
     if (!ok) continue;
-    if (cells > std::max(16.0 * own_cells, (double)nu.N)) continue;
-    if (!best) best = sp.get();
+    int w = es_width_for(eps, sigma, max_w);
+    if ((w & 1) != sp->odd) ++w;       // the half-cell shift of the stored coordinates fixes the parity
+    if (w > max_w) continue;
+    for (int a = 0; a < nu.dim; ++a) ok = ok && sp->nf[a] >= 2 * w;
+    if (!ok) continue;
+    // a second sort costs about as much as three narrow transforms and holds another copy of the points
+    const double cost = transform_cost(nu.dim, (double)nu.N, w, cells);
+    if (cost > 4.0 * own_cost + 100.0 * (double)nu.N) continue;
+    if (!best || cost < best_cost) {
+      best = sp.get();
+      best_w = w;
+      best_cost = cost;
+    }
   }
   if (best) {
     double sigma = 1e30;
     for (int a = 0; a < nu.dim; ++a) sigma = std::min(sigma, (double)best->nf[a] / (double)n[a]);
-    int w = es_width_for(eps, std::min(sigma, 4.0), max_w);
-    if ((w & 1) != best->odd) ++w;
-    bool fits = w <= max_w;
-    for (int a = 0; a < nu.dim; ++a) fits = fits && best->nf[a] >= 2 * w;
-    if (fits) {
-      for (int a = 0; a < kMaxDim; ++a) gc.nf[a] = best->nf[a];
-      es_build_cached(gc.ker, w, std::min(sigma, 4.0));
-      best->last_use = ++nu.clock;
-      gc.sp = best;
-      return gc;
-    }
+    for (int a = 0; a < kMaxDim; ++a) gc.nf[a] = best->nf[a];
+    es_build_cached(gc.ker, best_w, sigma);
+    best->last_use = ++nu.clock;
+    gc.sp = best;
+    return gc;
   }
   double sigma = 1e30;
   for (int a = 0; a < nu.dim; ++a) sigma = std::min(sigma, (double)own[a] / (double)n[a]);
-  int w = es_width_for(eps, std::min(sigma, 4.0), max_w);
   for (int a = 0; a < kMaxDim; ++a) gc.nf[a] = own[a];
-  es_build_cached(gc.ker, w, std::min(sigma, 4.0));
-  gc.sp = get_sorted(nu, gc.nf, w & 1, st);
+  es_build_cached(gc.ker, w_own, sigma);
+  gc.sp = get_sorted(nu, gc.nf, w_own & 1, st);
   return gc;
 }
 

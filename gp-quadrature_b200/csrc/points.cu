@@ -65,7 +65,7 @@ struct SortGeom {
   uint32_t g;       // cells per level-2 bin (1 = exact cell sort)
   int nb1;          // level-1 buckets (<= kMaxBuckets)
   int nbins2;       // level-2 bins per bucket (<= kMaxBins2)
-  int log2P;        // points per thread of the tile-transposed layout
+  int P;            // points per thread of the tile-transposed layout (any value in 1..128)
 };
 
 constexpr int kMaxBuckets = 256;
@@ -127,13 +127,14 @@ __device__ __forceinline__ uint32_t fold_values(const T* xv, const FoldParams<T>
   return key;
 }
 
-// slot of sorted rank r in the tile-transposed layout (nufft.cuh)
-__device__ __forceinline__ int64_t slot_of_rank(int64_t r, int log2P) {
-  const int64_t tile_len = (int64_t)kTileThreads << log2P;
-  int64_t tile = r / tile_len;
-  int rr = (int)(r - tile * tile_len);
-  int t = rr >> log2P, j = rr & ((1 << log2P) - 1);
-  return tile * tile_len + (int64_t)j * kTileThreads + t;
+// slot of sorted rank r in the tile-transposed layout (nufft.cuh); r < 2^31 (checked on the host): 32-bit divisions
+__device__ __forceinline__ int64_t slot_of_rank(int64_t r, int P) {
+  const uint32_t tile_len = (uint32_t)kTileThreads * (uint32_t)P;
+  const uint32_t r32 = (uint32_t)r;
+  const uint32_t tile = r32 / tile_len;
+  const uint32_t rr = r32 - tile * tile_len;
+  const uint32_t t = rr / (uint32_t)P, j = rr - t * (uint32_t)P;
+  return (int64_t)tile * tile_len + (int64_t)j * kTileThreads + t;
 }
 
 // ------------------------------------------------------------------ level 1
@@ -371,7 +372,7 @@ bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* 
     if (q[k] == kNone) continue;
     const uint32_t a = s + k * kSortThreads + threadIdx.x;
     uint32_t r = base[q[k]] + atomicAdd(&cnt[q[k]], 1u);
-    int64_t slot = slot_of_rank((int64_t)r, g.log2P);
+    int64_t slot = slot_of_rank((int64_t)r, g.P);
     *reinterpret_cast<uint32_t*>(&w[k][D]) = a;
     store_record<T, RW>(rec + slot * RW, w[k]);
     B[a] = (uint32_t)slot;
@@ -380,10 +381,10 @@ bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* 
 
 template <typename T, int D>
 __global__ void __launch_bounds__(256)
-pad_slots_kernel(int64_t N, int64_t npos, int log2P, T* __restrict__ rec) {
+pad_slots_kernel(int64_t N, int64_t npos, int P, T* __restrict__ rec) {
   int64_t r = N + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= npos) return;
-  int64_t slot = slot_of_rank(r, log2P);
+  int64_t slot = slot_of_rank(r, P);
   constexpr int RW = rec_words(D);
   T w[RW];
 #pragma unroll
@@ -603,13 +604,25 @@ void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t 
 
 // ------------------------------------------------------------------ host driver
 static int pick_points_per_thread(int64_t N) {
-  // >= 4 waves of 148 SMs x 256 threads when N allows, and long register runs when N is large
-  int64_t P = N / (148 * 256 * 4);
+  // The 2-D spread / interp kernels run one CTA per tile of 256 * P points, two CTAs per SM for the narrow kernels
+  // and one for the wide ones: the tile count is made a whole number of waves of 2 * (SM count) CTAs (round 1 rounded
+  // P down to a power of two: 763 CTAs = 5.15 waves of 148 paid for 6 at the 8-GPU shard size), with the longest
+  // register runs (P <= 128) the wave count allows.
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        sms <= 0)
+      sms = 148;
+  }
+  const int64_t wave = 2 * (int64_t)sms;
+  const int64_t per_wave = wave * kTileThreads * 128;
+  const int64_t k = std::max<int64_t>(1, (N + per_wave - 1) / per_wave);
+  const int64_t tiles = k * wave;
+  int64_t P = (N + tiles * kTileThreads - 1) / (tiles * kTileThreads);
   if (P < 1) P = 1;
   if (P > 128) P = 128;
-  int p2 = 1;
-  while (p2 * 2 <= P) p2 *= 2;
-  return p2;
+  return (int)P;
 }
 
 template <typename T, int D>
@@ -708,7 +721,7 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
     bin_scatter_kernel<T, D><<<ntiles2_max, kSortThreads, 2 * g.nbins2 * sizeof(uint32_t), st>>>(
         R[0], R[1], R[2], RY, K2, bucketStart, tile2Base, g, binStart, binCursor, rec, sp.B);
     if (sp.npos > N)
-      pad_slots_kernel<T, D><<<div_up(sp.npos - N, 256), 256, 0, st>>>(N, sp.npos, g.log2P, rec);
+      pad_slots_kernel<T, D><<<div_up(sp.npos - N, 256), 256, 0, st>>>(N, sp.npos, g.P, rec);
   }
   EFGP_CUDA(cudaGetLastError());
   pool_free(scan_tmp);
@@ -774,8 +787,7 @@ static void build_t(SortedPoints& sp, const T* x, const T* ypay, int64_t N, int 
     }
   }
   g.nbins2 = (int)((g.cpb + g.g - 1) / g.g);
-  g.log2P = 0;
-  while ((1 << g.log2P) < sp.P) ++g.log2P;
+  g.P = sp.P;
   if (dim == 1) build_td<T, 1>(sp, x, ypay, N, p, g, st);
   if (dim == 2) build_td<T, 2>(sp, x, ypay, N, p, g, st);
   if (dim == 3) build_td<T, 3>(sp, x, ypay, N, p, g, st);

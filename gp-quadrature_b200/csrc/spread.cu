@@ -19,7 +19,7 @@ namespace efgp {
 
 template <typename T, int W>
 __device__ __forceinline__ void es_eval(const ESDev<T>& es, T s, T* __restrict__ k) {
-  constexpr int DEG = W + 2;
+  constexpr int DEG = es_degree(W);
   constexpr int NE = DEG / 2 + 1;    // even coefficients 0,2,..
   constexpr int NO = (DEG + 1) / 2;  // odd coefficients 1,3,..
   const T v = s * s;

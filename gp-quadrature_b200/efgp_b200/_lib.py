@@ -16,6 +16,15 @@ c_dblp = ctypes.POINTER(ctypes.c_double)
 c_intp = ctypes.POINTER(ctypes.c_int)
 vp = ctypes.c_void_p
 
+class FitArgs(ctypes.Structure):
+    """efgp_fit_args of include/efgp_b200.h, field for field."""
+    _fields_ = [("family", ctypes.c_int), ("c", ctypes.c_double), ("a", ctypes.c_double), ("b", ctypes.c_double),
+                ("p", ctypes.c_double), ("h", ctypes.c_double), ("hd", ctypes.c_double), ("mtot", ctypes.c_int),
+                ("sigmasq", ctypes.c_double), ("nufft_eps", ctypes.c_double), ("gen_eps", ctypes.c_double),
+                ("cg_tol", ctypes.c_double), ("max_iter", ctypes.c_int), ("precondition", ctypes.c_int),
+                ("force_pow2", ctypes.c_int), ("sharded", ctypes.c_int), ("warm_start", ctypes.c_int)]
+
+
 _SIGNATURES = {
     "efgp_version": (ctypes.c_int, []),
     "efgp_last_error": (ctypes.c_char_p, []),
@@ -48,6 +57,14 @@ _SIGNATURES = {
                                            ctypes.c_int, vp, c_intp, vp]),
     "efgp_lanczos": (ctypes.c_int, [vp, vp, ctypes.c_double, ctypes.c_int, vp, ctypes.c_int, ctypes.c_int,
                                     ctypes.c_double, vp, vp, vp]),
+    "efgp_nufft_rescale": (ctypes.c_int, [vp, ctypes.c_double, c_dblp]),
+    "efgp_comm_unique_id": (ctypes.c_int, [vp]),
+    "efgp_comm_init": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, vp]),
+    "efgp_comm_destroy": (ctypes.c_int, []),
+    "efgp_comm_world": (ctypes.c_int, []),
+    "efgp_allreduce": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
+    "efgp_bbox_async": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp]),
+    "efgp_fit": (ctypes.c_int, [vp, vp, ctypes.POINTER(FitArgs), vp, vp, vp, vp, ctypes.POINTER(vp), vp, c_intp, vp]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

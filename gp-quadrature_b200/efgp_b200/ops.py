@@ -75,6 +75,8 @@ class NufftPlan:
             check(_lib.lib().efgp_nufft_set_points(self._h, _ptr(self.x), int(self.N), self.h, dbl_array(xc),
                                                    _stream(self.device)))
 
+        self.xcen = tuple(xc)
+
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
         if h:
@@ -82,6 +84,15 @@ class NufftPlan:
                 _lib.lib().efgp_nufft_destroy(h)
             except Exception:
                 pass
+
+    def ensure(self, h, xcen=None):
+        """Same points, (possibly) new spacing / centre (efgp_nufft_rescale): a no-op when nothing changed."""
+        h = float(h)
+        xc = self.xcen if xcen is None else tuple(float(v) for v in xcen)
+        if h != self.h or xc != self.xcen:
+            check(_lib.lib().efgp_nufft_rescale(self._h, h, dbl_array(xc)))
+            self.h, self.xcen = h, xc
+        return self
 
     def _scale(self, scale, M):
         if scale is None:
@@ -204,6 +215,9 @@ class LazyIters:
 
     def resolve(self):
         if self._value is None:
+            if self._event is None:          # the call that should have enqueued the solve raised: nothing will arrive
+                self.set(self._max_iter)
+                return self._value
             self._event.synchronize()
             active, jmax = int(self._buf[0]), int(self._buf[1])
             if self._early and active <= 0:
@@ -253,6 +267,26 @@ class ToeplitzPlan:
         shp = (ctypes.c_int64 * self.d)()
         check(_lib.lib().efgp_toeplitz_fft_shape(self._h, shp))
         self.fft_shape = [int(s) for s in shp]
+
+    @classmethod
+    def from_handle(cls, handle, v):
+        """Wrap a Toeplitz handle the library created itself (efgp_fit); v is the generator it was built from."""
+        self = cls.__new__(cls)
+        self.v = v
+        self.cdtype = v.dtype
+        self.rdtype = real_of(v.dtype)
+        self.device = v.device
+        self.Ls = list(v.shape)
+        self.d = len(self.Ls)
+        self.ns = [(L + 1) // 2 for L in self.Ls]
+        self.size = 1
+        for n in self.ns:
+            self.size *= n
+        self._h = handle
+        shp = (ctypes.c_int64 * self.d)()
+        check(_lib.lib().efgp_toeplitz_fft_shape(self._h, shp))
+        self.fft_shape = [int(s) for s in shp]
+        return self
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
@@ -333,3 +367,84 @@ class ToeplitzPlan:
             check(_lib.lib().efgp_lanczos(self._h, _ptr(w), float(sigmasq), int(mode), _ptr(qs), P, int(steps),
                                           float(breakdown_tol), _ptr(alphas), _ptr(betas), _stream(self.device)))
         return alphas, betas
+
+
+# ----------------------------------------------------------------------------- fused fit, bounding box, communicator
+_BOX_RING = None
+_BOX_NEXT = 0
+
+
+def bbox_async(x, sharded=False):
+    """Enqueue [max x_a .., -min x_a ..] of x (N, d) into pinned host memory (efgp_bbox_async; MAX-reduced over the
+    library communicator when sharded).  Returns (pinned float64 tensor of 2 d entries, event): the caller does its
+    L-independent host work, then event.synchronize() and reads the tensor."""
+    global _BOX_RING, _BOX_NEXT
+    _require_cuda(x, "x")
+    if x.ndim == 1:
+        x = x[:, None]
+    x = x.contiguous()
+    N, d = x.shape
+    if _BOX_RING is None:
+        _BOX_RING = torch.zeros((16, 8), dtype=torch.float64).pin_memory()
+    buf = _BOX_RING[_BOX_NEXT]
+    _BOX_NEXT = (_BOX_NEXT + 1) % 16
+    with _on(x.device):
+        check(_lib.lib().efgp_bbox_async(_ptr(x), int(N), int(d), _dtype_code(x.dtype), 1 if sharded else 0,
+                                         ctypes.c_void_p(buf.data_ptr()), _stream(x.device)))
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(x.device))
+    return buf[:2 * d], ev
+
+
+def fit(plan, y, args, ws, vr, minv, beta, lazy):
+    """efgp_fit on the points of `plan` (a NufftPlan): fills ws, vr = [F^*1 ; ws F^*y], minv, beta (in/out) and returns
+    the library's Toeplitz handle.  `lazy` is the LazyIters that receives the iteration counters."""
+    handle = ctypes.c_void_p()
+    iters = ctypes.c_int(0)
+    with _on(plan.device):
+        check(_lib.lib().efgp_fit(plan._h, _ptr(y), ctypes.byref(args), _ptr(ws), _ptr(vr), _ptr(minv), _ptr(beta),
+                                  ctypes.byref(handle), lazy.ptr, ctypes.byref(iters), _stream(plan.device)))
+        if iters.value < 0:
+            lazy.enqueued()
+        else:
+            lazy.set(iters.value)
+    plan.h = float(args.h)
+    return handle
+
+
+_COMM_KEY = None
+
+
+def ensure_comm(group):
+    """Create the library's NCCL communicator over the ranks of `group` (once per group): rank 0 draws the unique id,
+    torch.distributed broadcasts its 128 bytes, every rank joins (efgp_comm_unique_id / efgp_comm_init)."""
+    global _COMM_KEY
+    import torch.distributed as dist
+    key = (id(group), dist.get_world_size(group))
+    if _COMM_KEY == key:
+        return
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    idbuf = (ctypes.c_char * 128)()
+    if rank == 0:
+        check(_lib.lib().efgp_comm_unique_id(ctypes.cast(idbuf, ctypes.c_void_p)))
+    dev = torch.device("cuda", torch.cuda.current_device())
+    backend = dist.get_backend(group)
+    t = torch.frombuffer(bytearray(idbuf.raw), dtype=torch.uint8).clone()
+    if backend == "nccl":
+        t = t.to(dev)
+    src = dist.get_global_rank(group, 0) if hasattr(dist, "get_global_rank") else 0
+    dist.broadcast(t, src=src, group=group)
+    raw = bytes(t.cpu().numpy().tobytes())
+    idbuf2 = ctypes.create_string_buffer(raw, 128)
+    check(_lib.lib().efgp_comm_init(int(rank), int(world), ctypes.cast(idbuf2, ctypes.c_void_p)))
+    _COMM_KEY = key
+
+
+def comm_allreduce(t, op="sum"):
+    """In-place all-reduce of a real device tensor over the library communicator (efgp_allreduce)."""
+    _require_cuda(t, "t")
+    assert t.is_contiguous() and t.dtype in (torch.float32, torch.float64)
+    with _on(t.device):
+        check(_lib.lib().efgp_allreduce(_ptr(t), int(t.numel()), _dtype_code(t.dtype), 0 if op == "sum" else 1,
+                                        _stream(t.device)))
+    return t

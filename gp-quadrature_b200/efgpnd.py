@@ -115,19 +115,59 @@ def shard_bounds(n_total, world, rank):
     return lo, lo + base + (1 if rank < extra else 0)
 
 
+# Domain size L = max_a (max x_a - min x_a) of tensors whose bounding box was already reduced, keyed on the tensor's
+# identity AND version counter (any in-place write changes the key): the one host synchronisation of a fit -- every
+# grid size depends on L -- is paid once per data set, not once per hyperparameter step on the same data.
+_BBOX_CACHE: "OrderedDict[tuple, float]" = OrderedDict()
+
+
+def _fit_domain_length(x, group, kernel, eps, use_cache=True):
+    """(L, (Ltime, Lfreq)) for the fused fit: the bounding box comes from the library (efgp_bbox_async, MAX-reduced
+    over the library communicator when the points are sharded) while the host runs the two L-independent bisections."""
+    key = (x.data_ptr(), tuple(x.shape), x.dtype, x.device, x._version, 0 if group is None else id(group))
+    L = _BBOX_CACHE.get(key) if use_cache else None
+    if L is not None:
+        return L, truncation_bounds(kernel, eps)
+    d = x.shape[1]
+    ext, ev = _ops.bbox_async(x, sharded=group is not None)
+    bounds = truncation_bounds(kernel, eps)
+    ev.synchronize()
+    e = ext.tolist()
+    L = max(e[a] + e[d + a] for a in range(d))
+    if use_cache:
+        _BBOX_CACHE[key] = L
+        while len(_BBOX_CACHE) > 8:
+            _BBOX_CACHE.popitem(last=False)
+    return L, bounds
+
+
 # ----------------------------------------------------------------------------- NUFFT
 _PLAN_CACHE: "OrderedDict[tuple, _ops.NufftPlan]" = OrderedDict()
 _PLAN_CACHE_SIZE = 3
 
 
+def _xcen_tuple(xcen, d):
+    if xcen is None:
+        return (0.0,) * d
+    if isinstance(xcen, torch.Tensor):
+        return tuple(float(v) for v in xcen.detach().reshape(-1).tolist())
+    if not hasattr(xcen, "__len__"):
+        return (float(xcen),) * d
+    return tuple(float(v) for v in xcen)
+
+
 def _shared_plan(x, h, xcen):
-    """NUFFT objects built on the same tensor and spacing share one bin-sorted point set (the
-    Toeplitz-generator transform at eps=6e-8 and the F*y / F beta transforms use the same points)."""
+    """NUFFT objects built on the same tensor share one library handle and its bin-sorted point sets (the
+    Toeplitz-generator transform at eps = 6e-8 and the F*y / F beta transforms use the same points).  The cache is keyed
+    on the TENSOR only: a new spacing h (every optimiser step of the reference's loop, efgpnd.py:1138-1195) re-scales
+    the existing handle (efgp_nufft_rescale) instead of building a new one."""
     if x.ndim == 1:
         x = x[:, None]
-    xc = tuple(float(v) for v in (xcen.detach().reshape(-1).tolist() if isinstance(xcen, torch.Tensor)
-                                  else ([xcen] * x.shape[1] if not hasattr(xcen, "__len__") else xcen)))
-    key = (x.data_ptr(), tuple(x.shape), x.dtype, x.device, x._version, float(h), xc)
+    xc = _xcen_tuple(xcen, x.shape[1])
+    if not x.is_contiguous():
+        # the plan would own a contiguous COPY while the key names the caller's storage: do not cache
+        return _ops.NufftPlan(x, float(h), xc)
+    key = (x.data_ptr(), tuple(x.shape), x.dtype, x.device, x._version)
     plan = _PLAN_CACHE.get(key)
     if plan is None:
         plan = _ops.NufftPlan(x, float(h), xc)
@@ -136,6 +176,7 @@ def _shared_plan(x, h, xcen):
             _PLAN_CACHE.popitem(last=False)
     else:
         _PLAN_CACHE.move_to_end(key)
+        plan.ensure(h, xc)
     return plan
 
 
@@ -161,7 +202,8 @@ class NUFFT:
                 raise ValueError("xcen must be a d-vector (or an (N, d) tensor with identical rows)")
             xcen = xcen[0]
         self._x, self._xcen, self._h = x, xcen, h
-        self._plan = _shared_plan(x, _as_float(h), xcen if xcen is not None else [0.0] * self.d)
+        self._hf, self._xc = _as_float(h), _xcen_tuple(xcen, self.d)
+        self._plan = _shared_plan(x, self._hf, self._xc)
         self._phi = None
 
     @property
@@ -176,19 +218,22 @@ class NUFFT:
 
     def type1(self, vals, out_shape, *, scale=None, eps=None):
         """F^* vals: isign=-1, centred modes (efgpnd.py:1454-1508).  vals (N,) or (B, N)."""
-        out = self._plan.type1(vals.to(self.device), out_shape, self.eps if eps is None else eps, isign=-1,
-                               modeord=False, scale=scale)
+        out = self._plan.ensure(self._hf, self._xc).type1(vals.to(self.device), out_shape,
+                                                          self.eps if eps is None else eps, isign=-1,
+                                                          modeord=False, scale=scale)
         return out if out.dtype == self.cdtype else out.to(self.cdtype)
 
     def type1_ones(self, out_shape, eps=None):
         """F^* 1 without materialising the strengths (the Toeplitz generator)."""
-        return self._plan.type1(None, out_shape, self.eps if eps is None else eps, isign=-1, modeord=False)
+        return self._plan.ensure(self._hf, self._xc).type1(None, out_shape, self.eps if eps is None else eps,
+                                                           isign=-1, modeord=False)
 
     def type2(self, fk, out_shape=None, *, scale=None, real_out=False, modeord=False):
         """F fk: isign=+1 (efgpnd.py:1510-1549).  fk flat (M,), (B, M), or already shaped."""
         fk = fk.to(self.device)
         shape = tuple(out_shape) if out_shape is not None else tuple(fk.shape[-self.d:])
-        return self._plan.type2(fk, shape, self.eps, isign=+1, modeord=modeord, scale=scale, real_out=real_out)
+        return self._plan.ensure(self._hf, self._xc).type2(fk, shape, self.eps, isign=+1, modeord=modeord,
+                                                           scale=scale, real_out=real_out)
 
 
 def setup_nufft(x, xcen, h, nufft_eps, cdtype):
@@ -215,12 +260,13 @@ class ToeplitzND:
     (4m+1)^d generator v (reference efgpnd.py:1239-1393); the padded FFT pair and the crop run in
     libefgp_b200 (csrc/toeplitz.cu)."""
 
-    def __init__(self, v: torch.Tensor, *, force_pow2: bool = True, precompute_fft: bool = True):
+    def __init__(self, v: torch.Tensor, *, force_pow2: bool = True, precompute_fft: bool = True, _plan=None):
         if not torch.is_complex(v):
             v = v.to(torch.complex128 if v.dtype == torch.float64 else torch.complex64)
         if not v.is_cuda:
             raise EfgpError("ToeplitzND needs CUDA tensors: the EFGP hot path has no CPU fallback")
-        self.plan = _ops.ToeplitzPlan(v, force_pow2=force_pow2)
+        # _plan: a handle the library built itself inside efgp_fit (same generator v)
+        self.plan = _plan if _plan is not None else _ops.ToeplitzPlan(v, force_pow2=force_pow2)
         self.Ls = list(v.shape)
         self.ns = [(L + 1) // 2 for L in self.Ls]
         self.size = prod(self.ns)
@@ -462,7 +508,10 @@ def compute_prediction_variance(x_new, xis, ws, A_var, cg_tol, max_cg_iter, vari
         out = []
         for xb in torch.split(x_new, 8192, dim=0):
             fx = torch.exp(2 * math.pi * 1j * (xb @ xis.T)).to(cdtype)
-            rhs = _hermitian(ws * fx.conj())            # conj(fx)[-k] = fx[k]: symmetric rows
+            rhs = ws * fx.conj()
+            if getattr(ws, "_efgp_real", False) and hasattr(xis, "h_float"):
+                _hermitian(rhs)         # conj(fx)[-k] = fx[k] on OUR centred odd grid with even real weights
+                                        # (foreign xis / ws take the general matvec: the symmetry is not checked)
             gamma = ConjugateGradients(A_var, rhs, x0=_zero_guess(rhs, cdtype), tol=cg_tol,
                                        max_iter=max_cg_iter, early_stopping=True).solve()
             out.append(torch.real((fx * (ws * gamma)).sum(dim=-1)).clamp_min(0.0))
@@ -765,6 +814,9 @@ class EFGPND(nn.Module):
             else:
                 raise ValueError(f"Unknown kernel type: {kernel}")
         self.kernel = kernel
+        if estimate_params and _point_shard_group(self.opts) is not None:
+            raise EfgpError("estimate_params=True would estimate from one rank's shard under opts['shard_points']: "
+                            "pass the hyperparameters (estimate_params=False)")
         if estimate_params:
             try:
                 ell, var, noise = kernel.estimate_hyperparameters(x, y)
@@ -788,9 +840,9 @@ class EFGPND(nn.Module):
                 self.kernel._gp_params_ref = self._gp_params
         finally:
             torch.set_default_dtype(prev)
-        self.__dict__.update(_beta=None, _xis=None, _ws=None, _ws_real=None, _toeplitz=None, _fitted=False,
-                             _cached_params={}, _registered_optimizers=[], last_gradient_stats={},
-                             _last_gradient_beta=None)
+        self.__dict__.update(_beta=None, _xis_val=None, _ws_val=None, _ws_real=None, _toeplitz=None, _fitted=False,
+                             _fit_h=None, _fit_mtot=None, _cached_params={}, _registered_optimizers=[],
+                             last_gradient_stats={}, _last_gradient_beta=None)
         self._update_param_cache()
 
     # ------------------------------------------------------------------ parameter bookkeeping
@@ -846,6 +898,10 @@ class EFGPND(nn.Module):
         """Raw (log-space) gradient of the negative log marginal likelihood, order
         [lengthscale, variance, sigmasq] (efgpnd.py:573-708); fills last_gradient_stats."""
         self._update_param_cache()
+        if _point_shard_group(self.opts) is not None:
+            raise EfgpError("compute_gradients / optimize_hyperparameters are not defined for opts['shard_points'] "
+                            "(each rank would differentiate its own shard): shard the probes instead "
+                            "(opts['shard_probes'], every rank holds all points)")
         if nufft_eps is None:
             nufft_eps = self.eps * 0.1
         if noise_floor is None:
@@ -882,6 +938,81 @@ class EFGPND(nn.Module):
             return raw_grad, log_marginal
         return raw_grad
 
+    # ------------------------------------------------------------------ fitted state
+    # _xis (M, d) and the complex _ws (M,) are part of the reference's observable state (efgpnd.py:460-468); the fused
+    # fit only needs the real weights on the device, so both are materialised the first time somebody reads them.
+    @property
+    def _xis(self):
+        v = self.__dict__.get("_xis_val")
+        if v is None and self.__dict__.get("_fit_mtot") is not None:
+            d = 1 if self.x.ndim == 1 else self.x.shape[1]
+            hm = (self._fit_mtot - 1) // 2
+            x1 = (torch.arange(-hm, hm + 1, device=self.x.device, dtype=torch.float64) * self._fit_h).to(self.x.dtype)
+            v = torch.stack(torch.meshgrid(*(x1 for _ in range(d)), indexing="ij"), dim=-1).view(-1, d)
+            v.h_float = self._fit_h
+            self.__dict__["_xis_val"] = v
+        return v
+
+    @_xis.setter
+    def _xis(self, v):
+        self.__dict__["_xis_val"] = v
+
+    @property
+    def _ws(self):
+        v = self.__dict__.get("_ws_val")
+        if v is None and self.__dict__.get("_ws_real") is not None:
+            v = self._ws_real.to(dtype=_cmplx(self._ws_real.dtype))
+            v._efgp_real = True
+            v._efgp_real_part = self._ws_real
+            self.__dict__["_ws_val"] = v
+        return v
+
+    @_ws.setter
+    def _ws(self, v):
+        self.__dict__["_ws_val"] = v
+
+    def _fit_fused(self, x, y, now, s2, nufft_eps, group, fam):
+        """The whole fit as two library calls (efgp_bbox_async, efgp_fit): see csrc/fit.cu."""
+        device, rdtype = x.device, x.dtype
+        cdtype = _cmplx(rdtype)
+        N, d = x.shape
+        if group is not None:
+            _ops.ensure_comm(group)
+        L, bounds = _fit_domain_length(x, group, self.kernel, self.eps, self.opts.get("cache_bbox", True))
+        if L <= 1e-9:
+            L = 1.0
+        _, h_float, mtot = get_xis(kernel_obj=self.kernel, eps=self.eps, L=L, use_integral=True, l2scaled=False,
+                                   bounds=bounds)
+        M, lg = mtot ** d, 2 * (mtot - 1) + 1
+        Lg = lg ** d
+        precond = bool(self.opts.get("mean_cg_preconditioner", True))
+        ws_r = torch.empty(M, device=device, dtype=rdtype)
+        vr = torch.empty(Lg + M, device=device, dtype=cdtype)
+        minv = torch.empty(M, device=device, dtype=rdtype) if precond else None
+        prev = self._beta
+        warm = bool(self.opts.get("mean_cg_warm_start", True)) and prev is not None and prev.numel() == M
+        beta = prev.to(device=device, dtype=cdtype).reshape(M).clone() if warm else \
+            torch.zeros(M, device=device, dtype=cdtype)
+        # h^d in the model's dtype, as the reference's torch.tensor(h, dtype=rdtype) ** d (efgpnd.py:763-780)
+        hd = h_float ** d if rdtype == torch.float64 else float(torch.tensor(h_float, dtype=rdtype) ** d)
+        family, c, a, b, p = fam
+        max_iter = 2 * M
+        args = _ops._lib.FitArgs(int(family), float(c), float(a), float(b), float(p), float(h_float), float(hd), int(mtot),
+                                 float(s2), float(nufft_eps), 6e-8, float(self.opts.get("cg_tolerance", 1e-4)),
+                                 int(max_iter), 1 if precond else 0, 1 if _TOEPLITZ_POW2 else 0,
+                                 1 if group is not None else 0, 1 if warm else 0)
+        plan = _shared_plan(x, h_float, [0.0] * d)
+        lazy = _ops.LazyIters(device, max_iter, False, True)
+        handle = _ops.fit(plan, y, args, ws_r, vr, minv, beta, lazy)
+        v_kernel = vr[:Lg].view((lg,) * d)
+        toeplitz = ToeplitzND(v_kernel, force_pow2=_TOEPLITZ_POW2,
+                              _plan=_ops.ToeplitzPlan.from_handle(handle, v_kernel))
+        self.last_fit_stats = _LazyStats({"mean_cg_iters": lazy, "mtot": int(mtot), "h": h_float,
+                                          "feature_count": int(M)})
+        self.__dict__.update(_beta=beta, _xis_val=None, _ws_val=None, _ws_real=ws_r, _toeplitz=toeplitz, _fitted=True,
+                             _fit_params=now, _fit_h=h_float, _fit_mtot=int(mtot), _fit_buffers=(vr, minv))
+        self._cached_params.update(now)
+
     # ------------------------------------------------------------------ fit
     def _compute_common_parameters(self, force_recompute: bool = False, nufft_eps: Optional[float] = None) -> None:
         """Posterior-mean solve A_mean beta = ws * F^* y, cached until the hypers change
@@ -908,6 +1039,10 @@ class EFGPND(nn.Module):
             x = x[:, None]
         N, d = x.shape
         group = _point_shard_group(self.opts)
+        fam = self.kernel._spectral_family() if hasattr(self.kernel, "_spectral_family") else None
+        if (fam is not None and not y.is_complex() and x.is_contiguous() and y.is_contiguous()
+                and self.opts.get("fused_fit", True) and N >= 1):
+            return self._fit_fused(x, y, now, s2, nufft_eps, group, fam)
         L_dev = _domain_length_async(x, group)
         bounds = truncation_bounds(self.kernel, self.eps)      # host bisections overlap the device reduction
         L = float(L_dev.item())
@@ -961,8 +1096,8 @@ class EFGPND(nn.Module):
         ws._efgp_real = True
         # _ws_real: contiguous real weights, reused by predict's fused type-2 scaling; _fit_params: the hypers do not
         # change during a fit, so there is no second read-out after the solve
-        self.__dict__.update(_beta=beta, _xis=xis, _ws=ws, _ws_real=A_mean.ws_real, _toeplitz=toeplitz, _fitted=True,
-                             _fit_params=now)
+        self.__dict__.update(_beta=beta, _xis_val=xis, _ws_val=ws, _ws_real=A_mean.ws_real, _toeplitz=toeplitz,
+                             _fitted=True, _fit_params=now, _fit_h=h_float, _fit_mtot=int(mtot))
         self._cached_params.update(now)
 
     # ------------------------------------------------------------------ predict
@@ -991,10 +1126,13 @@ class EFGPND(nn.Module):
             if x_new.ndim == 1:
                 x_new = x_new[:, None]
             B, d = x_new.shape
-            beta, xis, ws, toeplitz = self._beta, self._xis, self._ws, self._toeplitz
-            h_float = xis.h_float
+            beta, toeplitz = self._beta, self._toeplitz
+            h_float = self._fit_h
             h = h_float                      # python scalars: no host->device copies on the predict path
-            mtot = int(round(xis.shape[0] ** (1.0 / d)))
+            mtot = self._fit_mtot
+            # the complex weights / the (M, d) frequency grid are only materialised where they are consumed
+            xis = self._xis if return_variance else None
+            ws = self._ws if (return_variance or compute_log_marginal) else None
             A_var = create_A_var(ws, toeplitz, s2, cdtype) if return_variance else None
             xcen = [0.0] * d
             OUT = (mtot,) * d

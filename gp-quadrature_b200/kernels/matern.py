@@ -59,6 +59,11 @@ class Matern(Kernel):
         sf = lambda r: var * sc * (2 * nu / ell ** 2 + (4 * math.pi ** 2) * (r * r)) ** (-(nu + d / 2))
         return kf, sf
 
+    def _spectral_family(self):
+        """(family, c, a, b, p) with S(xi) = c (b + 4 pi^2 |xi|^2)^(-p): what efgp_fit evaluates on the device."""
+        ell, var, nu, d = self.lengthscale, self.variance, self.nu, self.dimension
+        return 1, var * self._scaling(ell), 0.0, 2 * nu / ell ** 2, nu + d / 2
+
     def _scaling(self, ell):
         d, nu = self.dimension, self.nu
         return ((2 * math.sqrt(math.pi)) ** d * math.gamma(nu + d / 2) * (2 * nu) ** nu

@@ -25,6 +25,11 @@ class SquaredExponential(Kernel):
         c = ((2 * math.pi) ** 2) * ell ** 2
         return (lambda r: var * math.exp(-0.5 * (r / ell) ** 2)), (lambda r: pref * math.exp(-c * (r * r) / 2))
 
+    def _spectral_family(self):
+        """(family, c, a, b, p) with S(xi) = c exp(-a |xi|^2): what efgp_fit evaluates on the device."""
+        ell, var, d = self.get_hyper("lengthscale"), self.get_hyper("variance"), self.dimension
+        return 0, ((2 * math.pi) * ell ** 2) ** (d / 2) * var, ((2 * math.pi) ** 2) * ell ** 2 / 2, 0.0, 0.0
+
     def _sq_norm(self, xid):
         if xid.ndim == 1:
             xid = xid.unsqueeze(-1)

@@ -47,6 +47,10 @@ int efgp_nufft_create(efgp_nufft** out, int dim, int dtype);
 int efgp_nufft_set_points(efgp_nufft* nu, const void* x, int64_t npts, double h, const double* xcen,
                           void* stream);
 void efgp_nufft_destroy(efgp_nufft* nu);
+/* Same points, new spacing / centre: what the reference's training loop does at every optimiser step (a new
+ * NUFFT(x, xcen, h, eps) object on the same x, efgpnd.py:103-107 inside efgpnd.py:1138-1195).  Keeps the handle and its
+ * borrowed point pointer; the bin-sorted sets are rebuilt by the next transform if (h, xcen) changed. */
+int efgp_nufft_rescale(efgp_nufft* nu, double h, const double* xcen);
 
 /* NUFFT.type1 -> pff.finufft_type1(phi, vals, out_shape, eps, isign=-1, modeord=False)
  * (efgpnd.py:1454-1508).  strengths: (batch, npts) real (is_complex=0) or complex (1), NULL = all
@@ -132,6 +136,44 @@ int efgp_cg_solve_async(efgp_toeplitz* t, const void* ws, double sigmasq, int mo
  * blocks that add log 1 = 0 to the quadrature.  Enqueues on the stream, does not synchronise. */
 int efgp_lanczos(efgp_toeplitz* t, const void* ws, double sigmasq, int mode, void* q, int batch, int steps,
                  double breakdown_tol, double* alphas, double* betas, void* stream);
+
+/* ---- library communicator: SURVEY.md 8b's efgp_init(nccl) / efgp_allreduce_grid.  The reference has no
+ * multi-device code; these serve the point-sharded fit (one rank per GPU).  Rank 0 calls
+ * efgp_comm_unique_id, the host program broadcasts the 128 bytes (e.g. torch.distributed), every rank calls
+ * efgp_comm_init.  NCCL is loaded with dlopen only here.  efgp_allreduce: in place on the stream, dtype 0 = f32,
+ * 1 = f64, op 0 = sum, 1 = max; a no-op without a communicator. */
+int efgp_comm_unique_id(void* id128);
+int efgp_comm_init(int rank, int world, const void* id128);
+int efgp_comm_destroy(void);
+int efgp_comm_world(void);
+int efgp_allreduce(void* buf, int64_t count, int dtype, int op, void* stream);
+
+/* ---- the posterior-mean fit in one call: EFGPND._compute_common_parameters (efgpnd.py:745-822).
+ * efgp_bbox_async: [max x_0.., -min x_0..] of the points ((npts, dim) row-major) -> ext_pinned (2 dim doubles of PINNED
+ * host memory, valid once the stream reaches that point; MAX-reduced over the communicator when sharded != 0):
+ * L = max_a (max - min) of efgpnd.py:751.  The host derives (h, mtot) from L (get_xis, utils/kernels.py:72-143). */
+int efgp_bbox_async(const void* x, int64_t npts, int dim, int dtype, int sharded, double* ext_pinned, void* stream);
+
+typedef struct efgp_fit_args {
+  int family;            /* spectral density on xi = h * (k - (mtot-1)/2):  0: S = c exp(-a |xi|^2)  (squared_exponential.py:64-91) */
+  double c, a, b, p;     /*                                                 1: S = c (b + 4 pi^2 |xi|^2)^(-p)  (matern.py:100-122) */
+  double h, hd;          /* grid spacing and h^dim (efgpnd.py:756-780: ws = sqrt(S h^d)) */
+  int mtot;              /* modes per axis (odd) */
+  double sigmasq, nufft_eps, gen_eps, cg_tol;   /* gen_eps: tolerance of the F^*1 transform (6e-8, efgpnd.py:1418) */
+  int max_iter;          /* < 0: 2 M (cg.py:60-65) */
+  int precondition;      /* Jacobi preconditioner of efgpnd.py:795-799 */
+  int force_pow2;        /* Toeplitz FFT size: next power of two (efgpnd.py:791) or next 2-3-5-smooth size */
+  int sharded;           /* points sharded over the communicator: [F^*1 ; ws F^*y] is sum-reduced before the solve */
+  int warm_start;        /* beta holds the starting guess (efgpnd.py:803-806); otherwise it must hold zeros */
+} efgp_fit_args;
+
+/* nu: handle of the training points (efgp_nufft_set_points); y: (npts,) real.  Caller-owned device outputs:
+ * ws (M,) real; vr ((4m+1)^d + M,) complex = [F^*1 ; ws F^*y] (kept alive by the caller while *toep_out is used: the
+ * generator is read once, the right-hand side by the solve); minv (M,) real Jacobi diagonal (may be NULL when
+ * precondition = 0); beta (M,) complex in/out.  *toep_out is a new Toeplitz handle (efgp_toeplitz_destroy).  The solve
+ * is enqueued like efgp_cg_solve_async (counters_pinned, iters_completed have the same meaning). */
+int efgp_fit(efgp_nufft* nu, const void* y, const efgp_fit_args* args, void* ws, void* vr, void* minv, void* beta,
+             efgp_toeplitz** toep_out, int* counters_pinned, int* iters_completed, void* stream);
 
 #ifdef __cplusplus
 }

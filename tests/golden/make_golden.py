@@ -126,6 +126,9 @@ def load_case(case):
         d = torch.load(os.path.join(REFDATA, "gp_samples_100000_0.2_2_0.2.pt"))
         x, y = d[0][:4000], d[1][:4000]
         return x, y, "matern32", 0.4, 1.0, 0.2, 1e-3, torch.float64
+    if case == "cfg2_full":  # BASELINE.json configs[1] at its REAL size: all 1e5 points, Matern-3/2, eps 1e-4 (mtot 101)
+        d = torch.load(os.path.join(REFDATA, "gp_samples_100000_0.2_2_0.2.pt"))
+        return d[0], d[1], "matern32", 0.2, 1.0, 0.2, 1e-4, torch.float64
     if case == "usa_f32":  # float32 mode on real data
         d = torch.load(os.path.join(REFDATA, "usa_temp_data.pt"))
         x, y = d["x"][:1500].float(), d["y"][:1500].float()
@@ -145,7 +148,7 @@ def load_case(case):
     raise KeyError(case)
 
 
-CASES = ["cfg1_se1d", "se2d", "matern32_2d", "usa_f32", "se3d", "matern52_3d"]
+CASES = ["cfg1_se1d", "se2d", "matern32_2d", "usa_f32", "se3d", "matern52_3d", "cfg2_full"]
 
 
 def golden_model(case):
@@ -219,7 +222,9 @@ def golden_model(case):
 
 if __name__ == "__main__":
     torch.set_num_threads(8)
-    golden_host()
-    golden_toeplitz_cg()
-    for c in CASES:
+    only = sys.argv[1:]
+    if not only:
+        golden_host()
+        golden_toeplitz_cg()
+    for c in (only or CASES):
         golden_model(c)

@@ -1,0 +1,90 @@
+"""Parity at BASELINE sizes the exact O(N M) NUDFT cannot reach: the tier-2 oracle (oracle/fast_nufft.py on
+oracle/cnufft.c, itself pinned to the exact NUDFT in tests/test_oracle.py) + the oracle's restatement of the fit
+(oracle/efgp_oracle.fit, efgpnd.py:745-822) run on the host cores at the SAME N as the CUDA path:
+
+  * type-1 grids (F^*1 at eps 6e-8, F^*y) against fast_nufft,
+  * beta against the oracle fit,
+  * the posterior mean at 10^4 sampled points against the EXACT nonuniform DFT of the oracle's beta.
+
+N = 1e7 in 2-D exercises the level-1 bucket sort, the uint16 tile map and the multi-wave launches that the small
+golden cases never reach; the N = 1e8 headline size gets the same check inside bench.py (`parity` in its JSON line).
+"""
+import math
+
+import pytest
+import torch
+
+from conftest import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a = torch.as_tensor(a).detach().cpu().to(torch.complex128).reshape(-1)
+    b = torch.as_tensor(b).detach().cpu().to(torch.complex128).reshape(-1)
+    return float(torch.linalg.norm(a - b) / torch.linalg.norm(b))
+
+
+def _data(N, d, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    x = torch.rand(N, d, dtype=torch.float64, device="cuda", generator=g) * 2 - 1
+    y = torch.sin(3 * x[:, 0]) * torch.cos(4 * x[:, -1]) + 0.5 * x[:, 0] * x[:, -1]
+    y = y + 0.2 * torch.randn(N, dtype=torch.float64, device="cuda", generator=g)
+    return x, y
+
+
+@pytest.mark.parametrize("d,N,ell,eps", [(2, 10_000_000, 0.05, 1e-4), (3, 2_000_000, 0.15, 1e-4)])
+def test_fit_and_mean_against_the_oracle_at_scale(d, N, ell, eps):
+    import efgpnd
+    from kernels import SquaredExponential
+    O = oracle()
+    import fast_nufft as F
+    from pytorch_finufft import functional as exact
+    x, y = _data(N, d, 21 + d)
+    s2, neps, ctol = 0.1, 1e-9, 1e-10
+    kern = SquaredExponential(dimension=d, init_lengthscale=ell, init_variance=1.0)
+    m = efgpnd.EFGPND(x, y, kern, sigmasq=s2, eps=eps, nufft_eps=neps, opts={"cg_tolerance": ctol},
+                      estimate_params=False)
+    mean, _ = m.predict(x, return_variance=False)
+    xc, yc = x.cpu(), y.cpu()
+    ok = O.OracleKernel("se", d, ell, 1.0, param_dtype=torch.float64)
+    s2o = float(torch.exp(torch.log(torch.tensor(s2, dtype=torch.float64))))
+    f = O.fit(xc, yc, ok, s2o, eps, neps, cg_tol=ctol, backend=F)
+    assert m.last_fit_stats["mtot"] == f.mtot
+    assert abs(m.last_fit_stats["h"] - f.h) <= 1e-13 * f.h
+    # generator F^*1 (always at eps 6e-8, efgpnd.py:1418) and the right-hand side, grid for grid
+    assert rel(m._toeplitz.plan.v, f.v) < 10 * 6e-8
+    assert rel(m._beta, f.beta) < 1e-6
+    g = torch.Generator().manual_seed(5)
+    idx = torch.randint(0, N, (10000,), generator=g)
+    phi = (2 * math.pi * f.h * xc[idx]).T.contiguous()
+    mean_ref = exact.finufft_type2(phi, (f.ws * f.beta).reshape((f.mtot,) * d), isign=+1, modeord=False).real
+    assert rel(mean[idx.cuda()], mean_ref) < 1e-6
+    # the reference's default tolerances (the timed configuration): NUFFT contract 10 * eps on both sides
+    kern2 = SquaredExponential(dimension=d, init_lengthscale=ell, init_variance=1.0)
+    m2 = efgpnd.EFGPND(x, y, kern2, sigmasq=s2, eps=eps, nufft_eps=1e-4, opts={"cg_tolerance": 1e-4},
+                       estimate_params=False)
+    mean2, _ = m2.predict(x, return_variance=False)
+    assert rel(mean2[idx.cuda()], mean_ref) < 20 * 1e-4
+
+
+def test_type1_type2_against_fast_oracle_at_1e7():
+    """Operator level at N = 1e7 (2-D): both transforms against the C/OpenMP ES-kernel NUFFT with random complex modes
+    and strengths (no structure to hide a misplaced point), and clustered points (bucket imbalance)."""
+    from efgp_b200 import ops
+    oracle()
+    import fast_nufft as F
+    N, n, h, eps = 10_000_000, 47, 0.41, 1e-7
+    g = torch.Generator(device="cuda").manual_seed(9)
+    x = torch.rand(N, 2, dtype=torch.float64, device="cuda", generator=g) * 2 - 1
+    x[: N // 2] = 0.05 * torch.randn(N // 2, 2, dtype=torch.float64, device="cuda", generator=g) + 0.3   # a dense cluster
+    c = torch.randn(N, dtype=torch.float64, device="cuda", generator=g)
+    plan = ops.NufftPlan(x, h)
+    phi = (2 * math.pi * h * x.cpu()).T.contiguous()
+    t1 = plan.type1(c, (n, n), eps)
+    r1 = F.finufft_type1(phi, c.cpu().to(torch.complex128), (n, n), eps=1e-9, isign=-1, modeord=False)
+    assert rel(t1, r1) < 10 * eps
+    fk = torch.randn(n, n, dtype=torch.complex128, device="cuda", generator=g)
+    t2 = plan.type2(fk, (n, n), eps)
+    r2 = F.finufft_type2(phi, fk.cpu(), eps=1e-9, isign=+1, modeord=False)
+    assert rel(t2, r2) < 10 * eps

@@ -13,7 +13,9 @@ from conftest import GOLDEN
 
 pytestmark = pytest.mark.gpu
 
-CASES = ["cfg1_se1d", "se2d", "matern32_2d", "usa_f32", "se3d", "matern52_3d"]
+# cfg2_full: BASELINE.json configs[1] at its real size (all 1e5 points of gp_samples_100000_0.2_2_0.2.pt, Matern-3/2,
+# eps 1e-4: mtot 101, 201^2 generator), generated from the unmodified reference like the others
+CASES = ["cfg1_se1d", "se2d", "matern32_2d", "usa_f32", "se3d", "matern52_3d", "cfg2_full"]
 
 
 def rel(a, b):

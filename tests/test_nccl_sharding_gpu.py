@@ -1,0 +1,97 @@
+"""The NCCL paths of both shardings, checked against one rank (skipped on a box with fewer than 2 GPUs; run with
+`gpurun --gpus 2 -- python -m pytest tests/test_nccl_sharding_gpu.py`):
+
+  * points sharded (opts["shard_points"]): rank r holds a slice of ONE seeded data set; the all-reduced system must
+    give every rank the beta one rank computes from all points (1e-10), and the sharded means must be the slices of
+    the one-rank mean;
+  * probes sharded (opts["shard_probes"]): the NCCL variant of tests/test_probe_sharding_gpu.py.
+"""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import ROOT, PKG
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _data(N):
+    g = torch.Generator().manual_seed(17)
+    x = torch.rand(N, 2, dtype=torch.float64, generator=g) * 2 - 1
+    y = torch.sin(3 * x[:, 0]) * torch.cos(2 * x[:, 1]) + 0.1 * torch.randn(N, dtype=torch.float64, generator=g)
+    return x, y
+
+
+def _worker(rank, world, port, out_dir, mode):
+    import sys
+    for p in (PKG, ROOT):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    import efgpnd
+    from kernels import SquaredExponential
+    N = 300_000
+    x, y = _data(N)
+    kern = SquaredExponential(dimension=2, init_lengthscale=0.2, init_variance=1.0)
+    if mode == "points":
+        lo, hi = efgpnd.shard_bounds(N, world, rank)
+        xs, ys = x[lo:hi].to(dev), y[lo:hi].to(dev)
+        m = efgpnd.EFGPND(xs, ys, kern, sigmasq=0.05, eps=1e-4, nufft_eps=1e-9,
+                          opts={"cg_tolerance": 1e-11, "shard_points": world > 1}, estimate_params=False)
+        mean, _ = m.predict(xs, return_variance=False)
+        torch.save({"beta": m._beta.detach().cpu(), "mean": mean.detach().cpu(), "lo": lo, "hi": hi,
+                    "mtot": m.last_fit_stats["mtot"]}, os.path.join(out_dir, f"{mode}_w{world}_r{rank}.pt"))
+    else:
+        m = efgpnd.EFGPND(x.to(dev), y.to(dev), kern, sigmasq=0.05, eps=1e-4, opts={"shard_probes": True},
+                          estimate_params=False)
+        torch.manual_seed(1234)
+        g = m.compute_gradients(trace_samples=6, cg_tol=1e-9, nufft_eps=1e-9, apply_gradients=False)
+        torch.save({"grad": g.detach().cpu(), "stats": dict(m.last_gradient_stats.items())},
+                   os.path.join(out_dir, f"{mode}_w{world}_r{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+needs2 = pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2,
+                            reason="needs two GPUs (NCCL)")
+
+
+@needs2
+def test_point_sharded_beta_equals_one_rank_beta(tmp_path):
+    for world in (1, 2):
+        mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), "points"), nprocs=world, join=True)
+    one = torch.load(os.path.join(str(tmp_path), "points_w1_r0.pt"))
+    for r in range(2):
+        two = torch.load(os.path.join(str(tmp_path), f"points_w2_r{r}.pt"))
+        assert two["mtot"] == one["mtot"]
+        rb = float((two["beta"] - one["beta"]).norm() / one["beta"].norm())
+        assert rb < 1e-10, rb
+        ref = one["mean"][two["lo"]:two["hi"]]
+        rm = float((two["mean"] - ref).norm() / ref.norm())
+        assert rm < 1e-9, rm
+
+
+@needs2
+def test_probe_sharded_gradient_equals_one_rank_nccl(tmp_path):
+    for world in (1, 2):
+        mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), "probes"), nprocs=world, join=True)
+    one = torch.load(os.path.join(str(tmp_path), "probes_w1_r0.pt"))
+    for r in range(2):
+        two = torch.load(os.path.join(str(tmp_path), f"probes_w2_r{r}.pt"))
+        rel = float((two["grad"] - one["grad"]).norm() / one["grad"].norm())
+        assert rel < 1e-7, rel
+        assert two["stats"]["trace_num_rhs"] == one["stats"]["trace_num_rhs"] == 12
