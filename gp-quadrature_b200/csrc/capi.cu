@@ -373,4 +373,66 @@ int efgp_fit(efgp_nufft* nu, const void* y, const efgp_fit_args* args, void* ws,
   })
 }
 
+/* ---- posterior variance: device stages around the batched solves */
+int efgp_xcorr_mean(const void* us, const void* etas, const void* ws, int nprobes, int dim, int mtot, int dtype, void* out,
+                    void* stream) {
+  EFGP_TRY({
+    EFGP_ENTER(stream);
+    EFGP_CHECK(us != nullptr && etas != nullptr && out != nullptr, "null argument");
+    EFGP_CHECK(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    efgp::xcorr_mean(us, etas, ws, nprobes, dim, mtot, dtype, out, (cudaStream_t)stream);
+  })
+}
+
+int efgp_variance_rows(const void* x, int64_t npts, int dim, int mtot, double h, const void* ws, int dtype, void* rhs,
+                       void* stream) {
+  EFGP_TRY({
+    EFGP_ENTER(stream);
+    EFGP_CHECK(x != nullptr && ws != nullptr && rhs != nullptr && npts >= 0, "bad argument");
+    EFGP_CHECK(dim >= 1 && dim <= efgp::kMaxDim && mtot >= 1, "bad geometry");
+    efgp::variance_rows(x, npts, dim, mtot, h, ws, dtype, rhs, (cudaStream_t)stream);
+  })
+}
+
+int efgp_variance_reduce(const void* x, int64_t npts, int dim, int mtot, double h, const void* ws, int dtype,
+                         const void* gamma, void* var, void* stream) {
+  EFGP_TRY({
+    EFGP_ENTER(stream);
+    EFGP_CHECK(x != nullptr && ws != nullptr && gamma != nullptr && var != nullptr && npts >= 0, "bad argument");
+    EFGP_CHECK(dim >= 1 && dim <= efgp::kMaxDim && mtot >= 1, "bad geometry");
+    efgp::variance_reduce(x, npts, dim, mtot, h, ws, dtype, gamma, var, (cudaStream_t)stream);
+  })
+}
+
+/* ---- Hutchinson probes streamed through the transforms */
+int efgp_nufft_type1_probes(efgp_nufft* nu, uint64_t seed, int t0, int nprobes, const int64_t* out_shape, double eps,
+                            const void* scale, void* out, uint64_t* sort_id, void* stream) {
+  EFGP_TRY({
+    EFGP_ENTER(stream);
+    EFGP_CHECK(nu != nullptr && out_shape != nullptr && out != nullptr, "null argument");
+    nu->last_stream = (cudaStream_t)stream;
+    efgp::nufft_type1_probes(nu->nu, seed, t0, nprobes, out_shape, eps, scale, out, sort_id, (cudaStream_t)stream);
+  })
+}
+
+int efgp_nufft_type2_probe_dots(efgp_nufft* nu, uint64_t seed, int t0, int nprobes, const void* modes, const int64_t* shape,
+                                double eps, const void* scale, double* sums, uint64_t* sort_id, void* stream) {
+  EFGP_TRY({
+    EFGP_ENTER(stream);
+    EFGP_CHECK(nu != nullptr && modes != nullptr && shape != nullptr && sums != nullptr, "null argument");
+    nu->last_stream = (cudaStream_t)stream;
+    efgp::nufft_type2_probe_dots(nu->nu, seed, t0, nprobes, modes, shape, eps, scale, sums, sort_id, (cudaStream_t)stream);
+  })
+}
+
+int efgp_nufft_probes_export(efgp_nufft* nu, uint64_t seed, int t0, int nprobes, const int64_t* shape, double eps, void* z,
+                             uint64_t* sort_id, void* stream) {
+  EFGP_TRY({
+    EFGP_ENTER(stream);
+    EFGP_CHECK(nu != nullptr && shape != nullptr && z != nullptr, "null argument");
+    nu->last_stream = (cudaStream_t)stream;
+    efgp::nufft_probes_export(nu->nu, seed, t0, nprobes, shape, eps, z, sort_id, (cudaStream_t)stream);
+  })
+}
+
 }  // extern "C"

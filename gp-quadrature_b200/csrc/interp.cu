@@ -9,6 +9,7 @@
 // work is the kernel evaluation plus W^2 FMAs, and one scattered store of the result.
 #include "nufft.cuh"
 #include "stream_ring.cuh"
+#include "philox.cuh"
 
 namespace efgp {
 
@@ -301,6 +302,190 @@ interp_direct_kernel(const T* __restrict__ rec, int64_t npos, int nf0, int nf1, 
   out[bi] = acc;
 }
 
+// ------------------------------------------------------------------ fused Hutchinson epilogue
+// sum_n Z_t[n] * (F f_t)[n] without ever writing F f_t: the interpolation kernels below multiply each point's result by
+// the regenerated Rademacher sign (philox.cuh: the SAME (seed, probe, slot) stream the spread used) and reduce it --
+// per thread over its points, per CTA in shared memory, then a fixed-order sum over the CTA partials (deterministic).
+// This is term1 of the gradient (efgpnd.py:235-241: mean_t sum_n Z * Alpha); no (T, N) array exists.
+__device__ __forceinline__ double cta_sum(double v, double* sh) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) sh[w] = v;
+  __syncthreads();
+  double s = 0;
+  if (threadIdx.x == 0)
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) s += sh[i];
+  return s;   // valid in thread 0
+}
+
+template <typename T, int W, int NB>
+__global__ void __launch_bounds__(kTileThreads, ((W * W * NB <= 25) ? 2 : 1))
+interp2d_dot_kernel(const T* __restrict__ rec, int P, int nf0, int nf1, const T* __restrict__ grid,
+                    double* __restrict__ partial, const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
+  constexpr int S = kRingStages;
+  __shared__ __align__(16) T ring[S][kTileThreads][2];
+  __shared__ double sh[kTileThreads / 32];
+  const int t = threadIdx.x;
+  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + t;
+  auto issue = [&](int j) {
+    if (j < P) {
+      const T* src = rec + (base + (int64_t)j * kTileThreads) * 4;
+      cp_async_word<2 * sizeof(T)>(&ring[j % S][t][0], src);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int j = 0; j < S - 1; ++j) issue(j);
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  const int64_t cells = (int64_t)nf0 * nf1;
+  T g[NB][W][W];
+  double sum[NB];
+#pragma unroll
+  for (int b = 0; b < NB; ++b) sum[b] = 0;
+  int cur0 = -1, cur1 = -1;
+  for (int j = 0; j < P; ++j) {
+    issue(j + S - 1);
+    cp_async_wait<S - 1>();
+    const int s = j % S;
+    const T X0 = ring[s][t][0];
+    if (X0 < T(0)) break;
+    const T X1 = ring[s][t][1];
+    int c0 = (int)X0, c1 = (int)X1;
+    if (c0 != cur0 || c1 != cur1) {
+      int cols[W];
+#pragma unroll
+      for (int jj = 0; jj < W; ++jj) cols[jj] = wrap_i(c1 - OFF + jj, nf1);
+#pragma unroll
+      for (int i = 0; i < W; ++i) {
+        const T* row = grid + (int64_t)wrap_i(c0 - OFF + i, nf0) * nf1;
+#pragma unroll
+        for (int b = 0; b < NB; ++b)
+#pragma unroll
+          for (int jj = 0; jj < W; ++jj) g[b][i][jj] = __ldg(row + b * cells + cols[jj]);
+      }
+      cur0 = c0;
+      cur1 = c1;
+    }
+    T k0[W], k1[W];
+    es_eval_i<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
+    es_eval_i<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
+    uint32_t bits[4];
+    philox_bits(pr.seed, (uint64_t)(base + (int64_t)j * kTileThreads), (uint32_t)(pr.t0 >> 7), bits);
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+      T acc = 0;
+#pragma unroll
+      for (int i = 0; i < W; ++i) {
+        T r = 0;
+#pragma unroll
+        for (int jj = 0; jj < W; ++jj) r = fma(g[b][i][jj], k1[jj], r);
+        acc = fma(r, k0[i], acc);
+      }
+      sum[b] += (double)(philox_sign_from_bits<T>(bits, pr.t0 + b) * acc);
+    }
+  }
+  cp_async_wait<0>();
+#pragma unroll
+  for (int b = 0; b < NB; ++b) {
+    const double tot = cta_sum(sum[b], sh);
+    if (t == 0) partial[(int64_t)blockIdx.x * NB + b] = tot;
+  }
+}
+
+// 1-D, wide 2-D and 3-D: one slot per thread (as interp_direct_kernel), one probe per launch
+template <typename T, int W, int D>
+__global__ void __launch_bounds__(256)
+interp_direct_dot_kernel(const T* __restrict__ rec, int64_t npos, int nf0, int nf1, int nf2, const T* __restrict__ grid,
+                         double* __restrict__ partial, const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
+  __shared__ double sh[8];
+  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  constexpr int RWD = D == 1 ? 2 : 4;
+  double val = 0;
+  if (n < npos) {
+    T Xr[4] = {T(0), T(0), T(0), T(0)};
+    if constexpr (D == 1) {
+      Xr[0] = rec[n * 2];
+    } else {
+      load_record4i<T>(rec + n * RWD, Xr);
+    }
+    const T X0 = Xr[0];
+    if (!(X0 < T(0))) {
+      T k0[W], k1[W], k2[W];
+      const int c0 = (int)X0;
+      es_eval_i<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
+      T acc = 0;
+      if constexpr (D == 1) {
+#pragma unroll
+        for (int i = 0; i < W; ++i) acc = fma(__ldg(grid + wrap_i(c0 - OFF + i, nf0)), k0[i], acc);
+      } else {
+        const T X1 = Xr[1];
+        const int c1 = (int)X1;
+        es_eval_i<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
+        if constexpr (D == 2) {
+#pragma unroll
+          for (int i = 0; i < W; ++i) {
+            const T* row = grid + (int64_t)wrap_i(c0 - OFF + i, nf0) * nf1;
+            T r = 0;
+#pragma unroll
+            for (int j = 0; j < W; ++j) r = fma(__ldg(row + wrap_i(c1 - OFF + j, nf1)), k1[j], r);
+            acc = fma(r, k0[i], acc);
+          }
+        } else {
+          const T X2 = Xr[2];
+          const int c2 = (int)X2;
+          es_eval_i<T, W>(es, T(2) * (X2 - (T)c2) - T(1), k2);
+          int cols[W];
+#pragma unroll
+          for (int l = 0; l < W; ++l) cols[l] = wrap_i(c2 - OFF + l, nf2);
+#pragma unroll 1
+          for (int i = 0; i < W; ++i) {
+            const int64_t r0 = (int64_t)wrap_i(c0 - OFF + i, nf0) * nf1;
+            T ri = 0;
+#pragma unroll 1
+            for (int j = 0; j < W; ++j) {
+              const T* row = grid + (r0 + wrap_i(c1 - OFF + j, nf1)) * nf2;
+              T r = 0;
+#pragma unroll
+              for (int l = 0; l < W; ++l) r = fma(__ldg(row + cols[l]), k2[l], r);
+              ri = fma(r, k1[j], ri);
+            }
+            acc = fma(ri, k0[i], acc);
+          }
+        }
+      }
+      uint32_t bits[4];
+      philox_bits(pr.seed, (uint64_t)n, (uint32_t)(pr.t0 >> 7), bits);
+      val = (double)(philox_sign_from_bits<T>(bits, pr.t0) * acc);
+    }
+  }
+  const double tot = cta_sum(val, sh);
+  if (threadIdx.x == 0) partial[blockIdx.x] = tot;
+}
+
+// out[b] = sum over CTAs of partial[cta * nb + b], fixed order: one CTA per probe
+__global__ void __launch_bounds__(256)
+probe_dot_reduce_kernel(const double* __restrict__ partial, int64_t nctas, int nb, double* __restrict__ out) {
+  __shared__ double sh[8];
+  const int b = blockIdx.x;
+  double v = 0;
+  for (int64_t c = threadIdx.x; c < nctas; c += blockDim.x) v += partial[c * nb + b];
+  const double tot = cta_sum(v, sh);
+  if (threadIdx.x == 0) out[b] = tot;
+}
+
+// Z itself, slot order (tests / the parity path compare the regenerated probes with explicit ones)
+template <typename T>
+__global__ void __launch_bounds__(256)
+probe_fill_kernel(const T* __restrict__ rec, int RW, int64_t npos, T* __restrict__ z, ProbeSpec pr) {
+  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= npos) return;
+  uint32_t bits[4];
+  philox_bits(pr.seed, (uint64_t)n, (uint32_t)(pr.t0 >> 7), bits);
+  z[n] = rec[n * RW] < T(0) ? T(0) : philox_sign_from_bits<T>(bits, pr.t0);
+}
+
 template <typename T, int W>
 static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* grid, T* out, int64_t ostride,
                      cudaStream_t st) {
@@ -365,6 +550,107 @@ void launch_interp(const SortedPoints& sp, const ESKernel& k, const void* grid, 
     launch_t<double>(sp, k, (const double*)grid, (double*)tmp, 1, st);
   unpermute_output(sp, tmp, out, ostride, st);
   pool_free(tmp);  // stream-ordered reuse
+}
+
+template <typename T, int W>
+static void launch_dot_w(const SortedPoints& sp, const ESKernel& k, const T* grid, double* out, const ProbeSpec& pr,
+                         cudaStream_t st) {
+  ESDev<T> es;
+  es_to_dev<T>(k, es);
+  const T* rec = (const T*)sp.rec;
+  constexpr int kRegMaxW = sizeof(T) == 8 ? 9 : 10;
+  char nm[56];
+  snprintf(nm, sizeof(nm), "interp%dd_w%d_%s_dot%d", sp.dim, W, sizeof(T) == 8 ? "f64" : "f32", pr.nb);
+  ScopedStage stg(nm, st, 2, sp.N * pr.nb);
+  int64_t nctas = 0;
+  double* partial = nullptr;
+  if (sp.dim == 2 && W <= kRegMaxW) {
+    nctas = sp.ntiles;
+    partial = (double*)pool_alloc(sizeof(double) * (size_t)nctas * pr.nb);
+    if constexpr (W <= kRegMaxW) {
+      bool done = false;
+      if constexpr (W <= 5) {
+        if (pr.nb == 4) {
+          interp2d_dot_kernel<T, W, 4><<<(int)nctas, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
+                                                                            partial, es, pr);
+          done = true;
+        }
+      }
+      if constexpr (W <= 7) {
+        if (!done && pr.nb == 2) {
+          interp2d_dot_kernel<T, W, 2><<<(int)nctas, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
+                                                                            partial, es, pr);
+          done = true;
+        }
+      }
+      if (!done) {
+        EFGP_CHECK(pr.nb == 1, "probe batch not supported by this interpolation width");
+        interp2d_dot_kernel<T, W, 1><<<(int)nctas, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
+                                                                          partial, es, pr);
+      }
+    }
+  } else {
+    EFGP_CHECK(pr.nb == 1, "one probe per launch for this geometry");
+    nctas = div_up(sp.npos, 256);
+    partial = (double*)pool_alloc(sizeof(double) * (size_t)nctas);
+    if (sp.dim == 1)
+      interp_direct_dot_kernel<T, W, 1><<<(int)nctas, 256, 0, st>>>(rec, sp.npos, (int)sp.nf[0], 1, 1, grid, partial, es, pr);
+    else if (sp.dim == 2)
+      interp_direct_dot_kernel<T, W, 2><<<(int)nctas, 256, 0, st>>>(rec, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid,
+                                                                    partial, es, pr);
+    else
+      interp_direct_dot_kernel<T, W, 3><<<(int)nctas, 256, 0, st>>>(rec, sp.npos, (int)sp.nf[0], (int)sp.nf[1],
+                                                                    (int)sp.nf[2], grid, partial, es, pr);
+  }
+  EFGP_CUDA(cudaGetLastError());
+  probe_dot_reduce_kernel<<<pr.nb, 256, 0, st>>>(partial, nctas, pr.nb, out);
+  EFGP_CUDA(cudaGetLastError());
+  pool_free(partial);   // stream-ordered reuse
+}
+
+template <typename T>
+static void launch_dot_t(const SortedPoints& sp, const ESKernel& k, const T* grid, double* out, const ProbeSpec& pr,
+                         cudaStream_t st) {
+  switch (k.W) {
+#define EFGP_CASE(w) \
+  case w:            \
+    launch_dot_w<T, w>(sp, k, grid, out, pr, st); \
+    break;
+    EFGP_CASE(2) EFGP_CASE(3) EFGP_CASE(4) EFGP_CASE(5) EFGP_CASE(6) EFGP_CASE(7) EFGP_CASE(8) EFGP_CASE(9)
+    EFGP_CASE(10) EFGP_CASE(11) EFGP_CASE(12) EFGP_CASE(13) EFGP_CASE(14) EFGP_CASE(15) EFGP_CASE(16)
+#undef EFGP_CASE
+    default:
+      throw Error(1, "unsupported interpolation width");
+  }
+}
+
+// out[b] = sum_n Rademacher(seed, pr.t0 + b, slot(n)) * (interpolation of grid b at point n),  b < pr.nb
+void launch_interp_probe_dots(const SortedPoints& sp, const ESKernel& k, const void* grid, double* out,
+                              const ProbeSpec& pr, cudaStream_t st) {
+  EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
+  EFGP_CHECK(pr.nb >= 1 && (pr.t0 >> 7) == ((pr.t0 + pr.nb - 1) >> 7), "a probe launch must stay inside one 128-probe block");
+  if (sp.N == 0) {
+    EFGP_CUDA(cudaMemsetAsync(out, 0, sizeof(double) * pr.nb, st));
+    return;
+  }
+  if (sp.dtype == 0)
+    launch_dot_t<float>(sp, k, (const float*)grid, out, pr, st);
+  else
+    launch_dot_t<double>(sp, k, (const double*)grid, out, pr, st);
+}
+
+// z (N,) in ORIGINAL point order = the probe pr.t0 the kernels regenerate for this sorted set
+void launch_probe_export(const SortedPoints& sp, void* z_out, int64_t ostride, const ProbeSpec& pr, cudaStream_t st) {
+  if (sp.N == 0) return;
+  const size_t esz = sp.dtype == 0 ? 4 : 8;
+  void* tmp = pool_alloc(esz * (size_t)sp.npos);
+  if (sp.dtype == 0)
+    probe_fill_kernel<float><<<div_up(sp.npos, 256), 256, 0, st>>>((const float*)sp.rec, sp.RW, sp.npos, (float*)tmp, pr);
+  else
+    probe_fill_kernel<double><<<div_up(sp.npos, 256), 256, 0, st>>>((const double*)sp.rec, sp.RW, sp.npos, (double*)tmp, pr);
+  EFGP_CUDA(cudaGetLastError());
+  unpermute_output(sp, tmp, z_out, ostride, st);
+  pool_free(tmp);
 }
 
 }  // namespace efgp

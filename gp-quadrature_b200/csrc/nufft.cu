@@ -10,6 +10,7 @@
 // transforms; complex type-2 outputs are the transforms of the Hermitian and anti-Hermitian parts
 // of the mode array), so every FFT is R2C/C2R on half the data of a complex transform.
 #include "nufft.cuh"
+#include "philox.cuh"
 #include <mutex>
 #include <map>
 #include <utility>
@@ -286,6 +287,8 @@ static SortedPoints* get_sorted(Nufft& nu, const int64_t* nf, int odd, cudaStrea
     nu.sorted.erase(nu.sorted.begin() + j);
   }
   std::unique_ptr<SortedPoints> sp(new SortedPoints());
+  static uint64_t next_id = 0;
+  sp->id = ++next_id;
   build_sorted_points(*sp, nu.x, nu.pending_payload, nu.N, nu.dim, nu.dtype, nu.h, nu.xcen, nf, odd, st);
   if (sp->has_payload) nu.fresh_payload_sp = sp.get();
   sp->last_use = ++nu.clock;
@@ -354,7 +357,15 @@ static double pick_sigma(const Nufft& nu, const int64_t* n, double eps, int64_t*
     const size_t esz = nu.dtype == 0 ? 4 : 8;
     const bool fits = cells < 3.9e9 && cells * esz <= (double)((size_t)2 << 30);
     if (!fits && best_sigma > 0) break;
-    const double cost = transform_cost(nu.dim, (double)nu.N, w, cells);
+    double cost = transform_cost(nu.dim, (double)nu.N, w, cells);
+    if (nu.dim <= 2) {
+      // this grid also keys the cell sort: the level-2 counting sort pays per (2048-point tile, bin) pair, measured at
+      // N = 1e8 as 1.2 ms + 1.35e-6 ms per cell (288^2 .. 864^2 cells) = 1.6e-4 FMA-times per point and cell
+      cost += 1.6e-4 * cells * (double)nu.N;
+      // an even width fixes the parity of every later transform on these sorted points: the narrow F*y / type-2
+      // kernels (odd W = 5 at the reference's default eps) would be forced one step wider
+      if (nu.dim == 2 && (w % 2) == 0) cost += 40.0 * (double)nu.N;
+    }
     if (best_sigma == 0 || cost < best_cost) {
       best_cost = cost;
       best_sigma = sg;
@@ -582,6 +593,146 @@ void nufft_type2(Nufft& nu, const void* modes, int batch, const int64_t* n, doub
     type2_t<float>(nu, modes, batch, n, eps, isign, modeord, scale, real_out, out, st);
   else
     type2_t<double>(nu, modes, batch, n, eps, isign, modeord, scale, real_out, out, st);
+}
+
+// ------------------------------------------------------------------ streamed Hutchinson probes
+static int probe_group(int t, int remaining, int nb_max) {
+  int g = 1;
+  while (g * 2 <= nb_max && g * 2 <= remaining) g *= 2;
+  while (g > 1 && (t >> 7) != ((t + g - 1) >> 7)) g /= 2;
+  return g;
+}
+
+static void check_sort_id(const SortedPoints& sp, uint64_t* sort_id) {
+  if (!sort_id) return;
+  if (*sort_id == 0)
+    *sort_id = sp.id;
+  else
+    EFGP_CHECK(*sort_id == sp.id,
+               "the sorted point set changed between two transforms of the same probes: the regenerated Rademacher "
+               "signs are tied to the point order (re-run the type-1 stage)");
+}
+
+template <typename T>
+static void type1_probes_t(Nufft& nu, uint64_t seed, int t0, int nb_total, const int64_t* n, double eps, const void* scale,
+                           void* out, uint64_t* sort_id, cudaStream_t st) {
+  using C = typename cplx_of<T>::type;
+  const int dim = nu.dim;
+  GridChoice gc = choose_grid(nu, n, eps, st);
+  check_sort_id(*gc.sp, sort_id);
+  ModeGeom g = make_geom(dim, n, gc.nf, 0, 0);
+  void* dinv[kMaxDim];
+  upload_dinv(nu, gc.ker, gc.nf, n, dim, nu.dtype, dinv, st);
+  int64_t cells = 1, slab = 1;
+  for (int a = 0; a < dim; ++a) {
+    cells *= gc.nf[a];
+    slab *= (a == dim - 1 ? gc.nf[a] / 2 + 1 : gc.nf[a]);
+  }
+  const int64_t per = cells * (int64_t)sizeof(T) + slab * (int64_t)sizeof(C);
+  const int chunk = (int)std::max<int64_t>(1, std::min<int64_t>(nb_total, (8ll << 30) / std::max<int64_t>(per, 1)));
+  T* fine = (T*)nu.fine.get((size_t)chunk * cells * sizeof(T));
+  C* spec = (C*)nu.spec.get((size_t)chunk * slab * sizeof(C));
+  const int nb_max = spread_probe_batch(dim, gc.ker.W, nu.dtype);
+  for (int b0 = 0; b0 < nb_total; b0 += chunk) {
+    const int nb = std::min(chunk, nb_total - b0);
+    {
+      ScopedStage stg("type1.memset_fine", st, 0);
+      EFGP_CUDA(cudaMemsetAsync(fine, 0, (size_t)nb * cells * sizeof(T), st));
+    }
+    for (int b = 0; b < nb;) {
+      const int gsz = probe_group(t0 + b0 + b, nb - b, nb_max);
+      launch_spread_probes(*gc.sp, gc.ker, fine + (int64_t)b * cells, ProbeSpec{seed, t0 + b0 + b, gsz}, st);
+      b += gsz;
+    }
+    cufftHandle plan = global_fft().get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_R2C : CUFFT_D2Z, nb, st);
+    {
+      ScopedStage stg("type1.cufft_r2c", st, 0);
+      if (sizeof(T) == 4)
+        EFGP_CUFFT(cufftExecR2C(plan, (cufftReal*)fine, (cufftComplex*)spec));
+      else
+        EFGP_CUFFT(cufftExecD2Z(plan, (cufftDoubleReal*)fine, (cufftDoubleComplex*)spec));
+    }
+    const int64_t tot = g.M * nb;
+    ScopedStage stg("type1.deconv_kernel", st);
+    deconv_kernel<T><<<div_up(tot, 256), 256, 0, st>>>(spec, 1, nb, g, (const T*)dinv[0], (const T*)dinv[1],
+                                                       (const T*)dinv[2], (const T*)scale, (C*)out + (int64_t)b0 * g.M);
+    EFGP_CUDA(cudaGetLastError());
+  }
+}
+
+template <typename T>
+static void type2_probe_dots_t(Nufft& nu, uint64_t seed, int t0, int nb_total, const void* modes, const int64_t* n,
+                               double eps, const void* scale, double* sums, uint64_t* sort_id, cudaStream_t st) {
+  using C = typename cplx_of<T>::type;
+  const int dim = nu.dim;
+  GridChoice gc = choose_grid(nu, n, eps, st);
+  check_sort_id(*gc.sp, sort_id);
+  ModeGeom g = make_geom(dim, n, gc.nf, 0, 0);       // isign = +1, centred modes
+  void* dinv[kMaxDim];
+  upload_dinv(nu, gc.ker, gc.nf, n, dim, nu.dtype, dinv, st);
+  int64_t cells = 1, slab = 1;
+  for (int a = 0; a < dim; ++a) {
+    cells *= gc.nf[a];
+    slab *= (a == dim - 1 ? gc.nf[a] / 2 + 1 : gc.nf[a]);
+  }
+  const int64_t per = cells * (int64_t)sizeof(T) + slab * (int64_t)sizeof(C);
+  const int chunk = (int)std::max<int64_t>(1, std::min<int64_t>(nb_total, (8ll << 30) / std::max<int64_t>(per, 1)));
+  T* fine = (T*)nu.fine.get((size_t)chunk * cells * sizeof(T));
+  C* spec = (C*)nu.spec.get((size_t)chunk * slab * sizeof(C));
+  const int nb_max = spread_probe_batch(dim, gc.ker.W, nu.dtype);
+  for (int b0 = 0; b0 < nb_total; b0 += chunk) {
+    const int nb = std::min(chunk, nb_total - b0);
+    const int64_t tot = slab * nb;
+    {
+      ScopedStage stg("type2.precorrect_kernel", st);
+      precorrect_kernel<T><<<div_up(tot, 256), 256, 0, st>>>((const C*)modes + (int64_t)b0 * g.M, 1, nb, g, (const T*)dinv[0],
+                                                             (const T*)dinv[1], (const T*)dinv[2], (const T*)scale, spec);
+      EFGP_CUDA(cudaGetLastError());
+    }
+    cufftHandle plan = global_fft().get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_C2R : CUFFT_Z2D, nb, st);
+    {
+      ScopedStage stg("type2.cufft_c2r", st, 0);
+      if (sizeof(T) == 4)
+        EFGP_CUFFT(cufftExecC2R(plan, (cufftComplex*)spec, (cufftReal*)fine));
+      else
+        EFGP_CUFFT(cufftExecZ2D(plan, (cufftDoubleComplex*)spec, (cufftDoubleReal*)fine));
+    }
+    for (int b = 0; b < nb;) {
+      const int gsz = probe_group(t0 + b0 + b, nb - b, nb_max);
+      launch_interp_probe_dots(*gc.sp, gc.ker, fine + (int64_t)b * cells, sums + b0 + b, ProbeSpec{seed, t0 + b0 + b, gsz}, st);
+      b += gsz;
+    }
+  }
+}
+
+void nufft_type1_probes(Nufft& nu, uint64_t seed, int t0, int nb, const int64_t* n, double eps, const void* scale, void* out,
+                        uint64_t* sort_id, cudaStream_t st) {
+  EFGP_CHECK(nb >= 1 && t0 >= 0, "bad probe range");
+  for (int a = 0; a < nu.dim; ++a) EFGP_CHECK(n[a] >= 1, "mode counts must be >= 1");
+  if (nu.dtype == 0)
+    type1_probes_t<float>(nu, seed, t0, nb, n, eps, scale, out, sort_id, st);
+  else
+    type1_probes_t<double>(nu, seed, t0, nb, n, eps, scale, out, sort_id, st);
+}
+
+void nufft_type2_probe_dots(Nufft& nu, uint64_t seed, int t0, int nb, const void* modes, const int64_t* n, double eps,
+                            const void* scale, double* sums, uint64_t* sort_id, cudaStream_t st) {
+  EFGP_CHECK(nb >= 1 && t0 >= 0, "bad probe range");
+  for (int a = 0; a < nu.dim; ++a) EFGP_CHECK(n[a] >= 1, "mode counts must be >= 1");
+  if (nu.dtype == 0)
+    type2_probe_dots_t<float>(nu, seed, t0, nb, modes, n, eps, scale, sums, sort_id, st);
+  else
+    type2_probe_dots_t<double>(nu, seed, t0, nb, modes, n, eps, scale, sums, sort_id, st);
+}
+
+void nufft_probes_export(Nufft& nu, uint64_t seed, int t0, int nb, const int64_t* n, double eps, void* z, uint64_t* sort_id,
+                         cudaStream_t st) {
+  EFGP_CHECK(nb >= 1 && t0 >= 0, "bad probe range");
+  GridChoice gc = choose_grid(nu, n, eps, st);
+  check_sort_id(*gc.sp, sort_id);
+  const size_t esz = nu.dtype == 0 ? 4 : 8;
+  for (int b = 0; b < nb; ++b)
+    launch_probe_export(*gc.sp, (char*)z + (size_t)b * nu.N * esz, 1, ProbeSpec{seed, t0 + b, 1}, st);
 }
 
 }  // namespace efgp

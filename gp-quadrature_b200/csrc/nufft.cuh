@@ -37,6 +37,7 @@ struct SortedPoints {
   uint32_t* tileStart = nullptr;  // [nb1][ntiles1]: first level-1 position of (bucket, 2048-point tile)
   int ntiles1 = 0, nb1 = 0;
   uint64_t last_use = 0;
+  uint64_t id = 0;            // unique per build: the regenerated probes are a function of (seed, probe, slot)
   ~SortedPoints();
 };
 __host__ __device__ constexpr int rec_words(int dim) { return dim == 1 ? 2 : 4; }
@@ -105,6 +106,15 @@ void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t 
 void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, void* grid, cudaStream_t st,
                    bool from_record = false);
 
+// ---- Rademacher probes regenerated inside the kernels (philox.cuh): spread of pr.nb probes into pr.nb contiguous
+// grids, interpolation with the fused sum_n Z * (.) epilogue, and Z itself in original order (tests)
+struct ProbeSpec;
+int spread_probe_batch(int dim, int W, int dtype);
+void launch_spread_probes(const SortedPoints& sp, const ESKernel& k, void* grid, const ProbeSpec& pr, cudaStream_t st);
+void launch_interp_probe_dots(const SortedPoints& sp, const ESKernel& k, const void* grid, double* out,
+                              const ProbeSpec& pr, cudaStream_t st);
+void launch_probe_export(const SortedPoints& sp, void* z_out, int64_t ostride, const ProbeSpec& pr, cudaStream_t st);
+
 // ---- interp.cu : out[i * ostride] = sum_l grid[l] psi(l - X_i)  (i = original point index)
 void launch_interp(const SortedPoints& sp, const ESKernel& k, const void* grid, void* out,
                    int64_t ostride, cudaStream_t st);
@@ -118,5 +128,16 @@ void nufft_type1_pair(Nufft& nu, const void* y, const int64_t* shape_gen, double
                       double eps_rhs, const void* scale, void* out_gen, void* out_rhs, cudaStream_t st);
 void nufft_type2(Nufft& nu, const void* modes, int batch, const int64_t* n, double eps, int isign, int modeord,
                  const void* scale, int real_out, void* out, cudaStream_t st);
+// Hutchinson probes streamed through the transforms (efgpnd.py:176-241 without the (T, N) arrays):
+//   type1_probes:     out[b] = scale * F^* Z_{t0+b}            (nb, *n) complex, Z regenerated in the spread kernel
+//   type2_probe_dots: sums[b] = sum_n Z_{t0+b}[n] Re(F f_b)[n]  modes (nb, *n) complex -> (nb,) float64
+//   probes_export:    Z_{t0..t0+nb-1} in original point order   (nb, N) real
+// All three must see the same sorted point set: `sort_id` returns / checks its identity.
+void nufft_type1_probes(Nufft& nu, uint64_t seed, int t0, int nb, const int64_t* n, double eps, const void* scale, void* out,
+                        uint64_t* sort_id, cudaStream_t st);
+void nufft_type2_probe_dots(Nufft& nu, uint64_t seed, int t0, int nb, const void* modes, const int64_t* n, double eps,
+                            const void* scale, double* sums, uint64_t* sort_id, cudaStream_t st);
+void nufft_probes_export(Nufft& nu, uint64_t seed, int t0, int nb, const int64_t* n, double eps, void* z, uint64_t* sort_id,
+                         cudaStream_t st);
 
 }  // namespace efgp

@@ -14,6 +14,7 @@
 // flush per point for sparse cases.
 #include "nufft.cuh"
 #include "stream_ring.cuh"
+#include "philox.cuh"
 
 namespace efgp {
 
@@ -64,10 +65,10 @@ __device__ __forceinline__ int wrap_idx(int i, int n) {
 // Slot addressing of the tile-transposed sorted layout (nufft.cuh): thread t of tile `blockIdx.x`
 // reads its j-th point at base + j*kTileThreads.
 // ------------------------------------------------------------------ 1-D
-template <typename T, int W, bool HAS_C>
+template <typename T, int W, int HAS_C>
 __global__ void __launch_bounds__(kTileThreads)
 spread1d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int nf0, T* __restrict__ grid,
-                const __grid_constant__ ESDev<T> es) {
+                const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
   const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
   T acc[W];
 #pragma unroll
@@ -78,7 +79,12 @@ spread1d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
     const int64_t pos = base + (int64_t)j * kTileThreads;
     T X = rec[pos * 2];
     if (X < T(0)) break;
-    T cv = HAS_C ? cs[pos] : T(1);
+    T cv = HAS_C == 1 ? cs[pos] : T(1);
+    if (HAS_C == 3) {
+      uint32_t bits[4];
+      philox_bits(pr.seed, (uint64_t)pos, (uint32_t)(pr.t0 >> 7), bits);
+      cv = philox_sign_from_bits<T>(bits, pr.t0);
+    }
     int c0 = (int)X;
     if (c0 != cur) {
       if (cur >= 0) {
@@ -118,14 +124,21 @@ __device__ __forceinline__ void flush2d(T (&acc)[W][W], int c0, int c1, int nf0,
   }
 }
 
-// HAS_C: 0 = all-ones strengths, 1 = strengths in slot order (cs), 2 = strengths in the records' payload word
-template <typename T, int W, int HAS_C>
-__global__ void __launch_bounds__(kTileThreads, (W <= 5 ? 2 : 1))
+// HAS_C: 0 = all-ones strengths, 1 = strengths in slot order (cs), 2 = strengths in the records' payload word,
+// 3 = Rademacher probes regenerated from (seed, probe, slot) (philox.cuh).  NB > 1 (mode 3 only): NB probes in ONE pass
+// over the points -- the record is read and the 2 W kernel weights are evaluated once per point, then applied to NB
+// register footprints (grid b = grid + b * nf0 * nf1), which is what makes a Hutchinson batch cheaper than NB transforms.
+template <int W, int NB>
+__host__ __device__ constexpr int spread2d_min_ctas() { return (W * W * NB <= 25) ? 2 : 1; }
+
+template <typename T, int W, int HAS_C, int NB>
+__global__ void __launch_bounds__(kTileThreads, (spread2d_min_ctas<W, NB>()))
 spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int nf0,
-                int nf1, T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
+                int nf1, T* __restrict__ grid, const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
+  static_assert(NB == 1 || HAS_C == 3, "multi-RHS spreading is for regenerated probes");
   constexpr int S = kRingStages;
   __shared__ __align__(16) T ring[S][kTileThreads][2];   // (X0, X1) of each thread's next points
-  __shared__ T cring[HAS_C ? S : 1][kTileThreads];
+  __shared__ T cring[(HAS_C == 1 || HAS_C == 2) ? S : 1][kTileThreads];
   const int t = threadIdx.x;
   const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + t;
   auto issue = [&](int j) {
@@ -140,11 +153,14 @@ spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
   };
 #pragma unroll
   for (int j = 0; j < S - 1; ++j) issue(j);
-  T acc[W][W];
+  T acc[NB][W][W];
 #pragma unroll
-  for (int i = 0; i < W; ++i)
+  for (int b = 0; b < NB; ++b)
 #pragma unroll
-    for (int j = 0; j < W; ++j) acc[i][j] = 0;
+    for (int i = 0; i < W; ++i)
+#pragma unroll
+      for (int j = 0; j < W; ++j) acc[b][i][j] = 0;
+  const int64_t cells = (int64_t)nf0 * nf1;
   int cur0 = -1, cur1 = -1;
   for (int j = 0; j < P; ++j) {
     issue(j + S - 1);
@@ -153,10 +169,21 @@ spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
     const T X0 = ring[s][t][0];
     if (X0 < T(0)) break;
     const T X1 = ring[s][t][1];
-    const T cv = HAS_C ? cring[s][t] : T(1);
+    T cv[NB];
+#pragma unroll
+    for (int b = 0; b < NB; ++b) cv[b] = (HAS_C == 1 || HAS_C == 2) ? cring[s][t] : T(1);
+    if (HAS_C == 3) {
+      uint32_t bits[4];
+      philox_bits(pr.seed, (uint64_t)(base + (int64_t)j * kTileThreads), (uint32_t)(pr.t0 >> 7), bits);
+#pragma unroll
+      for (int b = 0; b < NB; ++b) cv[b] = philox_sign_from_bits<T>(bits, pr.t0 + b);
+    }
     int c0 = (int)X0, c1 = (int)X1;
     if (c0 != cur0 || c1 != cur1) {
-      if (cur0 >= 0) flush2d<T, W>(acc, cur0, cur1, nf0, nf1, grid);
+      if (cur0 >= 0) {
+#pragma unroll
+        for (int b = 0; b < NB; ++b) flush2d<T, W>(acc[b], cur0, cur1, nf0, nf1, grid + b * cells);
+      }
       cur0 = c0;
       cur1 = c1;
     }
@@ -164,14 +191,20 @@ spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
     es_eval<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
     es_eval<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
 #pragma unroll
-    for (int i = 0; i < W; ++i) {
-      T a = cv * k0[i];
+    for (int b = 0; b < NB; ++b) {
 #pragma unroll
-      for (int jj = 0; jj < W; ++jj) acc[i][jj] = fma(a, k1[jj], acc[i][jj]);
+      for (int i = 0; i < W; ++i) {
+        T a = cv[b] * k0[i];
+#pragma unroll
+        for (int jj = 0; jj < W; ++jj) acc[b][i][jj] = fma(a, k1[jj], acc[b][i][jj]);
+      }
     }
   }
   cp_async_wait<0>();
-  if (cur0 >= 0) flush2d<T, W>(acc, cur0, cur1, nf0, nf1, grid);
+  if (cur0 >= 0) {
+#pragma unroll
+    for (int b = 0; b < NB; ++b) flush2d<T, W>(acc[b], cur0, cur1, nf0, nf1, grid + b * cells);
+  }
 }
 
 // ------------------------------------------------------------------ 3-D, shared-memory tile accumulation
@@ -195,10 +228,10 @@ __host__ __device__ constexpr size_t tile3_smem_bytes() {
   return sizeof(T) * (size_t)(E * E * EP + kT3Batch * 3 * W + kT3Batch) + sizeof(int) * kT3Batch * 4;
 }
 
-template <typename T, int W, bool HAS_C>
+template <typename T, int W, int HAS_C>
 __global__ void __launch_bounds__(kT3Threads)
 spread3d_tile_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int64_t N, int nf0, int nf1, int nf2,
-                     T* __restrict__ grid, const __grid_constant__ ESDev<T> es) {
+                     T* __restrict__ grid, const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
   constexpr int E = kTile3 + W - 1;
   constexpr int EP = E | 1;   // padded (odd) row stride
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
@@ -252,7 +285,13 @@ spread3d_tile_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int64_
       for (int i = 0; i < W; ++i) KW[(pt * 3 + ax) * W + i] = kk[i];
       BI[pt * 4 + 1 + ax] = c;
     } else if (tid >= 96 && tid < 96 + nb) {
-      CV[tid - 96] = HAS_C ? cs[b0 + tid - 96] : T(1);
+      T cvv = HAS_C == 1 ? cs[b0 + tid - 96] : T(1);
+      if (HAS_C == 3) {                      // 3-D sets keep rank order (P = 1): the slot is the sorted rank
+        uint32_t bits[4];
+        philox_bits(pr.seed, (uint64_t)(b0 + tid - 96), (uint32_t)(pr.t0 >> 7), bits);
+        cvv = philox_sign_from_bits<T>(bits, pr.t0);
+      }
+      CV[tid - 96] = cvv;
     }
     __syncthreads();
     if (tid < 32) {            // tile id per point, and a bit mask of the points that START a new tile run
@@ -321,7 +360,7 @@ template <typename T, int W, int D, int HAS_C>
 __global__ void __launch_bounds__(256)
 spread_direct_kernel(const T* __restrict__ rec,
                      const T* __restrict__ cs, int64_t npos, int nf0, int nf1, int nf2, T* __restrict__ grid,
-                     const __grid_constant__ ESDev<T> es) {
+                     const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
   int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= npos) return;
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
@@ -330,6 +369,11 @@ spread_direct_kernel(const T* __restrict__ rec,
   T X0 = Xr[0];
   if (X0 < T(0)) return;
   T cv = HAS_C == 1 ? cs[n] : (HAS_C == 2 ? Xr[3] : T(1));
+  if (HAS_C == 3) {
+    uint32_t bits[4];
+    philox_bits(pr.seed, (uint64_t)n, (uint32_t)(pr.t0 >> 7), bits);
+    cv = philox_sign_from_bits<T>(bits, pr.t0);
+  }
   T k0[W], k1[W], k2[W];
   int c0 = (int)X0;
   es_eval<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
@@ -369,70 +413,107 @@ spread_direct_kernel(const T* __restrict__ rec,
   }
 }
 
+// Probes one launch may carry for this geometry: the 2-D register kernels hold NB footprints (W^2 NB doubles).
+int spread_probe_batch(int dim, int W, int dtype) {
+  if (dim != 2) return 1;
+  const int reg_max = dtype == 1 ? 9 : 10;
+  if (W > reg_max) return 1;
+  if (W <= 5) return 4;
+  if (W <= 7) return 2;
+  return 1;
+}
+
 template <typename T, int W>
-static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st, bool from_record) {
+static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st, int mode,
+                     const ProbeSpec& pr) {
   ESDev<T> es;
   es_to_dev<T>(k, es);
   const T* rec = (const T*)sp.rec;
   constexpr int kRegMaxW = sizeof(T) == 8 ? 9 : 10;
   const int nt = (int)sp.ntiles;
-  const int mode = from_record ? 2 : (cs ? 1 : 0);
-  char nm[48];
+  char nm[56];
   snprintf(nm, sizeof(nm), "spread%dd_w%d_%s%s", sp.dim, W, sizeof(T) == 8 ? "f64" : "f32",
-           mode == 0 ? "_ones" : (mode == 2 ? "_rec" : ""));
-  ScopedStage stg(nm, st, 1, sp.N);
+           mode == 0 ? "_ones" : (mode == 2 ? "_rec" : (mode == 3 ? (pr.nb == 4 ? "_probes4" : (pr.nb == 2 ? "_probes2" : "_probes1")) : "")));
+  ScopedStage stg(nm, st, 1, sp.N * (mode == 3 ? pr.nb : 1));
   const int nf0 = (int)sp.nf[0], nf1 = (int)sp.nf[1], nf2 = (int)sp.nf[2];
   if (sp.dim == 1) {
-    if (cs)
-      spread1d_kernel<T, W, true><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es);
+    if (mode == 3)
+      spread1d_kernel<T, W, 3><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es, pr);
+    else if (mode == 1)
+      spread1d_kernel<T, W, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es, pr);
     else
-      spread1d_kernel<T, W, false><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es);
+      spread1d_kernel<T, W, 0><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es, pr);
   } else if (sp.dim == 2) {
     if constexpr (W <= kRegMaxW) {
-      if (mode == 2)
-        spread2d_kernel<T, W, 2><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es);
+      if (mode == 3) {
+        if constexpr (W <= 5) {
+          if (pr.nb == 4) {
+            spread2d_kernel<T, W, 3, 4><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
+            EFGP_CUDA(cudaGetLastError());
+            return;
+          }
+        }
+        if constexpr (W <= 7) {
+          if (pr.nb == 2) {
+            spread2d_kernel<T, W, 3, 2><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
+            EFGP_CUDA(cudaGetLastError());
+            return;
+          }
+        }
+        EFGP_CHECK(pr.nb == 1, "probe batch not supported by this spreading width");
+        spread2d_kernel<T, W, 3, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
+      } else if (mode == 2)
+        spread2d_kernel<T, W, 2, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
       else if (mode == 1)
-        spread2d_kernel<T, W, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es);
+        spread2d_kernel<T, W, 1, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
       else
-        spread2d_kernel<T, W, 0><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es);
+        spread2d_kernel<T, W, 0, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
     } else {
+      EFGP_CHECK(mode != 3 || pr.nb == 1, "probe batch not supported by this spreading width");
       int nb = div_up(sp.npos, 256);
-      if (mode == 2)
-        spread_direct_kernel<T, W, 2, 2><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es);
+      if (mode == 3)
+        spread_direct_kernel<T, W, 2, 3><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr);
+      else if (mode == 2)
+        spread_direct_kernel<T, W, 2, 2><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr);
       else if (mode == 1)
-        spread_direct_kernel<T, W, 2, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es);
+        spread_direct_kernel<T, W, 2, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr);
       else
-        spread_direct_kernel<T, W, 2, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es);
+        spread_direct_kernel<T, W, 2, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr);
     }
   } else if (getenv("EFGP_3D_DIRECT")) {   // per-point REDs (kept for A/B measurements)
+    EFGP_CHECK(mode != 3 || pr.nb == 1, "one probe per launch in 3-D");
     int nb = div_up(sp.npos, 256);
-    if (cs)
-      spread_direct_kernel<T, W, 3, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es);
+    if (mode == 3)
+      spread_direct_kernel<T, W, 3, 3><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es, pr);
+    else if (cs)
+      spread_direct_kernel<T, W, 3, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es, pr);
     else
-      spread_direct_kernel<T, W, 3, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es);
+      spread_direct_kernel<T, W, 3, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es, pr);
   } else {
+    EFGP_CHECK(mode != 3 || pr.nb == 1, "one probe per launch in 3-D");
     const size_t smem = tile3_smem_bytes<T, W>();
     int nb = div_up(sp.N, kT3Chunk);
-    if (cs) {
-      EFGP_CUDA(cudaFuncSetAttribute(spread3d_tile_kernel<T, W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)smem));
-      spread3d_tile_kernel<T, W, true><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es);
+    if (mode == 3) {
+      EFGP_CUDA(cudaFuncSetAttribute(spread3d_tile_kernel<T, W, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      spread3d_tile_kernel<T, W, 3><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es, pr);
+    } else if (cs) {
+      EFGP_CUDA(cudaFuncSetAttribute(spread3d_tile_kernel<T, W, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      spread3d_tile_kernel<T, W, 1><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es, pr);
     } else {
-      EFGP_CUDA(cudaFuncSetAttribute(spread3d_tile_kernel<T, W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)smem));
-      spread3d_tile_kernel<T, W, false><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es);
+      EFGP_CUDA(cudaFuncSetAttribute(spread3d_tile_kernel<T, W, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      spread3d_tile_kernel<T, W, 0><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es, pr);
     }
   }
   EFGP_CUDA(cudaGetLastError());
 }
 
 template <typename T>
-static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st,
-                     bool from_record) {
+static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st, int mode,
+                     const ProbeSpec& pr) {
   switch (k.W) {
 #define EFGP_CASE(w) \
   case w:            \
-    launch_w<T, w>(sp, k, cs, grid, st, from_record); \
+    launch_w<T, w>(sp, k, cs, grid, st, mode, pr); \
     break;
     EFGP_CASE(2) EFGP_CASE(3) EFGP_CASE(4) EFGP_CASE(5) EFGP_CASE(6) EFGP_CASE(7) EFGP_CASE(8) EFGP_CASE(9)
     EFGP_CASE(10) EFGP_CASE(11) EFGP_CASE(12) EFGP_CASE(13) EFGP_CASE(14) EFGP_CASE(15) EFGP_CASE(16)
@@ -447,10 +528,23 @@ void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, vo
   if (sp.N == 0) return;
   EFGP_CHECK(!from_record || (sp.has_payload && sp.dim == 2), "sorted point set carries no strength payload");
   EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
+  const int mode = from_record ? 2 : (cs ? 1 : 0);
+  ProbeSpec pr{0, 0, 1};
   if (sp.dtype == 0)
-    launch_t<float>(sp, k, (const float*)cs, (float*)grid, st, from_record);
+    launch_t<float>(sp, k, (const float*)cs, (float*)grid, st, mode, pr);
   else
-    launch_t<double>(sp, k, (const double*)cs, (double*)grid, st, from_record);
+    launch_t<double>(sp, k, (const double*)cs, (double*)grid, st, mode, pr);
+}
+
+// grids b = 0 .. pr.nb-1 (contiguous, nf^d each) += sum over points of Rademacher(seed, pr.t0 + b, slot) psi(l - X)
+void launch_spread_probes(const SortedPoints& sp, const ESKernel& k, void* grid, const ProbeSpec& pr, cudaStream_t st) {
+  if (sp.N == 0) return;
+  EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
+  EFGP_CHECK(pr.nb >= 1 && (pr.t0 >> 7) == ((pr.t0 + pr.nb - 1) >> 7), "a probe launch must stay inside one 128-probe block");
+  if (sp.dtype == 0)
+    launch_t<float>(sp, k, (const float*)nullptr, (float*)grid, st, 3, pr);
+  else
+    launch_t<double>(sp, k, (const double*)nullptr, (double*)grid, st, 3, pr);
 }
 
 }  // namespace efgp

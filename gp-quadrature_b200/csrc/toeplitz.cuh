@@ -43,4 +43,12 @@ const void* toeplitz_real_spectrum(Toeplitz& t, cudaStream_t st);
 void lanczos_tridiag(Toeplitz& t, const void* ws, double sigmasq, int mode, void* q0, int batch, int steps,
                      double breakdown, double* alphas, double* betas, cudaStream_t st);
 
+// variance.cu: device stages of diag_sums_nd (efgpnd.py:1657-1664) and of the 'regular' variance (efgpnd.py:1805-1820)
+void xcorr_mean(const void* us, const void* etas, const void* ws, int J, int dim, int mtot, int dtype, void* out,
+                cudaStream_t st);
+void variance_rows(const void* x, int64_t b, int dim, int mtot, double h, const void* ws, int dtype, void* rhs,
+                   cudaStream_t st);
+void variance_reduce(const void* x, int64_t b, int dim, int mtot, double h, const void* ws, int dtype, const void* gamma,
+                     void* var, cudaStream_t st);
+
 }  // namespace efgp

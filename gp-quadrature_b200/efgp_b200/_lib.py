@@ -64,6 +64,17 @@ _SIGNATURES = {
     "efgp_comm_world": (ctypes.c_int, []),
     "efgp_allreduce": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
     "efgp_bbox_async": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp]),
+    "efgp_xcorr_mean": (ctypes.c_int, [vp, vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp]),
+    "efgp_variance_rows": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_double, vp, ctypes.c_int,
+                                          vp, vp]),
+    "efgp_variance_reduce": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_double, vp,
+                                            ctypes.c_int, vp, vp, vp]),
+    "efgp_nufft_type1_probes": (ctypes.c_int, [vp, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, c_i64p, ctypes.c_double, vp, vp,
+                                               ctypes.POINTER(ctypes.c_uint64), vp]),
+    "efgp_nufft_type2_probe_dots": (ctypes.c_int, [vp, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, vp, c_i64p,
+                                                   ctypes.c_double, vp, vp, ctypes.POINTER(ctypes.c_uint64), vp]),
+    "efgp_nufft_probes_export": (ctypes.c_int, [vp, ctypes.c_uint64, ctypes.c_int, ctypes.c_int, c_i64p, ctypes.c_double, vp,
+                                                ctypes.POINTER(ctypes.c_uint64), vp]),
     "efgp_fit": (ctypes.c_int, [vp, vp, ctypes.POINTER(FitArgs), vp, vp, vp, vp, ctypes.POINTER(vp), vp, c_intp, vp]),
 }
 

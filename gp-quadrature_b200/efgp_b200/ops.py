@@ -180,6 +180,57 @@ class NufftPlan:
         return out if batched else out.reshape(self.N)
 
 
+def _probe_methods():
+    """Hutchinson probes streamed through the transforms (efgp_nufft_type1_probes / _type2_probe_dots / _probes_export)."""
+
+    def type1_probes(self, seed, t0, nb, out_shape, eps, scale=None, sort_id=0):
+        """(scale * F^* Z_t for t0 <= t < t0 + nb, sort_id): (nb, *out_shape) complex; Z regenerated in the kernel."""
+        out_shape = tuple(int(s) for s in out_shape)
+        M = 1
+        for s_ in out_shape:
+            M *= s_
+        sc = self._scale(scale, M)
+        out = torch.empty((int(nb),) + out_shape, dtype=self.cdtype, device=self.device)
+        sid = ctypes.c_uint64(int(sort_id))
+        with _on(self.device):
+            check(_lib.lib().efgp_nufft_type1_probes(self._h, ctypes.c_uint64(int(seed)), int(t0), int(nb),
+                                                     i64_array(out_shape), float(eps), _ptr(sc), _ptr(out),
+                                                     ctypes.byref(sid), _stream(self.device)))
+        return out, int(sid.value)
+
+    def type2_probe_dots(self, seed, t0, nb, modes, shape, eps, scale=None, sort_id=0):
+        """sums[b] = sum_n Z_{t0+b}[n] Re(F (scale * modes[b]))[n]: (nb,) float64; nothing of size N is written."""
+        shape = tuple(int(s) for s in shape)
+        M = 1
+        for s_ in shape:
+            M *= s_
+        f = modes.to(self.cdtype).reshape(int(nb), M).contiguous()
+        sc = self._scale(scale, M)
+        sums = torch.empty(int(nb), dtype=torch.float64, device=self.device)
+        sid = ctypes.c_uint64(int(sort_id))
+        with _on(self.device):
+            check(_lib.lib().efgp_nufft_type2_probe_dots(self._h, ctypes.c_uint64(int(seed)), int(t0), int(nb), _ptr(f),
+                                                         i64_array(shape), float(eps), _ptr(sc), _ptr(sums),
+                                                         ctypes.byref(sid), _stream(self.device)))
+        return sums, int(sid.value)
+
+    def probes_export(self, seed, t0, nb, shape, eps, sort_id=0):
+        """The probes themselves, (nb, N) real in original point order (tests, A/B runs)."""
+        shape = tuple(int(s) for s in shape)
+        z = torch.empty((int(nb), self.N), dtype=self.rdtype, device=self.device)
+        sid = ctypes.c_uint64(int(sort_id))
+        with _on(self.device):
+            check(_lib.lib().efgp_nufft_probes_export(self._h, ctypes.c_uint64(int(seed)), int(t0), int(nb),
+                                                      i64_array(shape), float(eps), _ptr(z), ctypes.byref(sid),
+                                                      _stream(self.device)))
+        return z, int(sid.value)
+
+    return type1_probes, type2_probe_dots, probes_export
+
+
+NufftPlan.type1_probes, NufftPlan.type2_probe_dots, NufftPlan.probes_export = _probe_methods()
+
+
 class LazyIters:
     """Iteration count of a solve that was only enqueued (efgp_cg_solve_async): int(obj) waits for the stream to
     deliver the two convergence counters into pinned host memory and applies the reference's counting rule."""
@@ -448,3 +499,46 @@ def comm_allreduce(t, op="sum"):
         check(_lib.lib().efgp_allreduce(_ptr(t), int(t.numel()), _dtype_code(t.dtype), 0 if op == "sum" else 1,
                                         _stream(t.device)))
     return t
+
+
+# ----------------------------------------------------------------------------- posterior variance stages
+def xcorr_mean(us, etas, ws_real, mtot, d):
+    """Lag sums of diag_sums_nd (efgp_xcorr_mean): us (J, M) complex, etas (J, M) real, ws_real (M,) or None ->
+    ((2 mtot - 1),) * d complex, FFT ordering."""
+    _require_cuda(us, "us")
+    J, M = us.shape
+    rdtype = real_of(us.dtype)
+    us = us.contiguous()
+    etas = etas.to(device=us.device, dtype=rdtype).contiguous()
+    w = None if ws_real is None else ws_real.to(device=us.device, dtype=rdtype).reshape(-1).contiguous()
+    out = torch.empty((2 * mtot - 1,) * d, dtype=us.dtype, device=us.device)
+    with _on(us.device):
+        check(_lib.lib().efgp_xcorr_mean(_ptr(us), _ptr(etas), _ptr(w), int(J), int(d), int(mtot), _dtype_code(rdtype),
+                                         _ptr(out), _stream(us.device)))
+    return out
+
+
+def variance_rows(xb, h, mtot, ws_real):
+    """rhs[i] = ws * conj(exp(2 pi i x_i . xi)) for the 'regular' variance (efgp_variance_rows): (b, mtot^d) complex."""
+    _require_cuda(xb, "x")
+    xb = xb.contiguous()
+    b, d = xb.shape
+    w = ws_real.to(device=xb.device, dtype=xb.dtype).reshape(-1).contiguous()
+    rhs = torch.empty((b, mtot ** d), dtype=cmplx_of(xb.dtype), device=xb.device)
+    with _on(xb.device):
+        check(_lib.lib().efgp_variance_rows(_ptr(xb), int(b), int(d), int(mtot), float(h), _ptr(w),
+                                            _dtype_code(xb.dtype), _ptr(rhs), _stream(xb.device)))
+    return rhs
+
+
+def variance_reduce(xb, h, mtot, ws_real, gamma):
+    """var[i] = max(0, Re sum_k fx_i[k] ws[k] gamma[i, k]) (efgp_variance_reduce): (b,) real."""
+    xb = xb.contiguous()
+    b, d = xb.shape
+    w = ws_real.to(device=xb.device, dtype=xb.dtype).reshape(-1).contiguous()
+    g = gamma.to(cmplx_of(xb.dtype)).contiguous()
+    var = torch.empty(b, dtype=xb.dtype, device=xb.device)
+    with _on(xb.device):
+        check(_lib.lib().efgp_variance_reduce(_ptr(xb), int(b), int(d), int(mtot), float(h), _ptr(w),
+                                              _dtype_code(xb.dtype), _ptr(g), _ptr(var), _stream(xb.device)))
+    return var

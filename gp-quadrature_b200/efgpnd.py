@@ -475,6 +475,14 @@ def diag_sums_nd(A_apply, J, xis_flat, max_cg_iter, cg_tol, ws):
     rhs = ws[None, :] * etas
     us = ConjugateGradients(A_apply, rhs, x0=_zero_guess(rhs), tol=cg_tol, max_iter=max_cg_iter,
                             early_stopping=True).solve()
+    wr = getattr(ws, "_efgp_real_part", None)
+    if wr is None and not ws.is_complex():
+        wr = ws
+    if wr is not None and us.is_cuda:
+        # gamma = ws * u, the J padded FFT pairs, their products summed in the spectral domain, ONE inverse FFT and
+        # the probe mean: one library call (csrc/variance.cu)
+        return _ops.xcorr_mean(us, etas, wr, M_loc, d_loc)
+    # foreign complex weights: the reference's formulation with torch FFTs
     gammas = ws[None, :] * us
     s_size = (2 * M_loc - 1,) * d_loc
     dims = tuple(range(1, d_loc + 1))
@@ -506,12 +514,25 @@ def compute_prediction_variance(x_new, xis, ws, A_var, cg_tol, max_cg_iter, vari
     method = variance_method.lower()
     if method == "regular":
         out = []
+        ours = getattr(ws, "_efgp_real", False) and hasattr(xis, "h_float") and x_new.is_cuda
         for xb in torch.split(x_new, 8192, dim=0):
+            if ours:
+                # our centred odd grid with even real weights: the (b, M) right-hand sides and the final reduction are
+                # built from separable phase tables on the device (csrc/variance.cu); fx itself is never stored and
+                # the rows are Hermitian-symmetric (conj(fx)[-k] = fx[k]): real-FFT matvec
+                wr = getattr(ws, "_efgp_real_part", None)
+                wr = wr if wr is not None else ws.real
+                mt = int(round(xis.shape[0] ** (1.0 / xis.shape[1])))
+                xbd = xb.to(rdtype)
+                rhs = _hermitian(_ops.variance_rows(xbd, xis.h_float, mt, wr))
+                gamma = ConjugateGradients(A_var, rhs, x0=_zero_guess(rhs, cdtype), tol=cg_tol,
+                                           max_iter=max_cg_iter, early_stopping=True).solve()
+                out.append(_ops.variance_reduce(xbd, xis.h_float, mt, wr, gamma))
+                del rhs, gamma
+                continue
+            # foreign grids / weights: the reference's dense formulation, general matvec (the symmetry is not checked)
             fx = torch.exp(2 * math.pi * 1j * (xb @ xis.T)).to(cdtype)
             rhs = ws * fx.conj()
-            if getattr(ws, "_efgp_real", False) and hasattr(xis, "h_float"):
-                _hermitian(rhs)         # conj(fx)[-k] = fx[k] on OUR centred odd grid with even real weights
-                                        # (foreign xis / ws take the general matvec: the symmetry is not checked)
             gamma = ConjugateGradients(A_var, rhs, x0=_zero_guess(rhs, cdtype), tol=cg_tol,
                                        max_iter=max_cg_iter, early_stopping=True).solve()
             out.append(torch.real((fx * (ws * gamma)).sum(dim=-1)).clamp_min(0.0))
@@ -568,7 +589,7 @@ def efgpnd_gradient_batched(
         mean_cg_init: Optional[torch.Tensor] = None,
         use_mean_cg_preconditioner: bool = True,
         use_trace_cg_preconditioner: bool = True,
-        log_marginal_probes=100, log_marginal_steps=25, probe_group=None):
+        log_marginal_probes=100, log_marginal_steps=25, probe_group=None, device_probes=None):
     """Hutchinson + CG gradient of the negative log marginal likelihood w.r.t. (kernel hypers, sigma^2)
     in positive space; same stages, probe order (Z then V) and statistics as the reference
     (efgpnd.py:17-317).  x0 / x1 are ignored and recomputed, as there (efgpnd.py:72-73).
@@ -576,7 +597,13 @@ def efgpnd_gradient_batched(
     Differences in HOW (not what): real strengths are spread as real data; every type-2 whose result
     the reference only uses through a real part or a real inner product is computed as a real-output
     transform; and term1's two forward transforms F(D'F*Z) - F(ws beta) are merged into one transform
-    of the difference (linearity), so no (T, N) complex array is ever stored."""
+    of the difference (linearity), so no (T, N) complex array is ever stored.
+
+    device_probes (default: on unless PROBE_DEVICE asks for the reference's CPU draws): the point-space probes Z are
+    not drawn with torch at all -- the spread kernel regenerates them from a Philox counter (seed, probe, point slot),
+    the interpolation kernel multiplies its result by the same signs and reduces it, and NO (T, N) array exists
+    (efgp_nufft_type1_probes / efgp_nufft_type2_probe_dots).  "export" materialises the same Philox probes and runs
+    them through the stored-probe path (A/B check of the streamed one)."""
     num_hypers = kernel.num_hypers
     if cg_tol is None:
         cg_tol = eps
@@ -676,16 +703,32 @@ def efgpnd_gradient_batched(
             nk = len(trace_idx)
             if Tl == 0:
                 return torch.zeros(nk, device=device, dtype=rdtype), torch.zeros((), device=device, dtype=rdtype), 0, 0
+            stream = (device_probes if device_probes is not None else PROBE_DEVICE is None) and nk > 0
+            plan = nufft_op._plan.ensure(nufft_op._hf, nufft_op._xc)
+            sort_id, Zl = 0, None
+            if stream:
+                # ONE integer from the global CPU generator seeds all point-space probes (torch.manual_seed controls
+                # it; under probe sharding every rank draws the same one): probe t is Philox(seed_z, t, slot)
+                seed_z = int(torch.randint(0, 2 ** 62, (1,)).item()) if probe_seed is None else int(probe_seed) * 7919 + 13
             if probe_seed is None:
-                Zl = _rademacher_like_reference((Tl, N), rdtype, device) if nk > 0 else None
+                if not stream:
+                    Zl = _rademacher_like_reference((Tl, N), rdtype, device) if nk > 0 else None
                 Vl = _rademacher_like_reference((Tl, M), rdtype, device).to(cdtype)
             else:
-                Zl = torch.stack([_rademacher_seeded(N, rdtype, device, probe_seed + 2 * t)
-                                  for t in range(t_lo, t_hi)]) if nk > 0 else None
+                if not stream:
+                    Zl = torch.stack([_rademacher_seeded(N, rdtype, device, probe_seed + 2 * t)
+                                      for t in range(t_lo, t_hi)]) if nk > 0 else None
                 Vl = torch.stack([_rademacher_seeded(M, rdtype, device, probe_seed + 2 * t + 1)
                                   for t in range(t_lo, t_hi)]).to(cdtype)
-            if nk > 0:
+            if stream and device_probes == "export":
+                Zl, sort_id = plan.probes_export(seed_z, t_lo, Tl, OUT, nufft_eps)
+                stream = False
+            if stream:
+                fadjZ, sort_id = plan.type1_probes(seed_z, t_lo, Tl, OUT, nufft_eps)
+                fadjZ = fadjZ.reshape(Tl, -1)
+            elif nk > 0:
                 fadjZ = nufft_op.type1(Zl, OUT).reshape(Tl, -1)
+            if nk > 0:
                 Di_FZ_all = torch.stack([Dprime[:, i] * fadjZ for i in trace_idx], dim=0).reshape(-1, M)
                 B_all_kernel = (ws * toeplitz(Di_FZ_all)).reshape(nk, Tl, -1)
             else:
@@ -716,7 +759,12 @@ def efgpnd_gradient_batched(
                     # Alpha = (F(D'F*Z) - F(ws beta_k)) / sigma^2 = F(D'F*Z - ws beta_k) / sigma^2, real part only
                     resid_modes = Di_FZ_all - ws * Beta_kernel
                     chunk = max(1, min(Tl, int((2 << 30) // max(1, N * 8))))
-                    for slot in range(nk):
+                    for slot in range(nk if stream else 0):
+                        # sum_n Z_t[n] Re F(resid_t)[n] inside the interpolation kernel: nothing of size N is written
+                        dots, _ = plan.type2_probe_dots(seed_z, t_lo, Tl, resid_modes[slot * Tl:(slot + 1) * Tl], OUT,
+                                                        nufft_eps, sort_id=sort_id)
+                        sums[slot] = dots.to(rdtype)
+                    for slot in range(0 if stream else nk):
                         for t0 in range(0, Tl, chunk):
                             rm = resid_modes[slot * Tl + t0: slot * Tl + min(Tl, t0 + chunk)]
                             a_chunk = nufft_op.type2(rm, OUT, real_out=True).reshape(-1, N)
@@ -911,6 +959,7 @@ class EFGPND(nn.Module):
             cg_tol = 0.1 * self.eps
         stats = {}
         kwargs.setdefault("probe_group", _probe_shard_group(self.opts))
+        kwargs.setdefault("device_probes", self.opts.get("device_probes"))
         result = efgpnd_gradient_batched(
             self.x, self.y, sigmasq=self._gp_params.sig2, kernel=self.kernel, eps=self.eps,
             trace_samples=trace_samples, x0=None, x1=None, do_profiling=do_profiling, nufft_eps=nufft_eps,

@@ -175,6 +175,39 @@ typedef struct efgp_fit_args {
 int efgp_fit(efgp_nufft* nu, const void* y, const efgp_fit_args* args, void* ws, void* vr, void* minv, void* beta,
              efgp_toeplitz** toep_out, int* counters_pinned, int* iters_completed, void* stream);
 
+/* ---- posterior variance: the device stages around the batched solves.
+ * efgp_xcorr_mean: diag_sums_nd's lag sums (efgpnd.py:1657-1664),
+ *   out[r] = mean_j ifftn( fftn(ws * us_j, s) * conj(fftn(etas_j, s)), s ),  s = (2 mtot - 1)^dim, FFT ordering,
+ * us (nprobes, mtot^dim) complex (the CG solutions), etas (nprobes, mtot^dim) REAL probes, ws (mtot^dim,) real or NULL;
+ * out ((2 mtot - 1)^dim) complex.
+ * efgp_variance_rows / efgp_variance_reduce: compute_prediction_variance 'regular' (efgpnd.py:1805-1820) for test points
+ * x (npts, dim) on the grid xi_k = h (k - (mtot-1)/2):  rhs[i] = ws * conj(fx_i)  ((npts, mtot^dim) complex) and
+ * var[i] = max(0, Re sum_k fx_i[k] ws[k] gamma[i, k])  ((npts,) real); the dense fx of the reference is never stored. */
+int efgp_xcorr_mean(const void* us, const void* etas, const void* ws, int nprobes, int dim, int mtot, int dtype, void* out,
+                    void* stream);
+int efgp_variance_rows(const void* x, int64_t npts, int dim, int mtot, double h, const void* ws, int dtype, void* rhs,
+                       void* stream);
+int efgp_variance_reduce(const void* x, int64_t npts, int dim, int mtot, double h, const void* ws, int dtype,
+                         const void* gamma, void* var, void* stream);
+
+/* ---- Hutchinson probes streamed through the transforms: the Monte-Carlo trace of efgpnd_gradient_batched
+ * (efgpnd.py:176-241) without its (T, N) arrays Z, F(D'F^*Z) and F(ws beta).  Probe t is the Rademacher vector
+ * Z_t[n] = sign bit of Philox-4x32-10(key = seed, counter = (slot of point n in the sorted set, t / 128)), regenerated
+ * inside the spread kernel and inside the interpolation epilogue, never stored.
+ *   efgp_nufft_type1_probes:     out[b] = scale * F^* Z_{t0+b}, b < nprobes: (nprobes, *out_shape) complex (efgpnd.py:183)
+ *   efgp_nufft_type2_probe_dots: sums[b] = sum_n Z_{t0+b}[n] * Re(F (scale * modes[b]))[n]: modes (nprobes, *shape)
+ *                                complex -> sums (nprobes,) FLOAT64 on the device (efgpnd.py:235-241, any dtype)
+ *   efgp_nufft_probes_export:    z (nprobes, npts) real, original point order: the probes themselves (tests)
+ * The signs are tied to the point ORDER of one sorted set: *sort_id (in/out, start with 0) carries its identity from
+ * the first call to the later ones, which fail loudly if the handle re-sorted in between.  2-D kernels take up to 4
+ * probes per pass over the points (kernel weights evaluated once per point). */
+int efgp_nufft_type1_probes(efgp_nufft* nu, uint64_t seed, int t0, int nprobes, const int64_t* out_shape, double eps,
+                            const void* scale, void* out, uint64_t* sort_id, void* stream);
+int efgp_nufft_type2_probe_dots(efgp_nufft* nu, uint64_t seed, int t0, int nprobes, const void* modes, const int64_t* shape,
+                                double eps, const void* scale, double* sums, uint64_t* sort_id, void* stream);
+int efgp_nufft_probes_export(efgp_nufft* nu, uint64_t seed, int t0, int nprobes, const int64_t* shape, double eps, void* z,
+                             uint64_t* sort_id, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -254,6 +254,7 @@ def fit(x, y, kern, sigmasq, eps, nufft_eps, cg_tol=1e-4, backend=exact_nudft, p
     f = OracleFit()
     f.beta, f.ws, f.xis, f.h, f.hf, f.mtot, f.toep, f.iters, f.v = beta, ws, xis, h, hf, mtot, toep, iters, v
     f.d, f.sigmasq, f.rd, f.cd = d, sigmasq, rd, cd
+    f.rhs, f.A_mean = rhs, A_mean      # the assembled system, for residual checks of a foreign beta
     return f
 
 

@@ -54,7 +54,11 @@ def test_fit_and_mean_against_the_oracle_at_scale(d, N, ell, eps):
     assert abs(m.last_fit_stats["h"] - f.h) <= 1e-13 * f.h
     # generator F^*1 (always at eps 6e-8, efgpnd.py:1418) and the right-hand side, grid for grid
     assert rel(m._toeplitz.plan.v, f.v) < 10 * 6e-8
-    assert rel(m._beta, f.beta) < 1e-6
+    # beta is compared through the ORACLE's system (its operator and right-hand side): beta itself is only determined
+    # up to (CG tolerance) x (condition number) in the directions the spectral weights damp
+    bc = m._beta.detach().cpu().reshape(-1)
+    assert rel(f.A_mean(bc), f.rhs) < 1e-6
+    assert rel(f.ws.reshape(-1) * bc, f.ws.reshape(-1) * f.beta.reshape(-1)) < 1e-5
     g = torch.Generator().manual_seed(5)
     idx = torch.randint(0, N, (10000,), generator=g)
     phi = (2 * math.pi * f.h * xc[idx]).T.contiguous()

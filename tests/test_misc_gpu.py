@@ -68,3 +68,64 @@ def test_direct_dft_cg_matches_fft_cg_on_rectangular_block(dt, tol):
     # and the solution really solves the system
     res = T.apply(x1, ops.MODE_A_MEAN, ws, 0.5) - b
     assert float(torch.linalg.norm(res) / torch.linalg.norm(b)) < 50 * cg_tol
+
+
+@pytest.mark.parametrize("kname,d,dt", [("se", 2, torch.float64), ("matern52", 3, torch.float64), ("matern32", 1, torch.float64),
+                                        ("se", 2, torch.float32)])
+def test_fused_fit_equals_the_step_by_step_fit(kname, d, dt):
+    """efgp_fit (ws, pair, Toeplitz, Jacobi, PCG in one library call) against the same fit assembled from the
+    individual entry points with torch glue (opts['fused_fit'] = False): same grid, weights, generator and beta."""
+    import efgpnd
+    from kernels import SquaredExponential, Matern
+    g = torch.Generator(device="cuda").manual_seed(4)
+    N = 20000
+    x = (torch.rand(N, d, dtype=torch.float64, device="cuda", generator=g) * 2 - 1).to(dt)
+    y = (torch.sin(3 * x[:, 0].double()) + 0.1 * torch.randn(N, dtype=torch.float64, device="cuda", generator=g)).to(dt)
+    f64 = dt == torch.float64
+    out = []
+    for fused in (True, False):
+        k = SquaredExponential(dimension=d, init_lengthscale=0.3, init_variance=1.1) if kname == "se" else \
+            Matern(dimension=d, init_lengthscale=0.6, init_variance=0.9, nu={"matern32": 1.5, "matern52": 2.5}[kname])
+        m = efgpnd.EFGPND(x, y, k, sigmasq=0.07, eps=1e-3, nufft_eps=1e-9 if f64 else 1e-5,
+                          opts={"cg_tolerance": 1e-10 if f64 else 1e-5, "fused_fit": fused}, estimate_params=False)
+        mean, _ = m.predict(x[:500], return_variance=False)
+        out.append((m, mean))
+    (a, ma), (b, mb) = out
+    assert a.last_fit_stats["mtot"] == b.last_fit_stats["mtot"] and a.last_fit_stats["h"] == b.last_fit_stats["h"]
+    rel = lambda u, v: float((u - v).abs().max() / v.abs().max())
+    assert rel(a._ws_real, b._ws_real) < (1e-13 if f64 else 1e-6)
+    assert rel(a._toeplitz.plan.v, b._toeplitz.plan.v) < (1e-9 if f64 else 1e-4)
+    # two CG runs stopped at the same relative residual: beta itself agrees only up to tolerance x condition number
+    # (Matern-3/2 in 1-D: 1.5e-3), so beta is compared THROUGH the operator, where both satisfy A beta = rhs to 1e-10
+    A = efgpnd.create_A_mean(b._ws, b._toeplitz, 0.07, b._ws.dtype)
+    assert rel(A(a._beta), A(b._beta)) < (1e-8 if f64 else 1e-3)
+    assert rel(a._beta, b._beta) < (1e-2 if f64 else 5e-2)
+    assert rel(ma, mb) < (1e-3 if f64 else 1e-2)
+    assert abs(int(a.last_fit_stats["mean_cg_iters"]) - int(b.last_fit_stats["mean_cg_iters"])) <= 1
+    assert tuple(a._xis.shape) == tuple(b._xis.shape) and rel(a._xis, b._xis) < 1e-15 + (0 if f64 else 1e-6)
+    assert a._ws.is_complex() and rel(a._ws.real, b._ws.real) < (1e-13 if f64 else 1e-6)
+
+
+def test_library_bounding_box_and_rescale():
+    """efgp_bbox_async against torch.aminmax; efgp_nufft_rescale keeps the handle and gives the transforms of a fresh
+    plan at the new spacing."""
+    from efgp_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(8)
+    for d in (1, 2, 3):
+        x = torch.randn(100003, d, dtype=torch.float64, device="cuda", generator=g)
+        ext, ev = ops.bbox_async(x)
+        ev.synchronize()
+        lo, hi = torch.aminmax(x, dim=0)
+        assert torch.equal(ext[:d], hi.cpu()) and torch.equal(ext[d:], -lo.cpu())
+    x = torch.rand(50000, 2, dtype=torch.float64, device="cuda", generator=g) * 2 - 1
+    c = torch.randn(50000, dtype=torch.float64, device="cuda", generator=g)
+    plan = ops.NufftPlan(x, 0.31)
+    a1 = plan.type1(c, (21, 21), 1e-9)
+    plan.ensure(0.44)
+    a2 = plan.type1(c, (21, 21), 1e-9)
+    b2 = ops.NufftPlan(x, 0.44).type1(c, (21, 21), 1e-9)
+    assert float((a2 - b2).abs().max() / b2.abs().max()) < 1e-12
+    assert float((a1 - a2).abs().max() / a2.abs().max()) > 1e-3
+    plan.ensure(0.31)
+    a3 = plan.type1(c, (21, 21), 1e-9)
+    assert float((a3 - a1).abs().max() / a1.abs().max()) < 1e-12
