@@ -736,7 +736,16 @@ def main():
     tr = torch.tensor([e0.elapsed_time(e1) / args.steps], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tr, op=dist.ReduceOp.MAX)
+    _lib.timing_enable(True)
+    barrier()
+    for k in range(args.steps):
+        refit(k)
+    barrier()
+    refit_stages = {k: round(v["ms"] / args.steps, 4) for k, v in _lib.timing_report().items()}
+    _lib.timing_enable(False)
     refit_info = {"ms_per_step": float(tr.item()), "value": n_total / float(tr.item()) / 1e3, "unit": UNIT,
+                  "stages_ms": refit_stages, "mean_cg_iters": int(model_r.last_fit_stats["mean_cg_iters"]),
+                  "mtot": int(model_r.last_fit_stats["mtot"]),
                   "what": "predict() after a lengthscale change on the same EFGPND object (same points): no bounding-box "
                           "read-back; the spacing h changes with the lengthscale, so the cell sort is redone"}
     del model_r

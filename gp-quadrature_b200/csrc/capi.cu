@@ -55,6 +55,10 @@ int efgp_timing_report(char* buf, int64_t cap) {
   })
 }
 
+int efgp_set_deterministic(int on) {
+  EFGP_TRY({ efgp::set_deterministic(on); })
+}
+
 int efgp_pool_trim(void) {
   EFGP_TRY({ efgp::pool_trim(); })
 }
@@ -153,6 +157,17 @@ int efgp_nufft_rescale(efgp_nufft* nu, double h, const double* xcen) {
       for (int a = 0; a < efgp::kMaxDim; ++a) nu->nu.xcen[a] = (xcen && a < nu->nu.dim) ? xcen[a] : 0.0;
       efgp::set_current_stream(nu->last_stream);
       nu->nu.sorted.clear();      // the cell order depends on h: rebuilt by the next transform
+    }
+  })
+}
+
+int efgp_nufft_carry_index(efgp_nufft* nu, int on) {
+  EFGP_TRY({
+    EFGP_CHECK(nu != nullptr, "null handle");
+    if (nu->nu.carry_index != (on != 0)) {
+      nu->nu.carry_index = on != 0;
+      efgp::set_current_stream(nu->last_stream);
+      nu->nu.sorted.clear();
     }
   })
 }

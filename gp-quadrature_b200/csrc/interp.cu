@@ -325,6 +325,7 @@ interp2d_dot_kernel(const T* __restrict__ rec, int P, int nf0, int nf1, const T*
                     double* __restrict__ partial, const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
   constexpr int S = kRingStages;
   __shared__ __align__(16) T ring[S][kTileThreads][2];
+  __shared__ T oring[S][kTileThreads];       // record word 2: level-1 position | original index
   __shared__ double sh[kTileThreads / 32];
   const int t = threadIdx.x;
   const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + t;
@@ -332,6 +333,7 @@ interp2d_dot_kernel(const T* __restrict__ rec, int P, int nf0, int nf1, const T*
     if (j < P) {
       const T* src = rec + (base + (int64_t)j * kTileThreads) * 4;
       cp_async_word<2 * sizeof(T)>(&ring[j % S][t][0], src);
+      cp_async_word<sizeof(T)>(&oring[j % S][t], src + 2);
     }
     cp_async_commit();
   };
@@ -371,7 +373,8 @@ interp2d_dot_kernel(const T* __restrict__ rec, int P, int nf0, int nf1, const T*
     es_eval_i<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
     es_eval_i<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
     uint32_t bits[4];
-    philox_bits(pr.seed, (uint64_t)(base + (int64_t)j * kTileThreads), (uint32_t)(pr.t0 >> 7), bits);
+    philox_bits(pr.seed, probe_counter<T>(oring[s][t], base + (int64_t)j * kTileThreads, pr.use_orig),
+                (uint32_t)(pr.t0 >> 7), bits);
 #pragma unroll
     for (int b = 0; b < NB; ++b) {
       T acc = 0;
@@ -407,6 +410,7 @@ interp_direct_dot_kernel(const T* __restrict__ rec, int64_t npos, int nf0, int n
     T Xr[4] = {T(0), T(0), T(0), T(0)};
     if constexpr (D == 1) {
       Xr[0] = rec[n * 2];
+      Xr[1] = rec[n * 2 + 1];
     } else {
       load_record4i<T>(rec + n * RWD, Xr);
     }
@@ -456,7 +460,7 @@ interp_direct_dot_kernel(const T* __restrict__ rec, int64_t npos, int nf0, int n
         }
       }
       uint32_t bits[4];
-      philox_bits(pr.seed, (uint64_t)n, (uint32_t)(pr.t0 >> 7), bits);
+      philox_bits(pr.seed, probe_counter<T>(Xr[D], n, pr.use_orig), (uint32_t)(pr.t0 >> 7), bits);
       val = (double)(philox_sign_from_bits<T>(bits, pr.t0) * acc);
     }
   }
@@ -484,6 +488,16 @@ probe_fill_kernel(const T* __restrict__ rec, int RW, int64_t npos, T* __restrict
   uint32_t bits[4];
   philox_bits(pr.seed, (uint64_t)n, (uint32_t)(pr.t0 >> 7), bits);
   z[n] = rec[n * RW] < T(0) ? T(0) : philox_sign_from_bits<T>(bits, pr.t0);
+}
+
+// counter = original index: Z in original order needs no sorted set at all
+template <typename T>
+__global__ void __launch_bounds__(256) probe_fill_orig_kernel(int64_t N, T* __restrict__ z, int64_t ostride, ProbeSpec pr) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  uint32_t bits[4];
+  philox_bits(pr.seed, (uint64_t)i, (uint32_t)(pr.t0 >> 7), bits);
+  z[i * ostride] = philox_sign_from_bits<T>(bits, pr.t0);
 }
 
 template <typename T, int W>
@@ -642,6 +656,14 @@ void launch_interp_probe_dots(const SortedPoints& sp, const ESKernel& k, const v
 // z (N,) in ORIGINAL point order = the probe pr.t0 the kernels regenerate for this sorted set
 void launch_probe_export(const SortedPoints& sp, void* z_out, int64_t ostride, const ProbeSpec& pr, cudaStream_t st) {
   if (sp.N == 0) return;
+  if (pr.use_orig) {
+    if (sp.dtype == 0)
+      probe_fill_orig_kernel<float><<<div_up(sp.N, 256), 256, 0, st>>>(sp.N, (float*)z_out, ostride, pr);
+    else
+      probe_fill_orig_kernel<double><<<div_up(sp.N, 256), 256, 0, st>>>(sp.N, (double*)z_out, ostride, pr);
+    EFGP_CUDA(cudaGetLastError());
+    return;
+  }
   const size_t esz = sp.dtype == 0 ? 4 : 8;
   void* tmp = pool_alloc(esz * (size_t)sp.npos);
   if (sp.dtype == 0)

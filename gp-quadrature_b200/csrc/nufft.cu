@@ -63,6 +63,63 @@ static std::map<std::string, std::unique_ptr<DevBuf>>& global_dec_tables() {
   return *g;
 }
 
+// ------------------------------------------------------------------ deterministic (fixed-point) spreading
+static int g_deterministic = -1;
+void set_deterministic(int on) { g_deterministic = on ? 1 : 0; }
+bool deterministic() {
+  if (g_deterministic < 0) {
+    const char* e = std::getenv("EFGP_DETERMINISTIC");
+    g_deterministic = (e && std::atoi(e) != 0) ? 1 : 0;
+  }
+  return g_deterministic == 1;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+absmax_kernel(const T* __restrict__ c, int64_t n, int64_t stride, unsigned long long* __restrict__ out) {
+  double m = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const double v = fabs((double)c[i * stride]);
+    m = v > m ? v : m;
+  }
+  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(out, (unsigned long long)__double_as_longlong(m));   // order-preserving for m >= 0
+}
+
+// 2^k with (sum of |strengths|, bounded by N * cmax) * 2^k < 2^62: the integer grid cannot overflow
+static double det_scale_for(double n_times_cmax) {
+  if (!(n_times_cmax > 0)) n_times_cmax = 1.0;
+  int e = 0;
+  std::frexp(n_times_cmax, &e);            // n_times_cmax < 2^e
+  return std::ldexp(1.0, 62 - e);
+}
+
+// largest |strength| of (n, stride) values on the device (synchronises: deterministic mode is a parity / debug mode)
+static double device_absmax(const void* c, int64_t n, int64_t stride, int dtype, cudaStream_t st) {
+  unsigned long long* d = (unsigned long long*)pool_alloc(sizeof(unsigned long long));
+  EFGP_CUDA(cudaMemsetAsync(d, 0, sizeof(unsigned long long), st));
+  const int blocks = (int)std::min<int64_t>(1024, (n + 255) / 256);
+  if (dtype == 0)
+    absmax_kernel<float><<<blocks, 256, 0, st>>>((const float*)c, n, stride, d);
+  else
+    absmax_kernel<double><<<blocks, 256, 0, st>>>((const double*)c, n, stride, d);
+  unsigned long long h = 0;
+  EFGP_CUDA(cudaMemcpyAsync(&h, d, sizeof(h), cudaMemcpyDeviceToHost, st));
+  EFGP_CUDA(cudaStreamSynchronize(st));
+  pool_free(d);
+  double v;
+  std::memcpy(&v, &h, sizeof(v));
+  return v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+det_convert_kernel(const unsigned long long* __restrict__ ig, int64_t n, double inv_scale, T* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[i] = (T)((double)(long long)ig[i] * inv_scale);      // (in place when T = double: same element size)
+}
+
 // ------------------------------------------------------------------ mode bookkeeping
 struct ModeGeom {
   int dim;
@@ -289,7 +346,7 @@ static SortedPoints* get_sorted(Nufft& nu, const int64_t* nf, int odd, cudaStrea
   std::unique_ptr<SortedPoints> sp(new SortedPoints());
   static uint64_t next_id = 0;
   sp->id = ++next_id;
-  build_sorted_points(*sp, nu.x, nu.pending_payload, nu.N, nu.dim, nu.dtype, nu.h, nu.xcen, nf, odd, st);
+  build_sorted_points(*sp, nu.x, nu.pending_payload, nu.N, nu.dim, nu.dtype, nu.h, nu.xcen, nf, odd, st, nu.carry_index);
   if (sp->has_payload) nu.fresh_payload_sp = sp.get();
   sp->last_use = ++nu.clock;
   nu.sorted.push_back(std::move(sp));
@@ -469,7 +526,18 @@ static void type1_t(Nufft& nu, const void* strengths, int is_complex, int batch,
   C* spec = (C*)nu.spec.get((size_t)chunk * ncomp * slab * sizeof(C));
   for (int b0 = 0; b0 < batch; b0 += chunk) {
     int nb = std::min(chunk, batch - b0);
-    {
+    // deterministic mode: integer accumulation (for T = double the integer grid IS the fine-grid buffer)
+    const bool det = deterministic() && nu.N > 0;
+    unsigned long long* ig = nullptr;
+    double iscale = 0;
+    if (det) {
+      double cmax = 1.0;
+      if (strengths) cmax = device_absmax((const T*)strengths + (int64_t)b0 * nu.N * ncomp, (int64_t)nb * nu.N * ncomp, 1, nu.dtype, st);
+      iscale = det_scale_for((double)nu.N * cmax);
+      ig = sizeof(T) == 8 ? (unsigned long long*)fine
+                          : (unsigned long long*)nu.tmp.get((size_t)nb * ncomp * cells * sizeof(unsigned long long));
+      EFGP_CUDA(cudaMemsetAsync(ig, 0, (size_t)nb * ncomp * cells * sizeof(unsigned long long), st));
+    } else {
       ScopedStage stg("type1.memset_fine", st, 0);
       EFGP_CUDA(cudaMemsetAsync(fine, 0, (size_t)nb * ncomp * cells * sizeof(T), st));
     }
@@ -478,16 +546,22 @@ static void type1_t(Nufft& nu, const void* strengths, int is_complex, int batch,
     T* cs = (strengths && !from_rec) ? (T*)nu.cperm.get((size_t)gc.sp->npos * sizeof(T)) : nullptr;
     for (int b = 0; b < nb; ++b) {
       for (int comp = 0; comp < ncomp; ++comp) {
+        const int64_t goff = (int64_t)(b * ncomp + comp) * cells;
         if (from_rec) {
-          launch_spread(*gc.sp, gc.ker, nullptr, fine + (int64_t)(b * ncomp + comp) * cells, st, true);
+          launch_spread(*gc.sp, gc.ker, nullptr, fine + goff, st, true, ig ? ig + goff : nullptr, iscale);
           continue;
         }
         if (strengths) {
           const T* c = (const T*)strengths + (int64_t)(b0 + b) * nu.N * ncomp + comp;
           permute_strengths(*gc.sp, c, ncomp, cs, st);
         }
-        launch_spread(*gc.sp, gc.ker, cs, fine + (int64_t)(b * ncomp + comp) * cells, st);
+        launch_spread(*gc.sp, gc.ker, cs, fine + goff, st, false, ig ? ig + goff : nullptr, iscale);
       }
+    }
+    if (det) {
+      const int64_t tot = (int64_t)nb * ncomp * cells;
+      det_convert_kernel<T><<<div_up(tot, 256), 256, 0, st>>>(ig, tot, 1.0 / iscale, fine);
+      EFGP_CUDA(cudaGetLastError());
     }
     cufftHandle plan = global_fft().get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_R2C : CUFFT_D2Z, nb * ncomp, st);
     {
@@ -605,6 +679,10 @@ static int probe_group(int t, int remaining, int nb_max) {
 
 static void check_sort_id(const SortedPoints& sp, uint64_t* sort_id) {
   if (!sort_id) return;
+  if (sp.has_orig) {            // the probes are a function of the ORIGINAL index: any sorted set serves
+    *sort_id = ~0ull;
+    return;
+  }
   if (*sort_id == 0)
     *sort_id = sp.id;
   else
@@ -632,17 +710,31 @@ static void type1_probes_t(Nufft& nu, uint64_t seed, int t0, int nb_total, const
   const int chunk = (int)std::max<int64_t>(1, std::min<int64_t>(nb_total, (8ll << 30) / std::max<int64_t>(per, 1)));
   T* fine = (T*)nu.fine.get((size_t)chunk * cells * sizeof(T));
   C* spec = (C*)nu.spec.get((size_t)chunk * slab * sizeof(C));
-  const int nb_max = spread_probe_batch(dim, gc.ker.W, nu.dtype);
+  const int nb_max = deterministic() ? 1 : spread_probe_batch(dim, gc.ker.W, nu.dtype);
   for (int b0 = 0; b0 < nb_total; b0 += chunk) {
     const int nb = std::min(chunk, nb_total - b0);
-    {
+    const bool det = deterministic() && nu.N > 0;
+    unsigned long long* ig = nullptr;
+    double iscale = 0;
+    if (det) {
+      iscale = det_scale_for((double)nu.N);
+      ig = sizeof(T) == 8 ? (unsigned long long*)fine
+                          : (unsigned long long*)nu.tmp.get((size_t)nb * cells * sizeof(unsigned long long));
+      EFGP_CUDA(cudaMemsetAsync(ig, 0, (size_t)nb * cells * sizeof(unsigned long long), st));
+    } else {
       ScopedStage stg("type1.memset_fine", st, 0);
       EFGP_CUDA(cudaMemsetAsync(fine, 0, (size_t)nb * cells * sizeof(T), st));
     }
     for (int b = 0; b < nb;) {
       const int gsz = probe_group(t0 + b0 + b, nb - b, nb_max);
-      launch_spread_probes(*gc.sp, gc.ker, fine + (int64_t)b * cells, ProbeSpec{seed, t0 + b0 + b, gsz}, st);
+      launch_spread_probes(*gc.sp, gc.ker, fine + (int64_t)b * cells, ProbeSpec{seed, t0 + b0 + b, gsz, gc.sp->has_orig ? 1 : 0}, st,
+                           ig ? ig + (int64_t)b * cells : nullptr, iscale);
       b += gsz;
+    }
+    if (det) {
+      const int64_t tot = (int64_t)nb * cells;
+      det_convert_kernel<T><<<div_up(tot, 256), 256, 0, st>>>(ig, tot, 1.0 / iscale, fine);
+      EFGP_CUDA(cudaGetLastError());
     }
     cufftHandle plan = global_fft().get(dim, gc.nf, sizeof(T) == 4 ? CUFFT_R2C : CUFFT_D2Z, nb, st);
     {
@@ -699,7 +791,8 @@ static void type2_probe_dots_t(Nufft& nu, uint64_t seed, int t0, int nb_total, c
     }
     for (int b = 0; b < nb;) {
       const int gsz = probe_group(t0 + b0 + b, nb - b, nb_max);
-      launch_interp_probe_dots(*gc.sp, gc.ker, fine + (int64_t)b * cells, sums + b0 + b, ProbeSpec{seed, t0 + b0 + b, gsz}, st);
+      launch_interp_probe_dots(*gc.sp, gc.ker, fine + (int64_t)b * cells, sums + b0 + b,
+                               ProbeSpec{seed, t0 + b0 + b, gsz, gc.sp->has_orig ? 1 : 0}, st);
       b += gsz;
     }
   }
@@ -732,7 +825,7 @@ void nufft_probes_export(Nufft& nu, uint64_t seed, int t0, int nb, const int64_t
   check_sort_id(*gc.sp, sort_id);
   const size_t esz = nu.dtype == 0 ? 4 : 8;
   for (int b = 0; b < nb; ++b)
-    launch_probe_export(*gc.sp, (char*)z + (size_t)b * nu.N * esz, 1, ProbeSpec{seed, t0 + b, 1}, st);
+    launch_probe_export(*gc.sp, (char*)z + (size_t)b * nu.N * esz, 1, ProbeSpec{seed, t0 + b, 1, gc.sp->has_orig ? 1 : 0}, st);
 }
 
 }  // namespace efgp

@@ -29,6 +29,7 @@ struct SortedPoints {
   int P = 1;            // points per thread
   int RW = 2;           // words of T per record
   bool has_payload = false;   // 2-D only: word 3 of every record holds a real per-point strength
+  bool has_orig = false;      // 64-bit records: the upper half of the position word holds the point's ORIGINAL index
   int64_t ntiles = 0;
   int64_t npos = 0;     // ntiles * kTileThreads * P
   void* rec = nullptr;        // npos records
@@ -85,6 +86,7 @@ struct Nufft {
   uint64_t clock = 0;
   std::vector<std::unique_ptr<SortedPoints>> sorted;  // small LRU cache
   DevBuf fine, spec, tmp, dec, cperm;
+  bool carry_index = false;                    // sorted sets carry the original point index (probe streaming)
   const void* pending_payload = nullptr;       // set by nufft_type1_pair: next sort carries these strengths
   const SortedPoints* fresh_payload_sp = nullptr;  // the sorted set built with them during this call
 };
@@ -92,7 +94,8 @@ struct Nufft {
 // ---- points.cu
 // payload: optional real (N,) strengths carried through the sort into the records (2-D only)
 void build_sorted_points(SortedPoints& sp, const void* x, const void* payload, int64_t N, int dim, int dtype,
-                         double h, const double* xcen, const int64_t* nf, int odd, cudaStream_t st);
+                         double h, const double* xcen, const int64_t* nf, int odd, cudaStream_t st,
+                         bool carry_index = false);
 
 // ---- points.cu : cs[slot] = c[i * cstride] for the point i stored in that slot (npos entries), in two
 // sector-efficient stages (original -> bucket order -> slot order)
@@ -103,14 +106,19 @@ void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t 
 // ---- spread.cu : grid (real, nf^d) += sum_n c_n psi(l - X_n).  cs == nullptr means all ones;
 // otherwise cs holds the strengths in SLOT order (permute_strengths).
 // from_record: take the strengths from the records' payload word instead of cs (needs sp.has_payload)
+// igrid != nullptr: deterministic mode -- the flushes add round(v * iscale) to the 64-bit INTEGER grid igrid instead of
+// v to grid (see DetSpec in spread.cu); the caller converts afterwards (det_convert in nufft.cu)
 void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, void* grid, cudaStream_t st,
-                   bool from_record = false);
+                   bool from_record = false, void* igrid = nullptr, double iscale = 0.0);
+void set_deterministic(int on);
+bool deterministic();
 
 // ---- Rademacher probes regenerated inside the kernels (philox.cuh): spread of pr.nb probes into pr.nb contiguous
 // grids, interpolation with the fused sum_n Z * (.) epilogue, and Z itself in original order (tests)
 struct ProbeSpec;
 int spread_probe_batch(int dim, int W, int dtype);
-void launch_spread_probes(const SortedPoints& sp, const ESKernel& k, void* grid, const ProbeSpec& pr, cudaStream_t st);
+void launch_spread_probes(const SortedPoints& sp, const ESKernel& k, void* grid, const ProbeSpec& pr, cudaStream_t st,
+                          void* igrid = nullptr, double iscale = 0.0);
 void launch_interp_probe_dots(const SortedPoints& sp, const ESKernel& k, const void* grid, double* out,
                               const ProbeSpec& pr, cudaStream_t st);
 void launch_probe_export(const SortedPoints& sp, void* z_out, int64_t ostride, const ProbeSpec& pr, cudaStream_t st);

@@ -42,8 +42,28 @@ __host__ __device__ __forceinline__ T philox_sign_from_bits(const uint32_t (&bit
 
 struct ProbeSpec {
   uint64_t seed;
-  int t0;       // first probe of the launch
-  int nb;       // probes of the launch (all inside one 128-probe block)
+  int t0;         // first probe of the launch
+  int nb;         // probes of the launch (all inside one 128-probe block)
+  int use_orig;   // counter = ORIGINAL index of the point (64-bit records carry it: results do not depend on the order
+                  // inside a cell, on the number of ranks or on the run) instead of its slot in the sorted set
 };
+
+// the Philox counter of a point: upper half of the record word that also holds the level-1 position, or the slot
+template <typename T>
+__host__ __device__ __forceinline__ uint64_t probe_counter(T word, int64_t slot, int use_orig) {
+  if constexpr (sizeof(T) == 8) {
+    if (use_orig) {
+      unsigned long long bits;
+#ifdef __CUDA_ARCH__
+      bits = (unsigned long long)__double_as_longlong((double)word);
+#else
+      double w = (double)word;
+      __builtin_memcpy(&bits, &w, 8);
+#endif
+      return (uint64_t)(bits >> 32);
+    }
+  }
+  return (uint64_t)slot;
+}
 
 }  // namespace efgp

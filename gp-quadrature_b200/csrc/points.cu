@@ -166,7 +166,8 @@ template <typename T, int D, int NS>
 __global__ void __launch_bounds__(kL1Threads, 3)
 bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64_t N, FoldParams<T> p, SortGeom g,
                       int ntiles1, const uint32_t* __restrict__ tileStart, T* __restrict__ R0, T* __restrict__ R1,
-                      T* __restrict__ R2, T* __restrict__ R3, uint16_t* __restrict__ K2, uint16_t* __restrict__ A) {
+                      T* __restrict__ R2, T* __restrict__ R3, uint16_t* __restrict__ K2, uint16_t* __restrict__ A,
+                      uint32_t* __restrict__ RI) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* S = (T*)smem_raw;                                   // [NS][kSortTile]
   uint16_t* SK = (uint16_t*)(S + NS * kSortTile);        // level-2 bin
@@ -174,6 +175,7 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
   uint32_t* cnt = (uint32_t*)(SB + kSortTile);           // [kMaxBuckets]
   uint32_t* lstart = cnt + kMaxBuckets;
   uint32_t* gstart = lstart + kMaxBuckets;
+  uint32_t* SI = gstart + kMaxBuckets;                    // [kSortTile] original indices (only when RI != nullptr)
   __shared__ uint32_t wtot[kMaxBuckets / 32];
   const int tid = threadIdx.x;
   const int64_t tile = blockIdx.x;
@@ -226,6 +228,7 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
       for (int a = 0; a < NS; ++a) S[a * kSortTile + lp] = X[k][a];
       SK[lp] = k2[k];
       SB[lp] = (uint16_t)bk[k];
+      if (RI) SI[lp] = (uint32_t)i;
       A[i] = (uint16_t)lp;      // tile-local position in bucket-major order (< kSortTile)
     }
   }
@@ -239,6 +242,7 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
 #pragma unroll
     for (int d = 0; d < NS; ++d) R[d][a] = S[d * kSortTile + lp];
     K2[a] = SK[lp];
+    if (RI) RI[a] = SI[lp];
   }
 }
 
@@ -327,7 +331,8 @@ __global__ void __launch_bounds__(kSortThreads, 3)
 bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* __restrict__ R2,
                    const T* __restrict__ RY, const uint16_t* __restrict__ K2, const uint32_t* __restrict__ bucketStart,
                    const uint32_t* __restrict__ tile2Base, SortGeom g, const uint32_t* __restrict__ binStart,
-                   uint32_t* __restrict__ binCursor, T* __restrict__ rec, uint32_t* __restrict__ B) {
+                   uint32_t* __restrict__ binCursor, T* __restrict__ rec, uint32_t* __restrict__ B,
+                   const uint32_t* __restrict__ RI) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint32_t* cnt = (uint32_t*)smem_raw;   // [nbins2] counts, then running ranks
   uint32_t* base = cnt + g.nbins2;       // [nbins2] first sorted rank of this tile's points in the bin
@@ -338,15 +343,18 @@ bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* 
   constexpr int RW = rec_words(D);
   constexpr uint32_t kNone = 0xffffffffu;
   uint32_t q[kSortPer];
+  uint32_t oi[kSortPer];
   T w[kSortPer][RW];
 #pragma unroll
   for (int k = 0; k < kSortPer; ++k) {
     const uint32_t a = s + k * kSortThreads + threadIdx.x;
     q[k] = kNone;
+    oi[k] = 0;
 #pragma unroll
     for (int d = 0; d < RW; ++d) w[k][d] = T(0);
     if (a < e) {
       q[k] = K2[a];
+      if (RI) oi[k] = RI[a];
 #pragma unroll
       for (int d = 0; d < D; ++d) w[k][d] = R[d][a];
       if (D == 2 && RY) w[k][3] = RY[a];     // payload rides in the record's spare word
@@ -374,6 +382,9 @@ bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* 
     uint32_t r = base[q[k]] + atomicAdd(&cnt[q[k]], 1u);
     int64_t slot = slot_of_rank((int64_t)r, g.P);
     *reinterpret_cast<uint32_t*>(&w[k][D]) = a;
+    // 64-bit words have room for the ORIGINAL index next to the level-1 position: the regenerated Hutchinson probes
+    // are a function of (seed, probe, original index), independent of the (run-dependent) order inside a cell
+    if constexpr (sizeof(T) == 8) reinterpret_cast<uint32_t*>(&w[k][D])[1] = oi[k];
     store_record<T, RW>(rec + slot * RW, w[k]);
     B[a] = (uint32_t)slot;
   }
@@ -441,8 +452,11 @@ to_bucket_order_kernel(const T* __restrict__ c, int64_t cstride, const uint16_t*
                        T* __restrict__ tmp) {
   __shared__ T S[kSortTile];
   __shared__ uint32_t gstart[kMaxBuckets], lstart[kMaxBuckets], wsum[8];
+  __shared__ uint16_t longlist[kMaxBuckets];
+  __shared__ int nlong;
   const int tid = threadIdx.x;
   const int64_t tile = blockIdx.x;
+  if (tid == 0) nlong = 0;
   T v[kSortPer];
   uint32_t lp[kSortPer];
 #pragma unroll
@@ -470,11 +484,16 @@ to_bucket_order_kernel(const T* __restrict__ c, int64_t cstride, const uint16_t*
     for (uint32_t j = lane; j < cnt; j += G) tmp[gs + j] = S[ls + j];
   }
   // spatially coherent input (gridded data sets, presorted points, clusters): a tile falls into a few buckets with runs
-  // of hundreds of points -- the rest of such a run is copied by the whole CTA (uniform loop: lstart is shared)
-  for (int b = 0; b < nb1; ++b) {
+  // of hundreds of points -- the rest of such a run is copied by the whole CTA
+  if (tid < nb1) {
+    const uint32_t cb = (tid + 1 < nb1 ? lstart[tid + 1] : n_tile) - lstart[tid];
+    if (cb > kLong) longlist[atomicAdd(&nlong, 1)] = (uint16_t)tid;
+  }
+  __syncthreads();
+  for (int q = 0; q < nlong; ++q) {
+    const int b = longlist[q];
     const uint32_t ls = lstart[b];
     const uint32_t cnt = (b + 1 < nb1 ? lstart[b + 1] : n_tile) - ls;
-    if (cnt <= kLong) continue;
     const uint32_t gs = gstart[b];
     for (uint32_t j = kLong + tid; j < cnt; j += kMaxBuckets) tmp[gs + j] = S[ls + j];
   }
@@ -510,8 +529,11 @@ from_bucket_order_kernel(const T* __restrict__ tmp, const uint16_t* __restrict__
                          T* __restrict__ out, int64_t ostride) {
   __shared__ T S[kSortTile];
   __shared__ uint32_t gstart[kMaxBuckets], lstart[kMaxBuckets], wsum[8];
+  __shared__ uint16_t longlist[kMaxBuckets];
+  __shared__ int nlong;
   const int tid = threadIdx.x;
   const int64_t tile = blockIdx.x;
+  if (tid == 0) nlong = 0;                  // (tile_bucket_ranges synchronises before anybody adds to it)
   uint32_t lp[kSortPer];
 #pragma unroll
   for (int k = 0; k < kSortPer; ++k) {      // issued first: consumed after the staging phase
@@ -546,11 +568,17 @@ from_bucket_order_kernel(const T* __restrict__ tmp, const uint16_t* __restrict__
     }
   }
   // long runs (spatially coherent input: gridded data, presorted points, clusters) are finished by the whole CTA
-  // instead of one lane group (measured on Morton-presorted points: 3.4 ms -> see DESIGN.md for this kernel)
-  for (int b = 0; b < nb1; ++b) {
+  // instead of one lane group (measured on Morton-presorted points: 3.4 -> 1.0 ms); the buckets with long runs are
+  // listed first so that the usual case (none) costs one shared-memory flag
+  if (tid < nb1) {
+    const uint32_t cb = (tid + 1 < nb1 ? lstart[tid + 1] : n_tile) - lstart[tid];
+    if (cb > kLong) longlist[atomicAdd(&nlong, 1)] = (uint16_t)tid;
+  }
+  __syncthreads();
+  for (int q = 0; q < nlong; ++q) {
+    const int b = longlist[q];
     const uint32_t lsb = lstart[b];
     const uint32_t cb = (b + 1 < nb1 ? lstart[b + 1] : n_tile) - lsb;
-    if (cb <= kLong) continue;
     const uint32_t gsb = gstart[b];
     for (uint32_t j = kLong + tid; j < cb; j += kMaxBuckets) S[lsb + j] = tmp[gsb + j];
   }
@@ -649,8 +677,11 @@ static int pick_points_per_thread(int64_t N) {
 
 template <typename T, int D>
 static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, const FoldParams<T>& p,
-                     const SortGeom& g, cudaStream_t st) {
+                     const SortGeom& g, cudaStream_t st, bool carry) {
   if (D != 2) ypay = nullptr;   // only the 2-D record has a spare word
+  carry = carry && sizeof(T) == 8;
+  sp.has_orig = carry;
+  uint32_t* RI = carry ? (uint32_t*)pool_alloc(sizeof(uint32_t) * (size_t)N) : nullptr;
   const int ntiles1 = div_up(N, kSortTile);
   const int64_t nhist = (int64_t)g.nb1 * ntiles1;
   const int64_t nbin = (int64_t)g.nb1 * g.nbins2;
@@ -698,9 +729,9 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
     ScopedStage stg(ypay ? "sort.bucket_scatter_kernel_pay" : "sort.bucket_scatter_kernel", st, 1, N);
     const int ns = D + (ypay ? 1 : 0);
     const size_t smem = (size_t)ns * kSortTile * sizeof(T) + 2 * kSortTile * sizeof(uint16_t) +
-                        3 * kMaxBuckets * sizeof(uint32_t);
+                        3 * kMaxBuckets * sizeof(uint32_t) + (carry ? kSortTile * sizeof(uint32_t) : 0);
     const int smem_max = (int)(4 * kSortTile * sizeof(double) + 2 * kSortTile * sizeof(uint16_t) +
-                               3 * kMaxBuckets * sizeof(uint32_t));
+                               3 * kMaxBuckets * sizeof(uint32_t) + kSortTile * sizeof(uint32_t));
     static bool attr_set = false;
     if (!attr_set) {
       EFGP_CUDA(cudaFuncSetAttribute(bucket_scatter_kernel<T, D, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -714,10 +745,10 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
     // software pipeline.)
     if (ypay) {
       bucket_scatter_kernel<T, D, D + 1><<<ntiles1, kL1Threads, smem, st>>>(
-          x, ypay, N, p, g, ntiles1, tileStart, R[0], R[1], RY, nullptr, K2, sp.A);   // D == 2: word 2 = payload
+          x, ypay, N, p, g, ntiles1, tileStart, R[0], R[1], RY, nullptr, K2, sp.A, RI);   // D == 2: word 2 = payload
     } else {
       bucket_scatter_kernel<T, D, D><<<ntiles1, kL1Threads, smem, st>>>(x, nullptr, N, p, g, ntiles1, tileStart,
-                                                                          R[0], R[1], R[2], nullptr, K2, sp.A);
+                                                                          R[0], R[1], R[2], nullptr, K2, sp.A, RI);
     }
   }
   const int ntiles2_max = ntiles1 + g.nb1;
@@ -741,12 +772,13 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
       attr_set2 = true;
     }
     bin_scatter_kernel<T, D><<<ntiles2_max, kSortThreads, 2 * g.nbins2 * sizeof(uint32_t), st>>>(
-        R[0], R[1], R[2], RY, K2, bucketStart, tile2Base, g, binStart, binCursor, rec, sp.B);
+        R[0], R[1], R[2], RY, K2, bucketStart, tile2Base, g, binStart, binCursor, rec, sp.B, RI);
     if (sp.npos > N)
       pad_slots_kernel<T, D><<<div_up(sp.npos - N, 256), 256, 0, st>>>(N, sp.npos, g.P, rec);
   }
   EFGP_CUDA(cudaGetLastError());
   pool_free(scan_tmp);
+  if (RI) pool_free(RI);
   pool_free(K2);
   if (RY) pool_free(RY);
   for (int a = 0; a < D; ++a) pool_free(R[a]);
@@ -756,7 +788,7 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
 
 template <typename T>
 static void build_t(SortedPoints& sp, const T* x, const T* ypay, int64_t N, int dim, double h, const double* xcen,
-                    const int64_t* nf, int odd, cudaStream_t st) {
+                    const int64_t* nf, int odd, cudaStream_t st, bool carry) {
   FoldParams<T> p;
   p.h = (T)h;
   p.shift = odd ? T(0.5) : T(0);
@@ -810,13 +842,13 @@ static void build_t(SortedPoints& sp, const T* x, const T* ypay, int64_t N, int 
   }
   g.nbins2 = (int)((g.cpb + g.g - 1) / g.g);
   g.P = sp.P;
-  if (dim == 1) build_td<T, 1>(sp, x, ypay, N, p, g, st);
-  if (dim == 2) build_td<T, 2>(sp, x, ypay, N, p, g, st);
-  if (dim == 3) build_td<T, 3>(sp, x, ypay, N, p, g, st);
+  if (dim == 1) build_td<T, 1>(sp, x, ypay, N, p, g, st, carry);
+  if (dim == 2) build_td<T, 2>(sp, x, ypay, N, p, g, st, carry);
+  if (dim == 3) build_td<T, 3>(sp, x, ypay, N, p, g, st, carry);
 }
 
 void build_sorted_points(SortedPoints& sp, const void* x, const void* payload, int64_t N, int dim, int dtype,
-                         double h, const double* xcen, const int64_t* nf, int odd, cudaStream_t st) {
+                         double h, const double* xcen, const int64_t* nf, int odd, cudaStream_t st, bool carry_index) {
   sp.dim = dim;
   sp.dtype = dtype;
   sp.N = N;
@@ -824,9 +856,9 @@ void build_sorted_points(SortedPoints& sp, const void* x, const void* payload, i
   for (int a = 0; a < kMaxDim; ++a) sp.nf[a] = a < dim ? nf[a] : 1;
   if (N == 0) return;
   if (dtype == 0)
-    build_t<float>(sp, (const float*)x, (const float*)payload, N, dim, h, xcen, nf, odd, st);
+    build_t<float>(sp, (const float*)x, (const float*)payload, N, dim, h, xcen, nf, odd, st, carry_index);
   else
-    build_t<double>(sp, (const double*)x, (const double*)payload, N, dim, h, xcen, nf, odd, st);
+    build_t<double>(sp, (const double*)x, (const double*)payload, N, dim, h, xcen, nf, odd, st, carry_index);
 }
 
 }  // namespace efgp

@@ -56,6 +56,24 @@ __device__ __forceinline__ void load_record4(const T* __restrict__ p, T* w) {
   }
 }
 
+// Deterministic mode (efgp_set_deterministic): every (point, grid cell) contribution is added as a fixed-point integer.
+// Integer addition is associative, so the grid is BIT-IDENTICAL from run to run whatever order the atomics land in and
+// whatever order the sort left the points of a cell in (the default mode sums runs of points in floating point and
+// flushes with fp64 REDs: the last bits, and with them CG iteration counts at tight tolerances, vary).  Only the
+// per-point kernels (spread_direct_kernel) implement it; launch_w routes every geometry there in this mode.
+// det.scale = 2^k with N * max|c| * 2^k < 2^62: no overflow; resolution 2^-k of the largest possible cell value.
+struct DetSpec {
+  unsigned long long* ig;   // integer grid (same geometry), nullptr = floating-point mode
+  double scale;
+};
+template <typename T>
+__device__ __forceinline__ void grid_add(T* __restrict__ grid, int64_t idx, T v, const DetSpec& det) {
+  if (det.ig)
+    atomicAdd(det.ig + idx, (unsigned long long)__double2ll_rn((double)v * det.scale));
+  else
+    atomicAdd(grid + idx, v);
+}
+
 __device__ __forceinline__ int wrap_idx(int i, int n) {
   if (i < 0) i += n;
   if (i >= n) i -= n;
@@ -68,7 +86,7 @@ __device__ __forceinline__ int wrap_idx(int i, int n) {
 template <typename T, int W, int HAS_C>
 __global__ void __launch_bounds__(kTileThreads)
 spread1d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int nf0, T* __restrict__ grid,
-                const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
+                const __grid_constant__ ESDev<T> es, ProbeSpec pr, DetSpec det) {
   const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + threadIdx.x;
   T acc[W];
 #pragma unroll
@@ -82,7 +100,7 @@ spread1d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
     T cv = HAS_C == 1 ? cs[pos] : T(1);
     if (HAS_C == 3) {
       uint32_t bits[4];
-      philox_bits(pr.seed, (uint64_t)pos, (uint32_t)(pr.t0 >> 7), bits);
+      philox_bits(pr.seed, probe_counter<T>(pr.use_orig ? rec[pos * 2 + 1] : T(0), pos, pr.use_orig), (uint32_t)(pr.t0 >> 7), bits);
       cv = philox_sign_from_bits<T>(bits, pr.t0);
     }
     int c0 = (int)X;
@@ -134,11 +152,11 @@ __host__ __device__ constexpr int spread2d_min_ctas() { return (W * W * NB <= 25
 template <typename T, int W, int HAS_C, int NB>
 __global__ void __launch_bounds__(kTileThreads, (spread2d_min_ctas<W, NB>()))
 spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int nf0,
-                int nf1, T* __restrict__ grid, const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
+                int nf1, T* __restrict__ grid, const __grid_constant__ ESDev<T> es, ProbeSpec pr, DetSpec det) {
   static_assert(NB == 1 || HAS_C == 3, "multi-RHS spreading is for regenerated probes");
   constexpr int S = kRingStages;
   __shared__ __align__(16) T ring[S][kTileThreads][2];   // (X0, X1) of each thread's next points
-  __shared__ T cring[(HAS_C == 1 || HAS_C == 2) ? S : 1][kTileThreads];
+  __shared__ T cring[HAS_C ? S : 1][kTileThreads];      // strengths, or (mode 3) the record word with the original index
   const int t = threadIdx.x;
   const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + t;
   auto issue = [&](int j) {
@@ -148,6 +166,7 @@ spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
       cp_async_word<2 * sizeof(T)>(&ring[s][t][0], rec + pos * 4);   // one 16-byte (8 for f32) copy per point
       if (HAS_C == 1) cp_async_word<sizeof(T)>(&cring[s][t], cs + pos);
       if (HAS_C == 2) cp_async_word<sizeof(T)>(&cring[s][t], rec + pos * 4 + 3);
+      if (HAS_C == 3) cp_async_word<sizeof(T)>(&cring[s][t], rec + pos * 4 + 2);
     }
     cp_async_commit();
   };
@@ -174,7 +193,8 @@ spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
     for (int b = 0; b < NB; ++b) cv[b] = (HAS_C == 1 || HAS_C == 2) ? cring[s][t] : T(1);
     if (HAS_C == 3) {
       uint32_t bits[4];
-      philox_bits(pr.seed, (uint64_t)(base + (int64_t)j * kTileThreads), (uint32_t)(pr.t0 >> 7), bits);
+      philox_bits(pr.seed, probe_counter<T>(cring[s][t], base + (int64_t)j * kTileThreads, pr.use_orig),
+                  (uint32_t)(pr.t0 >> 7), bits);
 #pragma unroll
       for (int b = 0; b < NB; ++b) cv[b] = philox_sign_from_bits<T>(bits, pr.t0 + b);
     }
@@ -231,7 +251,7 @@ __host__ __device__ constexpr size_t tile3_smem_bytes() {
 template <typename T, int W, int HAS_C>
 __global__ void __launch_bounds__(kT3Threads)
 spread3d_tile_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int64_t N, int nf0, int nf1, int nf2,
-                     T* __restrict__ grid, const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
+                     T* __restrict__ grid, const __grid_constant__ ESDev<T> es, ProbeSpec pr, DetSpec det) {
   constexpr int E = kTile3 + W - 1;
   constexpr int EP = E | 1;   // padded (odd) row stride
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
@@ -288,7 +308,8 @@ spread3d_tile_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int64_
       T cvv = HAS_C == 1 ? cs[b0 + tid - 96] : T(1);
       if (HAS_C == 3) {                      // 3-D sets keep rank order (P = 1): the slot is the sorted rank
         uint32_t bits[4];
-        philox_bits(pr.seed, (uint64_t)(b0 + tid - 96), (uint32_t)(pr.t0 >> 7), bits);
+        philox_bits(pr.seed, probe_counter<T>(pr.use_orig ? rec[(b0 + tid - 96) * 4 + 3] : T(0), b0 + tid - 96, pr.use_orig),
+                    (uint32_t)(pr.t0 >> 7), bits);
         cvv = philox_sign_from_bits<T>(bits, pr.t0);
       }
       CV[tid - 96] = cvv;
@@ -360,23 +381,33 @@ template <typename T, int W, int D, int HAS_C>
 __global__ void __launch_bounds__(256)
 spread_direct_kernel(const T* __restrict__ rec,
                      const T* __restrict__ cs, int64_t npos, int nf0, int nf1, int nf2, T* __restrict__ grid,
-                     const __grid_constant__ ESDev<T> es, ProbeSpec pr) {
+                     const __grid_constant__ ESDev<T> es, ProbeSpec pr, DetSpec det) {
   int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= npos) return;
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
-  T Xr[4];
-  load_record4<T>(rec + n * 4, Xr);
+  T Xr[4] = {T(0), T(0), T(0), T(0)};
+  if constexpr (D == 1) {
+    Xr[0] = rec[n * 2];
+    Xr[1] = rec[n * 2 + 1];
+  } else {
+    load_record4<T>(rec + n * 4, Xr);
+  }
   T X0 = Xr[0];
   if (X0 < T(0)) return;
   T cv = HAS_C == 1 ? cs[n] : (HAS_C == 2 ? Xr[3] : T(1));
   if (HAS_C == 3) {
     uint32_t bits[4];
-    philox_bits(pr.seed, (uint64_t)n, (uint32_t)(pr.t0 >> 7), bits);
+    philox_bits(pr.seed, probe_counter<T>(Xr[D], n, pr.use_orig), (uint32_t)(pr.t0 >> 7), bits);
     cv = philox_sign_from_bits<T>(bits, pr.t0);
   }
   T k0[W], k1[W], k2[W];
   int c0 = (int)X0;
   es_eval<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
+  if constexpr (D == 1) {
+#pragma unroll
+    for (int i = 0; i < W; ++i) grid_add<T>(grid, wrap_idx(c0 - OFF + i, nf0), cv * k0[i], det);
+    return;
+  }
   T X1 = Xr[1];
   int c1 = (int)X1;
   es_eval<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
@@ -389,10 +420,10 @@ spread_direct_kernel(const T* __restrict__ rec,
   if (D == 2) {
 #pragma unroll
     for (int i = 0; i < W; ++i) {
-      T* row = grid + (int64_t)wrap_idx(c0 - OFF + i, nf0) * nf1;
+      const int64_t row = (int64_t)wrap_idx(c0 - OFF + i, nf0) * nf1;
       T a = cv * k0[i];
 #pragma unroll
-      for (int j = 0; j < W; ++j) atomicAdd(row + wrap_idx(c1 - OFF + j, nf1), a * k1[j]);
+      for (int j = 0; j < W; ++j) grid_add<T>(grid, row + wrap_idx(c1 - OFF + j, nf1), a * k1[j], det);
     }
   } else {
     int cols[W];
@@ -404,10 +435,10 @@ spread_direct_kernel(const T* __restrict__ rec,
       T a = cv * k0[i];
 #pragma unroll 1
       for (int j = 0; j < W; ++j) {
-        T* row = grid + (r0 + wrap_idx(c1 - OFF + j, nf1)) * nf2;
+        const int64_t row = (r0 + wrap_idx(c1 - OFF + j, nf1)) * nf2;
         T b = a * k1[j];
 #pragma unroll
-        for (int l = 0; l < W; ++l) atomicAdd(row + cols[l], b * k2[l]);
+        for (int l = 0; l < W; ++l) grid_add<T>(grid, row + cols[l], b * k2[l], det);
       }
     }
   }
@@ -425,7 +456,7 @@ int spread_probe_batch(int dim, int W, int dtype) {
 
 template <typename T, int W>
 static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st, int mode,
-                     const ProbeSpec& pr) {
+                     const ProbeSpec& pr, const DetSpec& det) {
   ESDev<T> es;
   es_to_dev<T>(k, es);
   const T* rec = (const T*)sp.rec;
@@ -436,72 +467,89 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
            mode == 0 ? "_ones" : (mode == 2 ? "_rec" : (mode == 3 ? (pr.nb == 4 ? "_probes4" : (pr.nb == 2 ? "_probes2" : "_probes1")) : "")));
   ScopedStage stg(nm, st, 1, sp.N * (mode == 3 ? pr.nb : 1));
   const int nf0 = (int)sp.nf[0], nf1 = (int)sp.nf[1], nf2 = (int)sp.nf[2];
+  // Deterministic mode: one fixed-point RED per (point, grid cell).  Register / shared-memory footprints would sum a
+  // run of points in floating point first, in the (run-dependent) order the sort left them inside a cell; per-point
+  // integer contributions are order-independent.  Slow by design: a parity / debug mode.
+  const bool per_point = det.ig != nullptr;
+  if (per_point && sp.dim <= 2) {
+    EFGP_CHECK(mode != 3 || pr.nb == 1, "one probe per launch in deterministic mode");
+    const int nb = div_up(sp.npos, 256);
+#define EFGP_DIRECT(D_)                                                                                          \
+    if (mode == 3) spread_direct_kernel<T, W, D_, 3><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr, det); \
+    else if (mode == 2) spread_direct_kernel<T, W, D_, 2><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr, det); \
+    else if (mode == 1) spread_direct_kernel<T, W, D_, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr, det); \
+    else spread_direct_kernel<T, W, D_, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr, det);
+    if (sp.dim == 1) { EFGP_DIRECT(1) } else { EFGP_DIRECT(2) }
+#undef EFGP_DIRECT
+    EFGP_CUDA(cudaGetLastError());
+    return;
+  }
   if (sp.dim == 1) {
     if (mode == 3)
-      spread1d_kernel<T, W, 3><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es, pr);
+      spread1d_kernel<T, W, 3><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es, pr, det);
     else if (mode == 1)
-      spread1d_kernel<T, W, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es, pr);
+      spread1d_kernel<T, W, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es, pr, det);
     else
-      spread1d_kernel<T, W, 0><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es, pr);
+      spread1d_kernel<T, W, 0><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es, pr, det);
   } else if (sp.dim == 2) {
     if constexpr (W <= kRegMaxW) {
       if (mode == 3) {
         if constexpr (W <= 5) {
           if (pr.nb == 4) {
-            spread2d_kernel<T, W, 3, 4><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
+            spread2d_kernel<T, W, 3, 4><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr, det);
             EFGP_CUDA(cudaGetLastError());
             return;
           }
         }
         if constexpr (W <= 7) {
           if (pr.nb == 2) {
-            spread2d_kernel<T, W, 3, 2><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
+            spread2d_kernel<T, W, 3, 2><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr, det);
             EFGP_CUDA(cudaGetLastError());
             return;
           }
         }
         EFGP_CHECK(pr.nb == 1, "probe batch not supported by this spreading width");
-        spread2d_kernel<T, W, 3, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
+        spread2d_kernel<T, W, 3, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr, det);
       } else if (mode == 2)
-        spread2d_kernel<T, W, 2, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
+        spread2d_kernel<T, W, 2, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr, det);
       else if (mode == 1)
-        spread2d_kernel<T, W, 1, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
+        spread2d_kernel<T, W, 1, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr, det);
       else
-        spread2d_kernel<T, W, 0, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr);
+        spread2d_kernel<T, W, 0, 1><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, nf1, grid, es, pr, det);
     } else {
       EFGP_CHECK(mode != 3 || pr.nb == 1, "probe batch not supported by this spreading width");
       int nb = div_up(sp.npos, 256);
       if (mode == 3)
-        spread_direct_kernel<T, W, 2, 3><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr);
+        spread_direct_kernel<T, W, 2, 3><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr, det);
       else if (mode == 2)
-        spread_direct_kernel<T, W, 2, 2><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr);
+        spread_direct_kernel<T, W, 2, 2><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr, det);
       else if (mode == 1)
-        spread_direct_kernel<T, W, 2, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr);
+        spread_direct_kernel<T, W, 2, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr, det);
       else
-        spread_direct_kernel<T, W, 2, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr);
+        spread_direct_kernel<T, W, 2, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, 1, grid, es, pr, det);
     }
-  } else if (getenv("EFGP_3D_DIRECT")) {   // per-point REDs (kept for A/B measurements)
+  } else if (per_point || getenv("EFGP_3D_DIRECT")) {   // per-point REDs (deterministic mode; A/B measurements)
     EFGP_CHECK(mode != 3 || pr.nb == 1, "one probe per launch in 3-D");
     int nb = div_up(sp.npos, 256);
     if (mode == 3)
-      spread_direct_kernel<T, W, 3, 3><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es, pr);
+      spread_direct_kernel<T, W, 3, 3><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es, pr, det);
     else if (cs)
-      spread_direct_kernel<T, W, 3, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es, pr);
+      spread_direct_kernel<T, W, 3, 1><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es, pr, det);
     else
-      spread_direct_kernel<T, W, 3, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es, pr);
+      spread_direct_kernel<T, W, 3, 0><<<nb, 256, 0, st>>>(rec, cs, sp.npos, nf0, nf1, nf2, grid, es, pr, det);
   } else {
     EFGP_CHECK(mode != 3 || pr.nb == 1, "one probe per launch in 3-D");
     const size_t smem = tile3_smem_bytes<T, W>();
     int nb = div_up(sp.N, kT3Chunk);
     if (mode == 3) {
       EFGP_CUDA(cudaFuncSetAttribute(spread3d_tile_kernel<T, W, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      spread3d_tile_kernel<T, W, 3><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es, pr);
+      spread3d_tile_kernel<T, W, 3><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es, pr, det);
     } else if (cs) {
       EFGP_CUDA(cudaFuncSetAttribute(spread3d_tile_kernel<T, W, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      spread3d_tile_kernel<T, W, 1><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es, pr);
+      spread3d_tile_kernel<T, W, 1><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es, pr, det);
     } else {
       EFGP_CUDA(cudaFuncSetAttribute(spread3d_tile_kernel<T, W, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      spread3d_tile_kernel<T, W, 0><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es, pr);
+      spread3d_tile_kernel<T, W, 0><<<nb, kT3Threads, smem, st>>>(rec, cs, sp.N, nf0, nf1, nf2, grid, es, pr, det);
     }
   }
   EFGP_CUDA(cudaGetLastError());
@@ -509,11 +557,11 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
 
 template <typename T>
 static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* cs, T* grid, cudaStream_t st, int mode,
-                     const ProbeSpec& pr) {
+                     const ProbeSpec& pr, const DetSpec& det) {
   switch (k.W) {
 #define EFGP_CASE(w) \
   case w:            \
-    launch_w<T, w>(sp, k, cs, grid, st, mode, pr); \
+    launch_w<T, w>(sp, k, cs, grid, st, mode, pr, det); \
     break;
     EFGP_CASE(2) EFGP_CASE(3) EFGP_CASE(4) EFGP_CASE(5) EFGP_CASE(6) EFGP_CASE(7) EFGP_CASE(8) EFGP_CASE(9)
     EFGP_CASE(10) EFGP_CASE(11) EFGP_CASE(12) EFGP_CASE(13) EFGP_CASE(14) EFGP_CASE(15) EFGP_CASE(16)
@@ -524,27 +572,30 @@ static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
 }
 
 void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, void* grid, cudaStream_t st,
-                   bool from_record) {
+                   bool from_record, void* igrid, double iscale) {
   if (sp.N == 0) return;
+  const DetSpec det{(unsigned long long*)igrid, iscale};
   EFGP_CHECK(!from_record || (sp.has_payload && sp.dim == 2), "sorted point set carries no strength payload");
   EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
   const int mode = from_record ? 2 : (cs ? 1 : 0);
-  ProbeSpec pr{0, 0, 1};
+  ProbeSpec pr{0, 0, 1, 0};
   if (sp.dtype == 0)
-    launch_t<float>(sp, k, (const float*)cs, (float*)grid, st, mode, pr);
+    launch_t<float>(sp, k, (const float*)cs, (float*)grid, st, mode, pr, det);
   else
-    launch_t<double>(sp, k, (const double*)cs, (double*)grid, st, mode, pr);
+    launch_t<double>(sp, k, (const double*)cs, (double*)grid, st, mode, pr, det);
 }
 
 // grids b = 0 .. pr.nb-1 (contiguous, nf^d each) += sum over points of Rademacher(seed, pr.t0 + b, slot) psi(l - X)
-void launch_spread_probes(const SortedPoints& sp, const ESKernel& k, void* grid, const ProbeSpec& pr, cudaStream_t st) {
+void launch_spread_probes(const SortedPoints& sp, const ESKernel& k, void* grid, const ProbeSpec& pr, cudaStream_t st,
+                          void* igrid, double iscale) {
   if (sp.N == 0) return;
+  const DetSpec det{(unsigned long long*)igrid, iscale};
   EFGP_CHECK((k.W & 1) == sp.odd, "kernel width parity does not match the sorted point set");
   EFGP_CHECK(pr.nb >= 1 && (pr.t0 >> 7) == ((pr.t0 + pr.nb - 1) >> 7), "a probe launch must stay inside one 128-probe block");
   if (sp.dtype == 0)
-    launch_t<float>(sp, k, (const float*)nullptr, (float*)grid, st, 3, pr);
+    launch_t<float>(sp, k, (const float*)nullptr, (float*)grid, st, 3, pr, det);
   else
-    launch_t<double>(sp, k, (const double*)nullptr, (double*)grid, st, 3, pr);
+    launch_t<double>(sp, k, (const double*)nullptr, (double*)grid, st, 3, pr, det);
 }
 
 }  // namespace efgp

@@ -31,6 +31,7 @@ _SIGNATURES = {
     "efgp_timing_enable": (ctypes.c_int, [ctypes.c_int]),
     "efgp_timing_report": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_int64]),
     "efgp_pool_trim": (ctypes.c_int, []),
+    "efgp_set_deterministic": (ctypes.c_int, [ctypes.c_int]),
     "efgp_measure_fp64_peak": (ctypes.c_int, [ctypes.POINTER(ctypes.c_double), ctypes.c_void_p]),
     "efgp_nufft_create": (ctypes.c_int, [ctypes.POINTER(vp), ctypes.c_int, ctypes.c_int]),
     "efgp_nufft_set_points": (ctypes.c_int, [vp, vp, ctypes.c_int64, ctypes.c_double, c_dblp, vp]),
@@ -58,6 +59,7 @@ _SIGNATURES = {
     "efgp_lanczos": (ctypes.c_int, [vp, vp, ctypes.c_double, ctypes.c_int, vp, ctypes.c_int, ctypes.c_int,
                                     ctypes.c_double, vp, vp, vp]),
     "efgp_nufft_rescale": (ctypes.c_int, [vp, ctypes.c_double, c_dblp]),
+    "efgp_nufft_carry_index": (ctypes.c_int, [vp, ctypes.c_int]),
     "efgp_comm_unique_id": (ctypes.c_int, [vp]),
     "efgp_comm_init": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, vp]),
     "efgp_comm_destroy": (ctypes.c_int, []),
@@ -116,6 +118,11 @@ def i64_array(vals):
 def dbl_array(vals):
     vals = [float(v) for v in vals]
     return (ctypes.c_double * len(vals))(*vals)
+
+
+def set_deterministic(on=True):
+    """Bit-reproducible type-1 transforms (fixed-point accumulation): see efgp_set_deterministic in the header."""
+    check(lib().efgp_set_deterministic(1 if on else 0))
 
 
 def timing_enable(on=True):

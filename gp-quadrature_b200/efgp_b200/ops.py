@@ -85,6 +85,12 @@ class NufftPlan:
             except Exception:
                 pass
 
+    def carry_index(self, on=True):
+        """Sorted sets carry the points' original indices (efgp_nufft_carry_index): the regenerated probes then do not
+        depend on the sort.  Changing the setting drops the existing sorted sets."""
+        check(_lib.lib().efgp_nufft_carry_index(self._h, 1 if on else 0))
+        return self
+
     def ensure(self, h, xcen=None):
         """Same points, (possibly) new spacing / centre (efgp_nufft_rescale): a no-op when nothing changed."""
         h = float(h)

@@ -654,6 +654,15 @@ def efgpnd_gradient_batched(
             xcen = torch.zeros(d, device=device, dtype=rdtype)
             m_conv = (mtot - 1) // 2
 
+        # Point-space probes regenerated inside the kernels (no (T, N) arrays)?  float64: the sorted sets carry the
+        # points' original indices, so the probes do not depend on the sort, the run or the number of ranks.
+        # float32 records have no room for the index: slot counters, which differ between ranks -> stored probes there.
+        stream_probes = bool(device_probes if device_probes is not None else PROBE_DEVICE is None) and len(trace_idx) > 0
+        if stream_probes and rdtype == torch.float32 and probe_group is not None:
+            stream_probes = False
+        if stream_probes and rdtype == torch.float64:
+            _shared_plan(x, h_f, xcen).carry_index(True)
+
         with rf("3_toeplitz_setup"):
             # generator first: the F*y / F beta transforms then reuse its (finer) sorted grid
             v_kernel = compute_convolution_vector_vectorized_dD(m_conv, x, h_f).to(dtype=cdtype)
@@ -703,7 +712,7 @@ def efgpnd_gradient_batched(
             nk = len(trace_idx)
             if Tl == 0:
                 return torch.zeros(nk, device=device, dtype=rdtype), torch.zeros((), device=device, dtype=rdtype), 0, 0
-            stream = (device_probes if device_probes is not None else PROBE_DEVICE is None) and nk > 0
+            stream = stream_probes
             plan = nufft_op._plan.ensure(nufft_op._hf, nufft_op._xc)
             sort_id, Zl = 0, None
             if stream:

@@ -38,6 +38,12 @@ const char* efgp_last_error(void);
 int efgp_timing_enable(int on);
 int efgp_timing_report(char* buf, int64_t cap);
 int efgp_pool_trim(void);
+/* Deterministic spreading (also EFGP_DETERMINISTIC=1): the type-1 kernels accumulate 64-bit FIXED-POINT integers, whose
+ * addition is associative, so every transform -- and with it every CG iterate and iteration count -- is bit-identical
+ * from run to run (the default fp64 atomics land in a varying order: last-bit differences).  Resolution: 2^-62 of
+ * N * max|strength| per addend; one host synchronisation per transform with explicit strengths.  A parity / debug
+ * mode ("deterministic-reduction mode for parity tests"). */
+int efgp_set_deterministic(int on);
 int efgp_measure_fp64_peak(double* tflops, void* stream);
 
 /* ---- NUFFT: replaces class NUFFT (efgpnd.py:1423-1549) and the pytorch_finufft calls under it */
@@ -51,6 +57,11 @@ void efgp_nufft_destroy(efgp_nufft* nu);
  * NUFFT(x, xcen, h, eps) object on the same x, efgpnd.py:103-107 inside efgpnd.py:1138-1195).  Keeps the handle and its
  * borrowed point pointer; the bin-sorted sets are rebuilt by the next transform if (h, xcen) changed. */
 int efgp_nufft_rescale(efgp_nufft* nu, double h, const double* xcen);
+/* on != 0: the sorted sets of this handle carry every point's ORIGINAL index (float64 handles: it rides in the unused
+ * half of a record word, +8 bytes per point of sort traffic), which makes the regenerated Hutchinson probes below a
+ * function of (seed, probe, original index): independent of the run, of the order inside a cell and of how probes are
+ * split over ranks.  Off (default, and always for float32): the counter is the point's slot in the sorted set. */
+int efgp_nufft_carry_index(efgp_nufft* nu, int on);
 
 /* NUFFT.type1 -> pff.finufft_type1(phi, vals, out_shape, eps, isign=-1, modeord=False)
  * (efgpnd.py:1454-1508).  strengths: (batch, npts) real (is_complex=0) or complex (1), NULL = all
@@ -192,7 +203,8 @@ int efgp_variance_reduce(const void* x, int64_t npts, int dim, int mtot, double 
 
 /* ---- Hutchinson probes streamed through the transforms: the Monte-Carlo trace of efgpnd_gradient_batched
  * (efgpnd.py:176-241) without its (T, N) arrays Z, F(D'F^*Z) and F(ws beta).  Probe t is the Rademacher vector
- * Z_t[n] = sign bit of Philox-4x32-10(key = seed, counter = (slot of point n in the sorted set, t / 128)), regenerated
+ * Z_t[n] = sign bit of Philox-4x32-10(key = seed, counter = (index of point n, t / 128)) -- the ORIGINAL index with
+ * efgp_nufft_carry_index(nu, 1), else the slot of the point in the sorted set --, regenerated
  * inside the spread kernel and inside the interpolation epilogue, never stored.
  *   efgp_nufft_type1_probes:     out[b] = scale * F^* Z_{t0+b}, b < nprobes: (nprobes, *out_shape) complex (efgpnd.py:183)
  *   efgp_nufft_type2_probe_dots: sums[b] = sum_n Z_{t0+b}[n] * Re(F (scale * modes[b]))[n]: modes (nprobes, *shape)

@@ -1,7 +1,7 @@
 #!/bin/bash
 # Round-2 GPU session 2 (1 GPU): full parity suite, headline bench (uninstrumented value), config-4 bench, presorted-input run.
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
-O=gpurun_out/s2
+O=gpurun_out/s3
 mkdir -p $O
 echo "== pytest" ; date
 timeout 2400 python -m pytest tests -q -m gpu --timeout=1200 --deselect tests/test_nccl_sharding_gpu.py > $O/pytest.log 2>&1

@@ -78,7 +78,7 @@ def test_fused_fit_equals_the_step_by_step_fit(kname, d, dt):
     import efgpnd
     from kernels import SquaredExponential, Matern
     g = torch.Generator(device="cuda").manual_seed(4)
-    N = 20000
+    N = 5000          # with sigma^2 = 0.5: well conditioned, CG converges far below its 2 M iteration cap
     x = (torch.rand(N, d, dtype=torch.float64, device="cuda", generator=g) * 2 - 1).to(dt)
     y = (torch.sin(3 * x[:, 0].double()) + 0.1 * torch.randn(N, dtype=torch.float64, device="cuda", generator=g)).to(dt)
     f64 = dt == torch.float64
@@ -86,7 +86,7 @@ def test_fused_fit_equals_the_step_by_step_fit(kname, d, dt):
     for fused in (True, False):
         k = SquaredExponential(dimension=d, init_lengthscale=0.3, init_variance=1.1) if kname == "se" else \
             Matern(dimension=d, init_lengthscale=0.6, init_variance=0.9, nu={"matern32": 1.5, "matern52": 2.5}[kname])
-        m = efgpnd.EFGPND(x, y, k, sigmasq=0.07, eps=1e-3, nufft_eps=1e-9 if f64 else 1e-5,
+        m = efgpnd.EFGPND(x, y, k, sigmasq=0.5, eps=1e-3, nufft_eps=1e-9 if f64 else 1e-5,
                           opts={"cg_tolerance": 1e-10 if f64 else 1e-5, "fused_fit": fused}, estimate_params=False)
         mean, _ = m.predict(x[:500], return_variance=False)
         out.append((m, mean))
@@ -97,11 +97,12 @@ def test_fused_fit_equals_the_step_by_step_fit(kname, d, dt):
     assert rel(a._toeplitz.plan.v, b._toeplitz.plan.v) < (1e-9 if f64 else 1e-4)
     # two CG runs stopped at the same relative residual: beta itself agrees only up to tolerance x condition number
     # (Matern-3/2 in 1-D: 1.5e-3), so beta is compared THROUGH the operator, where both satisfy A beta = rhs to 1e-10
-    A = efgpnd.create_A_mean(b._ws, b._toeplitz, 0.07, b._ws.dtype)
+    A = efgpnd.create_A_mean(b._ws, b._toeplitz, 0.5, b._ws.dtype)
     assert rel(A(a._beta), A(b._beta)) < (1e-8 if f64 else 1e-3)
-    assert rel(a._beta, b._beta) < (1e-2 if f64 else 5e-2)
-    assert rel(ma, mb) < (1e-3 if f64 else 1e-2)
-    assert abs(int(a.last_fit_stats["mean_cg_iters"]) - int(b.last_fit_stats["mean_cg_iters"])) <= 1
+    assert rel(a._beta, b._beta) < (1e-5 if f64 else 5e-2)
+    assert rel(ma, mb) < (1e-6 if f64 else 1e-2)
+    ia, ib = int(a.last_fit_stats["mean_cg_iters"]), int(b.last_fit_stats["mean_cg_iters"])
+    assert ia < 2 * a.last_fit_stats["feature_count"] and abs(ia - ib) <= max(1, ib // 25)
     assert tuple(a._xis.shape) == tuple(b._xis.shape) and rel(a._xis, b._xis) < 1e-15 + (0 if f64 else 1e-6)
     assert a._ws.is_complex() and rel(a._ws.real, b._ws.real) < (1e-13 if f64 else 1e-6)
 
@@ -129,3 +130,38 @@ def test_library_bounding_box_and_rescale():
     plan.ensure(0.31)
     a3 = plan.type1(c, (21, 21), 1e-9)
     assert float((a3 - a1).abs().max() / a1.abs().max()) < 1e-12
+
+
+@pytest.mark.parametrize("d", [1, 2, 3])
+def test_deterministic_mode_is_bit_reproducible(d):
+    """efgp_set_deterministic: fixed-point accumulation makes every type-1 transform, and with it the fit and the CG
+    iteration counts, BIT-identical from run to run (fresh sorts included), at the default accuracy."""
+    import efgpnd
+    from efgp_b200 import _lib, ops
+    from kernels import SquaredExponential
+    g = torch.Generator(device="cuda").manual_seed(12)
+    N = 40000
+    x = torch.rand(N, d, dtype=torch.float64, device="cuda", generator=g) * 2 - 1
+    y = torch.sin(3 * x[:, 0]) + 0.1 * torch.randn(N, dtype=torch.float64, device="cuda", generator=g)
+    shape = (17,) * d
+    ref = ops.NufftPlan(x, 0.4).type1(y, shape, 1e-9)
+    _lib.set_deterministic(True)
+    try:
+        outs = [ops.NufftPlan(x, 0.4).type1(y, shape, 1e-9) for _ in range(3)]          # three independent sorts
+        assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+        assert float((outs[0] - ref).abs().max() / ref.abs().max()) < 1e-9                 # same transform
+        ones = [ops.NufftPlan(x, 0.4).type1(None, shape, 6e-8) for _ in range(2)]
+        assert torch.equal(ones[0], ones[1])
+        pr = [ops.NufftPlan(x, 0.4).carry_index(True).type1_probes(5, 0, 3, shape, 1e-6)[0] for _ in range(2)]
+        assert torch.equal(pr[0], pr[1])
+        fits = []
+        for _ in range(2):
+            efgpnd._PLAN_CACHE.clear()
+            k = SquaredExponential(dimension=d, init_lengthscale=0.3, init_variance=1.0)
+            m = efgpnd.EFGPND(x, y, k, sigmasq=0.05, eps=1e-4, nufft_eps=1e-9, opts={"cg_tolerance": 1e-10},
+                              estimate_params=False)
+            mean, _ = m.predict(x[:100], return_variance=False)
+            fits.append((m._beta.clone(), int(m.last_fit_stats["mean_cg_iters"]), mean.clone()))
+        assert torch.equal(fits[0][0], fits[1][0]) and fits[0][1] == fits[1][1] and torch.equal(fits[0][2], fits[1][2])
+    finally:
+        _lib.set_deterministic(False)

@@ -202,7 +202,7 @@ def test_cg_hermitian_path_matches_general_path(d, m, rows, dt):
         minv = 1.0 / (N * ws * ws + s2)
         xg, itg = toep.plan.cg(b, None, mode, ws, s2, tol, minv=minv, x0_zero=True, hermitian=False)
         xh, ith = toep.plan.cg(b, None, mode, ws, s2, tol, minv=minv, x0_zero=True, hermitian=True)
-        slack = 1 if dt == torch.float64 else max(1, itg // 50)      # fp32 rounding moves long solves by a few iterations
+        slack = 1 if dt == torch.float64 else max(1, itg // 25)      # fp32 rounding moves long solves by a few iterations
         assert abs(itg - ith) <= slack
         # fp32: two rounding-different trajectories agree to ~eps32 x condition number (~1e4 here)
         assert rel(xh, xg) < (1e-8 if dt == torch.float64 else 1e-2)

@@ -28,9 +28,15 @@ def test_streamed_probes_equal_explicit_probes(d, dt, eps, n):
     N = 60_000
     x = (torch.rand(N, d, dtype=torch.float64, device="cuda", generator=g) * 2 - 1).to(dt)
     plan = ops.NufftPlan(x, 0.37)
+    carry = d != 1                                   # both counters: original index (float64 only) and slot
+    plan.carry_index(carry)
     shape = (n,) * d
     seed, t0, nb = 123456789012345, 125, 7          # crosses a 128-probe block boundary; groups of 2/1 and 4/2/1
     z, sid = plan.probes_export(seed, t0, nb, shape, eps)
+    if carry and dt == torch.float64:
+        # counter = original index: the probes are the same for ANY sorted set of these points (other spacing, new sort)
+        z_other, _ = ops.NufftPlan(x, 0.29).carry_index(True).probes_export(seed, t0, nb, shape, eps)
+        assert torch.equal(z, z_other)
     assert z.shape == (nb, N) and bool(((z == 1) | (z == -1)).all())
     assert abs(float(z.double().mean())) < 0.02                       # unbiased signs
     assert float((z[0] * z[1]).double().mean().abs()) < 0.02          # different probes are uncorrelated
@@ -56,6 +62,8 @@ def test_streamed_probes_equal_explicit_probes(d, dt, eps, n):
 
 
 def test_probe_transforms_refuse_a_changed_sort():
+    """Slot counters (no original index in the records) tie the probes to ONE sorted set: a re-sort in between is an
+    error, not a silently different estimator."""
     from efgp_b200 import ops
     from efgp_b200._lib import EfgpError
     g = torch.Generator(device="cuda").manual_seed(2)
@@ -82,15 +90,18 @@ def test_gradient_with_streamed_probes_equals_stored_probes(d, kname):
     for mode in (True, "export"):
         k = SquaredExponential(dimension=d, init_lengthscale=0.4, init_variance=1.0) if kname == "se" else \
             Matern(dimension=d, init_lengthscale=0.8, init_variance=1.0, nu=2.5)
-        m = efgpnd.EFGPND(x, y, k, sigmasq=0.1, eps=1e-3, opts={"device_probes": mode}, estimate_params=False)
+        # sigma^2 = 1: a well-conditioned system, so that CG converges long before its 2 M iteration cap and the
+        # comparison is about the probes, not about where two rounding-different CG runs stopped
+        m = efgpnd.EFGPND(x, y, k, sigmasq=1.0, eps=1e-3, opts={"device_probes": mode}, estimate_params=False)
         torch.manual_seed(77)
-        out[mode] = m.compute_gradients(trace_samples=6, cg_tol=1e-10, nufft_eps=1e-10, apply_gradients=False).double().cpu()
+        out[mode] = m.compute_gradients(trace_samples=6, cg_tol=1e-9, nufft_eps=1e-10, apply_gradients=False).double().cpu()
         assert m.last_gradient_stats["trace_num_rhs"] == 12
-    assert float((out[True] - out["export"]).norm() / out["export"].norm()) < 1e-7
+        assert m.last_gradient_stats["trace_cg_iters"] < 2 * m.last_gradient_stats["feature_count"]
+    assert float((out[True] - out["export"]).norm() / out["export"].norm()) < 1e-6
     # and a different seed gives a different Monte-Carlo estimate (the probes really enter)
     k = SquaredExponential(dimension=d, init_lengthscale=0.4, init_variance=1.0) if kname == "se" else \
         Matern(dimension=d, init_lengthscale=0.8, init_variance=1.0, nu=2.5)
-    m = efgpnd.EFGPND(x, y, k, sigmasq=0.1, eps=1e-3, estimate_params=False)
+    m = efgpnd.EFGPND(x, y, k, sigmasq=1.0, eps=1e-3, estimate_params=False)
     torch.manual_seed(78)
-    other = m.compute_gradients(trace_samples=6, cg_tol=1e-10, nufft_eps=1e-10, apply_gradients=False).double().cpu()
+    other = m.compute_gradients(trace_samples=6, cg_tol=1e-9, nufft_eps=1e-10, apply_gradients=False).double().cpu()
     assert float((other - out[True]).norm()) > 0
