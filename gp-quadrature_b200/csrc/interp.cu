@@ -10,6 +10,7 @@
 #include "nufft.cuh"
 #include "stream_ring.cuh"
 #include "philox.cuh"
+#include <cstdlib>
 
 namespace efgp {
 
@@ -153,6 +154,116 @@ interp2d_kernel(const T* __restrict__ rec, int P,
     out[pn] = acc;
   }
   cp_async_wait<0>();
+}
+
+// ------------------------------------------------------------------ 2-D, record slabs staged by bulk async copies (TMA)
+// A/B variant of interp2d_kernel (EFGP_INTERP_TMA=1): instead of 256 per-thread 16-byte cp.async per step, ONE elected
+// thread issues a 1-D bulk tensor copy (cp.async.bulk.shared::cluster.global, the TMA engine: SASS UBLKCP) of the CTA's
+// next kTmaSteps * 256 records = a contiguous 16 KB slab of the tile-transposed layout, completion signalled through an
+// mbarrier (complete_tx::bytes); the threads wait on the barrier's phase and read their record from shared memory.
+// The slab ring is refilled CTA-wide, so the steps of a slab are followed by one __syncthreads (the per-thread ring of
+// interp2d_kernel needs none).  Measured against the cp.async ring in DESIGN.md section 4.
+constexpr int kTmaStages = 4;
+constexpr int kTmaSteps = 2;       // point steps per slab: 2 * 256 records * 32 bytes = 16 KB (f64)
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+  unsigned ok;
+  do {
+    asm volatile(
+        "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+        : "=r"(ok)
+        : "r"(a), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void bulk_copy_g2s(void* smem_dst, const void* gsrc, unsigned bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   (unsigned)__cvta_generic_to_shared(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar))
+               : "memory");
+}
+
+template <typename T, int W>
+__global__ void __launch_bounds__(kTileThreads, (W <= 5 ? 2 : 1))
+interp2d_tma_kernel(const T* __restrict__ rec, int P, int nf0, int nf1, const T* __restrict__ grid, T* __restrict__ out,
+                    const __grid_constant__ ESDev<T> es) {
+  extern __shared__ __align__(128) unsigned char tma_smem[];
+  T* slab = reinterpret_cast<T*>(tma_smem);                          // [stages][steps][256][4]
+  __shared__ __align__(8) uint64_t full[kTmaStages];
+  const int t = threadIdx.x;
+  const int64_t tile0 = (int64_t)blockIdx.x * kTileThreads * P;      // first slot of this CTA's tile
+  const int ngroups = (P + kTmaSteps - 1) / kTmaSteps;
+  constexpr unsigned kStepBytes = kTileThreads * 4 * sizeof(T);
+  if (t == 0) {
+#pragma unroll
+    for (int s = 0; s < kTmaStages; ++s) mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  auto issue = [&](int g) {           // thread 0 only
+    const int s = g % kTmaStages;
+    const int steps = (P - g * kTmaSteps) < kTmaSteps ? (P - g * kTmaSteps) : kTmaSteps;
+    const unsigned bytes = (unsigned)steps * kStepBytes;
+    mbar_expect_tx(&full[s], bytes);
+    bulk_copy_g2s(slab + (size_t)s * kTmaSteps * kTileThreads * 4, rec + (tile0 + (int64_t)g * kTmaSteps * kTileThreads) * 4,
+                  bytes, &full[s]);
+  };
+  if (t == 0)
+    for (int g = 0; g < kTmaStages && g < ngroups; ++g) issue(g);
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  T g_[W][W];
+  int cur0 = -1, cur1 = -1;
+  for (int g = 0; g < ngroups; ++g) {
+    const int s = g % kTmaStages;
+    mbar_wait(&full[s], (unsigned)((g / kTmaStages) & 1));
+#pragma unroll
+    for (int kk = 0; kk < kTmaSteps; ++kk) {
+      const int j = g * kTmaSteps + kk;
+      if (j >= P) break;                                   // uniform over the CTA
+      const T* r = slab + (((size_t)s * kTmaSteps + kk) * kTileThreads + t) * 4;
+      const T X0 = r[0], X1 = r[1];
+      if (!(X0 < T(0))) {                                  // (pad slots of the last tile: no early exit, the CTA syncs)
+        const int64_t pn = tile0 + (int64_t)j * kTileThreads + t;
+        const int c0 = (int)X0, c1 = (int)X1;
+        if (c0 != cur0 || c1 != cur1) {
+          int cols[W];
+#pragma unroll
+          for (int jj = 0; jj < W; ++jj) cols[jj] = wrap_i(c1 - OFF + jj, nf1);
+#pragma unroll
+          for (int i = 0; i < W; ++i) {
+            const T* row = grid + (int64_t)wrap_i(c0 - OFF + i, nf0) * nf1;
+#pragma unroll
+            for (int jj = 0; jj < W; ++jj) g_[i][jj] = __ldg(row + cols[jj]);
+          }
+          cur0 = c0;
+          cur1 = c1;
+        }
+        T k0[W], k1[W];
+        es_eval_i<T, W>(es, T(2) * (X0 - (T)c0) - T(1), k0);
+        es_eval_i<T, W>(es, T(2) * (X1 - (T)c1) - T(1), k1);
+        T acc = 0;
+#pragma unroll
+        for (int i = 0; i < W; ++i) {
+          T rr = 0;
+#pragma unroll
+          for (int jj = 0; jj < W; ++jj) rr = fma(g_[i][jj], k1[jj], rr);
+          acc = fma(rr, k0[i], acc);
+        }
+        out[pn] = acc;
+      }
+    }
+    __syncthreads();                                       // every thread is done with slab s
+    if (t == 0 && g + kTmaStages < ngroups) issue(g + kTmaStages);
+  }
 }
 
 // ------------------------------------------------------------------ 3-D, shared-memory staged grid tiles
@@ -515,8 +626,15 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* grid, T
     interp1d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], grid, out, ostride, es);
   } else if (sp.dim == 2) {
     if constexpr (W <= kRegMaxW) {
-      interp2d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
-                                                         out, ostride, es);
+      static const bool use_tma = getenv("EFGP_INTERP_TMA") != nullptr && atoi(getenv("EFGP_INTERP_TMA")) != 0;
+      if (use_tma) {
+        const size_t smem = (size_t)kTmaStages * kTmaSteps * kTileThreads * 4 * sizeof(T);
+        EFGP_CUDA(cudaFuncSetAttribute(interp2d_tma_kernel<T, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        interp2d_tma_kernel<T, W><<<nt, kTileThreads, smem, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid, out, es);
+      } else {
+        interp2d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
+                                                           out, ostride, es);
+      }
     } else {
       interp_direct_kernel<T, W, 2><<<div_up(sp.npos, 256), 256, 0, st>>>(
           rec, sp.npos, (int)sp.nf[0], (int)sp.nf[1], 1, grid, out, ostride, es);

@@ -65,7 +65,7 @@ struct SortGeom {
   uint32_t g;       // cells per level-2 bin (1 = exact cell sort)
   int nb1;          // level-1 buckets (<= kMaxBuckets)
   int nbins2;       // level-2 bins per bucket (<= kMaxBins2)
-  int P;            // points per thread of the tile-transposed layout (any value in 1..128)
+  int P;            // points per thread of the tile-transposed layout (any value in 1..kMaxP)
 };
 
 constexpr int kMaxBuckets = 256;
@@ -657,7 +657,7 @@ static int pick_points_per_thread(int64_t N) {
   // The 2-D spread / interp kernels run one CTA per tile of 256 * P points, two CTAs per SM for the narrow kernels
   // and one for the wide ones: the tile count is made a whole number of waves of 2 * (SM count) CTAs (round 1 rounded
   // P down to a power of two: 763 CTAs = 5.15 waves of 148 paid for 6 at the 8-GPU shard size), with the longest
-  // register runs (P <= 128) the wave count allows.
+  // register runs (P <= kMaxP) the wave count allows.  EFGP_MAX_P overrides the cap (A/B measurements).
   static int sms = 0;
   if (!sms) {
     int dev = 0;
@@ -665,13 +665,18 @@ static int pick_points_per_thread(int64_t N) {
         sms <= 0)
       sms = 148;
   }
+  static const int kMaxP = [] {
+    const char* e = std::getenv("EFGP_MAX_P");
+    int v = e ? std::atoi(e) : 0;
+    return v >= 1 && v <= 4096 ? v : 512;
+  }();
   const int64_t wave = 2 * (int64_t)sms;
-  const int64_t per_wave = wave * kTileThreads * 128;
+  const int64_t per_wave = wave * kTileThreads * kMaxP;
   const int64_t k = std::max<int64_t>(1, (N + per_wave - 1) / per_wave);
   const int64_t tiles = k * wave;
   int64_t P = (N + tiles * kTileThreads - 1) / (tiles * kTileThreads);
   if (P < 1) P = 1;
-  if (P > 128) P = 128;
+  if (P > kMaxP) P = kMaxP;
   return (int)P;
 }
 

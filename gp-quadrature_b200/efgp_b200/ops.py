@@ -493,7 +493,18 @@ def ensure_comm(group):
     dist.broadcast(t, src=src, group=group)
     raw = bytes(t.cpu().numpy().tobytes())
     idbuf2 = ctypes.create_string_buffer(raw, 128)
-    check(_lib.lib().efgp_comm_init(int(rank), int(world), ctypes.cast(idbuf2, ctypes.c_void_p)))
+    # NCCL prints its version banner to STDOUT at the first communicator of a process when NCCL_DEBUG is set; callers
+    # (bench.py) own stdout, so the banner is sent to stderr for the duration of the call
+    import os
+    import sys
+    sys.stdout.flush()
+    saved = os.dup(1)
+    try:
+        os.dup2(2, 1)
+        check(_lib.lib().efgp_comm_init(int(rank), int(world), ctypes.cast(idbuf2, ctypes.c_void_p)))
+    finally:
+        os.dup2(saved, 1)
+        os.close(saved)
     _COMM_KEY = key
 
 

@@ -35,7 +35,7 @@ def _worker(rank, world, port, out_dir):
     x = (torch.rand(N, d, dtype=torch.float64) * 2 - 1).cuda()
     y = (torch.sin(3 * x[:, 0]) * torch.cos(2 * x[:, 1]) + 0.1 * torch.randn(N, dtype=torch.float64, device="cuda"))
     kern = SquaredExponential(dimension=d, init_lengthscale=0.3, init_variance=1.0)
-    m = efgpnd.EFGPND(x, y, kern, sigmasq=0.05, eps=1e-4, opts={"shard_probes": True}, estimate_params=False)
+    m = efgpnd.EFGPND(x, y, kern, sigmasq=1.0, eps=1e-4, opts={"shard_probes": True}, estimate_params=False)
     torch.manual_seed(1234)
     g = m.compute_gradients(trace_samples=7, cg_tol=1e-9, nufft_eps=1e-9, apply_gradients=False)
     torch.save({"grad": g.detach().cpu(), "stats": {k: v for k, v in m.last_gradient_stats.items()}},
