@@ -871,7 +871,9 @@ def main():
         ach = algorithmic_bytes(top, v["units"]) / v["ms"] / 1e6
         # DRAM bytes per launch from the committed `ncu --set full` capture of this kernel (same N only)
         traffic = None
-        tpath = os.path.join(ROOT, "profiles", "ncu_r01_traffic.json")
+        tpath = os.path.join(ROOT, "profiles", "ncu_r02_traffic.json")
+        if not os.path.exists(tpath):
+            tpath = os.path.join(ROOT, "profiles", "ncu_r01_traffic.json")
         if os.path.exists(tpath):
             ent = json.load(open(tpath)).get(top)
             if ent and ent.get("npts") == v["units"] // max(1, v["launches"]):

@@ -809,16 +809,19 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   const bool sym = hermitian && odd && !direct && !sym_off;
   const T* vreal = sym ? (const T*)toeplitz_real_spectrum(t, st) : nullptr;
 
+  // single Hermitian right-hand side on a small odd 2-D block: direct-convolution solve (cg_small.cu)
+  static const bool conv_off = std::getenv("EFGP_CG_CONV") && std::atoi(std::getenv("EFGP_CG_CONV")) == 0;
+  const bool try_conv = direct && !conv_off && hermitian && odd && B == 1 && M <= 6400 && t.v_raw != nullptr && w != nullptr;
   // Ap = A x0  (generic apply writes through P/Q as well); skipped for a cold start
   const dim3 gsym(div_up((M + 1) / 2, 256), B);
-  if (sym && !x0_zero) cg_symmetrize_kernel<T><<<gsym, 256, 0, st>>>(x, M);
+  if ((sym || try_conv) && !x0_zero) cg_symmetrize_kernel<T><<<gsym, 256, 0, st>>>(x, M);
   if (!x0_zero) toeplitz_apply(t, x, B, ws, sigmasq, mode, Ap, st);
   dim3 grid(s.NC, B), gf(div_up(t.Ftot, 256), B);
   {
     ScopedStage stg_init("cg.init", st, 2);
     cg_init_kernel<T><<<grid, 256, 0, st>>>(b, x0_zero ? (const C*)nullptr : (const C*)Ap, minv, r, p, M, s);
     cg_init_scal_kernel<<<B, 256, 0, st>>>(s);
-    if (sym) {
+    if (sym || try_conv) {
       cg_symmetrize_kernel<T><<<gsym, 256, 0, st>>>(r, M);
       cg_symmetrize_kernel<T><<<gsym, 256, 0, st>>>(p, M);
     }
@@ -839,6 +842,20 @@ static void solve_group(Toeplitz& t, const T* ws, double sigmasq, int mode, cons
   int check = my_hint > 0 ? std::min(my_hint, 64) : 4;
   bool first = true;
   ScopedStage stg("cg.iterations", st, 0);
+  if (try_conv && cg_conv_launch<T>(t, w, minv, x, r, p, c1, c2, tol, early, max_iter, s.rz + s.B, s.denom, s.counters,
+                                    s.conv_iter, st)) {
+    stg.add_launches(1);
+    if (async_counters) {
+      EFGP_CUDA(cudaMemcpyAsync(async_counters, s.counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+      all_conv = -1;
+      return;
+    }
+    EFGP_CUDA(cudaMemcpyAsync(h_counters, s.counters, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    EFGP_CUDA(cudaStreamSynchronize(st));
+    all_conv = early && h_counters[0] <= 0;
+    jmax = h_counters[1];
+    return;
+  }
   if (direct) {
     static const bool persist_off = std::getenv("EFGP_CG_PERSIST") && std::atoi(std::getenv("EFGP_CG_PERSIST")) == 0;
     static int sms = 0, coop = 0;

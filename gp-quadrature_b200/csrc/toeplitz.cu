@@ -206,6 +206,7 @@ void toeplitz_create(Toeplitz& t, const void* v, int dim, const int64_t* Ls, int
                      cudaStream_t st) {
   EFGP_CHECK(dim >= 1 && dim <= kMaxDim, "dim must be 1..3");
   t.dim = dim;
+  t.v_raw = v;
   t.dtype = dtype;
   t.M = 1;
   t.Ftot = 1;

@@ -11,6 +11,7 @@ struct Toeplitz {
   int64_t n[kMaxDim] = {1, 1, 1};   // block extents (L+1)/2
   int64_t F[kMaxDim] = {1, 1, 1};   // FFT extents
   int64_t M = 1, Ftot = 1;
+  const void* v_raw = nullptr;      // the generator itself (borrowed: the caller keeps it alive with the handle)
   void* vhat = nullptr;             // FFT of the zero-padded generator, pre-scaled by 1/Ftot
   void* vhat_real = nullptr;        // real spectrum of the CENTRED generator (Hermitian v), built on first use
   DevBuf P, Q;                      // padded input (zeros persist), spectrum / output
@@ -38,6 +39,12 @@ void cg_solve(Toeplitz& t, const void* ws, double sigmasq, int mode, const void*
 // there; otherwise the call is synchronous and fills the same two ints itself.
 // V[f] = (1 / Ftot) sum_j v[j] exp(-2 pi i f.j / F) over the centred generator index j: real when v[-j] = conj v[j].
 const void* toeplitz_real_spectrum(Toeplitz& t, cudaStream_t st);
+// cg_small.cu: the single-RHS Hermitian solve of a small 2-D block as one cooperative kernel with one barrier per
+// iteration (direct block-Toeplitz convolution); false = geometry does not qualify
+template <typename T>
+bool cg_conv_launch(Toeplitz& t, const T* ws, const T* minv, void* x, const void* r0, const void* p0, T c1, T c2,
+                    double tol, int early, int max_iter, const double* rz0, const double* denom, int* counters,
+                    int* conv_iter, cudaStream_t st);
 // lanczos.cu: `steps` lockstep Lanczos steps from the normalised start block q0 (overwritten); alphas / betas are
 // (batch, steps) doubles on the device.  Enqueues only (no synchronisation).
 void lanczos_tridiag(Toeplitz& t, const void* ws, double sigmasq, int mode, void* q0, int batch, int steps,

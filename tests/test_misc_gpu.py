@@ -165,3 +165,50 @@ def test_deterministic_mode_is_bit_reproducible(d):
         assert torch.equal(fits[0][0], fits[1][0]) and fits[0][1] == fits[1][1] and torch.equal(fits[0][2], fits[1][2])
     finally:
         _lib.set_deterministic(False)
+
+
+@pytest.mark.parametrize("n,dt,tol", [(21, torch.float64, 1e-9), (71, torch.float64, 1e-9), (35, torch.float32, 2e-3),
+                                      (9, torch.float64, 1e-9)])
+def test_convolution_cg_matches_fft_cg(n, dt, tol):
+    """cg_small.cu (one cooperative kernel, one grid barrier per iteration, direct block-Toeplitz convolution on the
+    modes k <= mid) against the cuFFT real-FFT path: the same Hermitian-symmetric system solved alone (convolution
+    kernel) and as 5 identical rows (batched cuFFT path), cold and warm start, same iteration counts."""
+    import efgpnd
+    from efgp_b200 import ops
+    cdt = torch.complex128 if dt == torch.float64 else torch.complex64
+    f64 = dt == torch.float64
+    g = torch.Generator(device="cuda").manual_seed(100 + n)
+    N = 20000
+    x = (torch.rand(N, 2, dtype=torch.float64, device="cuda", generator=g) * 2 - 1).to(dt)
+    m = (n - 1) // 2
+    h = 0.45
+    v = efgpnd.compute_convolution_vector_vectorized_dD(m, x, h)
+    toep = efgpnd.ToeplitzND(v, force_pow2=False)
+    M = n * n
+    grid = torch.stack(torch.meshgrid(*([torch.arange(-m, m + 1, device="cuda", dtype=dt)] * 2), indexing="ij"), -1)
+    ws = (0.05 * torch.exp(-0.003 * (grid ** 2).sum(-1))).reshape(-1)             # even, real, positive
+    c = torch.randn(N, dtype=dt, device="cuda", generator=g)
+    b = efgpnd.NUFFT(x, torch.zeros(2, dtype=dt, device="cuda"), h, 1e-9 if f64 else 1e-5).type1(c, (n, n)).reshape(M) * ws
+    s2 = 0.3
+    minv = 1.0 / (N * ws * ws + s2)
+    cg_tol = 1e-10 if f64 else 1e-5
+    x1, it1 = toep.plan.cg(b, None, ops.MODE_A_MEAN, ws, s2, cg_tol, minv=minv, x0_zero=True, hermitian=True, batched=False)
+    b5 = b.repeat(5, 1)
+    x5, it5 = toep.plan.cg(b5, None, ops.MODE_A_MEAN, ws, s2, cg_tol, minv=minv, x0_zero=True, hermitian=True, batched=False)
+    assert it1 < 2 * M
+    assert abs(it1 - it5) <= (1 if f64 else max(1, it5 // 25))
+    assert float(torch.linalg.norm(x5[0] - x1) / torch.linalg.norm(x1)) < tol
+    res = toep.plan.apply(x1, ops.MODE_A_MEAN, ws, s2) - b
+    assert float(torch.linalg.norm(res) / torch.linalg.norm(b)) < 50 * cg_tol
+    # Hermitian symmetry of the solution, exactly (the mirrored half is written as the conjugate)
+    flip = torch.flip(x1.reshape(n, n), dims=(0, 1)).reshape(M)
+    assert torch.equal(flip.conj(), x1)
+    # warm start from a nearby symmetric point
+    xw, itw = toep.plan.cg(b, x1 * 0.9, ops.MODE_A_MEAN, ws, s2, cg_tol, minv=minv, hermitian=True, batched=False)
+    xw5, itw5 = toep.plan.cg(b5, x5 * 0.9, ops.MODE_A_MEAN, ws, s2, cg_tol, minv=minv, hermitian=True, batched=False)
+    assert abs(itw - itw5) <= (1 if f64 else max(1, itw5 // 25))
+    assert float(torch.linalg.norm(xw - x1) / torch.linalg.norm(x1)) < 20 * tol      # two trajectories stopped at 1e-10
+    # iteration cap: no convergence reported
+    xc, itc = toep.plan.cg(b, None, ops.MODE_A_MEAN, ws, s2, cg_tol, max_iter=3, minv=minv, x0_zero=True, hermitian=True,
+                           batched=False)
+    assert itc == 3
