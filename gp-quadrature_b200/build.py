@@ -11,7 +11,7 @@ OUT_DIR = os.path.join(HERE, "efgp_b200")
 LIB = os.path.join(OUT_DIR, "libefgp_b200.so")
 OBJ_DIR = os.path.join(HERE, "build")
 
-SOURCES = ["es_kernel.cpp", "pool.cpp", "timing.cpp", "points.cu", "spread.cu", "interp.cu", "nufft.cu", "toeplitz.cu", "cg.cu", "cg_small.cu", "lanczos.cu", "variance.cu", "fit.cu", "comm.cpp", "capi.cu"]
+SOURCES = ["es_kernel.cpp", "pool.cpp", "timing.cpp", "points.cu", "spread.cu", "interp.cu", "nufft.cu", "toeplitz.cu", "cg.cu", "cg_small.cu", "lanczos.cu", "variance.cu", "fit.cu", "comm.cpp", "noalloc.cu", "capi.cu"]
 HEADERS = ["common.cuh", "nufft.cuh", "toeplitz.cuh", "stream_ring.cuh", "fit.cuh", os.path.join("..", "..", "include", "efgp_b200.h")]
 
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

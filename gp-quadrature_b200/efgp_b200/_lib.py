@@ -66,6 +66,7 @@ _SIGNATURES = {
     "efgp_comm_world": (ctypes.c_int, []),
     "efgp_allreduce": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
     "efgp_bbox_async": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp]),
+    "efgp_bbox_static": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp, vp]),
     "efgp_xcorr_mean": (ctypes.c_int, [vp, vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp]),
     "efgp_variance_rows": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_double, vp, ctypes.c_int,
                                           vp, vp]),

@@ -453,6 +453,27 @@ def bbox_async(x, sharded=False):
     return buf[:2 * d], ev
 
 
+BBOX_STATIC_MAX_POINTS = 134217728      # EFGP_BBOX_STATIC_MAX_POINTS of include/efgp_b200.h
+
+
+def bbox_static(x, out):
+    """efgp_bbox_static: [max x_a .., -min x_a ..] of x (N, d) into `out` (>= 2 d float64 on x's device, supplied by the
+    caller) with the partials in the library's static device array: the call allocates nothing (see csrc/noalloc.cu;
+    calls that overlap on the GPU race on that array).  x must already be contiguous -- no copy is made here."""
+    _require_cuda(x, "x")
+    _require_cuda(out, "out")
+    if x.ndim == 1:
+        x = x[:, None]
+    if not x.is_contiguous():
+        raise _lib.EfgpError("bbox_static: x must be contiguous (this entry point makes no copies)")
+    N, d = x.shape
+    if out.dtype != torch.float64 or out.numel() < 2 * d or not out.is_contiguous() or out.device != x.device:
+        raise _lib.EfgpError("bbox_static: out must be a contiguous float64 tensor of >= 2 d entries on x's device")
+    with _on(x.device):
+        check(_lib.lib().efgp_bbox_static(_ptr(x), int(N), int(d), _dtype_code(x.dtype), _ptr(out), _stream(x.device)))
+    return out
+
+
 def fit(plan, y, args, ws, vr, minv, beta, lazy):
     """efgp_fit on the points of `plan` (a NufftPlan): fills ws, vr = [F^*1 ; ws F^*y], minv, beta (in/out) and returns
     the library's Toeplitz handle.  `lazy` is the LazyIters that receives the iteration counters."""

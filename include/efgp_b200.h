@@ -165,6 +165,18 @@ int efgp_allreduce(void* buf, int64_t count, int dtype, int op, void* stream);
  * L = max_a (max - min) of efgpnd.py:751.  The host derives (h, mtot) from L (get_xis, utils/kernels.py:72-143). */
 int efgp_bbox_async(const void* x, int64_t npts, int dim, int dtype, int sharded, double* ext_pinned, void* stream);
 
+/* efgp_bbox_static: NO COUNTERPART IN THE REFERENCE -- added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same
+ * reduction as efgp_bbox_async ([max x_0.., -min x_0..], bit-identical: max/min are exact) with its per-CTA partials in
+ * a file-scope static __device__ array (csrc/noalloc.cu; 786,688 bytes held by every GPU that loads the library until
+ * exit) instead of the scratch pool: it enqueues one cudaMemsetAsync (the finishing-CTA ticket must start at zero) and
+ * one kernel, and calls no cudaMalloc, cudaFree or allocating library routine.  ext_dev: 2 dim doubles of DEVICE
+ * memory supplied by the caller (no communicator reduction, no host copy).  npts > EFGP_BBOX_STATIC_MAX_POINTS (one
+ * 8192-point tile per slot of the array) is refused with error code 1 and a message naming the limit.  Every call
+ * shares the one array: calls that OVERLAP on the GPU (two streams, two graphs replayed at once) race -- serialise them. */
+#define EFGP_BBOX_STATIC_MAX_POINTS 134217728LL
+int efgp_bbox_static(const void* x, int64_t npts, int dim, int dtype, double* ext_dev, void* stream);
+
 typedef struct efgp_fit_args {
   int family;            /* spectral density on xi = h * (k - (mtot-1)/2):  0: S = c exp(-a |xi|^2)  (squared_exponential.py:64-91) */
   double c, a, b, p;     /*                                                 1: S = c (b + 4 pi^2 |xi|^2)^(-p)  (matern.py:100-122) */
