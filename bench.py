@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=float, default=1e7, help="points in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-f32", action="store_true", help="skip the extra float32 figure")
     ap.add_argument("--no-parity", action="store_true", help="skip the full-size oracle comparison after the timing")
     ap.add_argument("--workload", default="config3", choices=["config3", "config4"])
     ap.add_argument("--probes", type=int, default=64, help="config4: Hutchinson probes per gradient step")
@@ -360,14 +361,20 @@ def algorithmic_bytes(stage, n, d=2, word=8):
 
 
 def algorithmic_flops(stage, n, d=2):
-    """FP64 flops (FMA = 2) the spreading / interpolation kernels need for n points: per dimension the even/odd
-    Horner evaluation of the W piecewise polynomials of degree W + 2 (spread.cu es_eval), then W^d FMAs."""
+    """FP64 flops (FMA = 2) the spreading / interpolation kernels need for n points.  Register-footprint kernels
+    (spread.cu es_eval + W^d FMAs): per dimension the even/odd Horner evaluation of the W piecewise polynomials of
+    degree W - 1 (W for W <= 4: common.cuh es_degree), then W^d FMAs.  The 2-D fp64 spreads of width >= 7 on dense
+    point sets (every bench workload) run the moment kernel (spread2d_moment_kernel): 2 (NC - 1) multiplications for the
+    powers of the two in-cell offsets and NC^2 FMAs per point, NC = degree + 1."""
     import re
-    m = re.match(r"(spread|interp)\dd_w(\d+)_", stage)
+    m = re.match(r"(spread|interp)(\d)d_w(\d+)_(f64|f32)(.*)", stage)
     if not m:
         return None
-    W = int(m.group(2))
-    deg = W + 2
+    kind, W, prec, rest = m.group(1), int(m.group(3)), m.group(4), m.group(5)
+    deg = W if W <= 4 else W - 1
+    if kind == "spread" and d == 2 and prec == "f64" and W >= 7 and "probes" not in rest:
+        nc = deg + 1
+        return n * (2 * (nc - 1) + 2 * nc * nc + 4 + (0 if rest == "_ones" else nc))
     ne, no = deg // 2 + 1, (deg + 1) // 2
     horner = (W // 2) * (2 * (ne + no - 2) + 3) + (2 * (ne - 1) if W % 2 else 0) + 4
     return n * (d * horner + 2 * W ** d + W)
@@ -750,6 +757,36 @@ def main():
                           "read-back; the spacing h changes with the lengthscale, so the cell sort is redone"}
     del model_r
 
+    # ---- the same cold step in float32 (an extra figure, not the headline: BASELINE.json's metric is fp64).  Inputs,
+    # records, grids and CG vectors are float32 (half the sort / record traffic); the result is compared with the fp64
+    # posterior mean of the timed configuration on the same points.
+    f32_info = None
+    if world == 1 and not args.no_f32:
+        x32, y32 = x.float(), y.float()
+        for _ in range(3):
+            m32 = solve(x32, y32)
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            m32 = solve(x32, y32)
+        e1.record()
+        barrier()
+        ms32 = e0.elapsed_time(e1) / args.steps
+        _lib.timing_enable(True)
+        barrier()
+        for _ in range(args.steps):
+            m32 = solve(x32, y32)
+        barrier()
+        st32 = {k: round(v["ms"] / args.steps, 4) for k, v in _lib.timing_report().items()}
+        _lib.timing_enable(False)
+        rel32 = float((torch.linalg.norm(m32.double() - mean.double()) / torch.linalg.norm(mean.double())).item())
+        f32_info = {"ms_per_step": ms32, "value": n_total / ms32 / 1e3, "unit": UNIT, "dtype": "f32",
+                    "mean_rel_vs_f64": rel32, "mean_cg_iters": stats.get("mean_cg_iters"), "stages_ms": st32,
+                    "what": "same cold step with float32 points, targets and arithmetic (nufft_eps, cg tolerance as "
+                            "timed); mean_rel_vs_f64 = |mean32 - mean64| / |mean64| over all N points"}
+        del x32, y32, m32
+        mean = solve(x, y)             # leave the fp64 state (stats, last model) behind for what follows
+
     # ---- end to end: pinned host buffers -> device -> solve -> result back on the host, every step
     e2e = None
     if not args.no_e2e:
@@ -906,7 +943,7 @@ def main():
             "config": workload_config(args, world, stats.get("mtot")),
             "numa_cpulist": numa, "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
             "stages": per_stage, "mean_cg_iters": stats.get("mean_cg_iters"), "result_rms": check,
-            "beta_fingerprint": beta_fingerprint, "parity": parity, "refit": refit_info,
+            "beta_fingerprint": beta_fingerprint, "parity": parity, "refit": refit_info, "f32": f32_info,
             "ms_per_step_with_stage_events": ms_instrumented}
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args)

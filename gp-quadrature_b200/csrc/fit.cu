@@ -64,12 +64,15 @@ bbox_partial_kernel(const T* __restrict__ x, int64_t N, double* __restrict__ par
   }
 }
 
+// one WARP per output [hi_0..hi_{d-1}, -lo_0..-lo_{d-1}]: lanes stride over the CTA partials (a single thread per
+// output walked 592 dependent loads: 44 us in the ncu launch list of round 2, replicated on every rank)
 __global__ void bbox_final_kernel(const double* __restrict__ part, int blocks, int dim, double* __restrict__ ext) {
-  const int c = threadIdx.x;      // one thread per output [hi_0..hi_{d-1}, -lo_0..-lo_{d-1}]
+  const int c = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (c >= 2 * dim) return;
   double m = -1.0e308;
-  for (int b = 0; b < blocks; ++b) m = fmax(m, part[(int64_t)b * 2 * dim + c]);
-  ext[c] = m;
+  for (int b = lane; b < blocks; b += 32) m = fmax(m, part[(int64_t)b * 2 * dim + c]);
+  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if (lane == 0) ext[c] = m;
 }
 
 void bbox_async(const void* x, int64_t N, int dim, int dtype, int sharded, double* ext_pinned, cudaStream_t st) {
@@ -87,7 +90,7 @@ void bbox_async(const void* x, int64_t N, int dim, int dtype, int sharded, doubl
       if (dim == 1) EFGP_BOX(double, 1); else if (dim == 2) EFGP_BOX(double, 2); else EFGP_BOX(double, 3);
     }
 #undef EFGP_BOX
-    bbox_final_kernel<<<1, 32, 0, st>>>(part, blocks, dim, ext);
+    bbox_final_kernel<<<1, 32 * 2 * dim, 0, st>>>(part, blocks, dim, ext);
     EFGP_CUDA(cudaGetLastError());
   }
   if (sharded) comm_allreduce(ext, 2 * dim, 1, 1, st);

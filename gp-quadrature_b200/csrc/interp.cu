@@ -97,19 +97,26 @@ interp1d_kernel(const T* __restrict__ rec, int P, int nf0,
 
 // Narrow kernels (W <= 5) keep their W x W patch in <= 128 registers, so two CTAs share an SM; the point
 // records stream through a per-thread cp.async ring (stream_ring.cuh) deep enough to cover DRAM latency.
-template <typename T, int W>
+//
+// SCAT: the result of a point goes straight to its level-1 (bucket-order) position, which the record carries in the
+// low 32 bits of word 2 (points.cu bin_scatter_kernel), instead of to its slot, and unpermute_output only runs its
+// second level.  The idea was to save the slot -> bucket-order pass (0.48 ms at N = 1e8); measured, the scattered
+// 8-byte stores are 6x slower than that pass's gathers (see launch_interp), so this is an A/B switch, not the default.
+template <typename T, int W, bool SCAT>
 __global__ void __launch_bounds__(kTileThreads, (W <= 5 ? 2 : 1))
 interp2d_kernel(const T* __restrict__ rec, int P,
                 int nf0, int nf1, const T* __restrict__ grid, T* __restrict__ out, int64_t ostride,
                 const __grid_constant__ ESDev<T> es) {
   constexpr int S = kRingStages;
   __shared__ __align__(16) T ring[S][kTileThreads][2];      // (X0, X1) of each thread's next points
+  __shared__ uint32_t bring[SCAT ? S : 1][kTileThreads];    // level-1 position of the point
   const int t = threadIdx.x;
   const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + t;
   auto issue = [&](int j) {
     if (j < P) {
       const T* src = rec + (base + (int64_t)j * kTileThreads) * 4;
       cp_async_word<2 * sizeof(T)>(&ring[j % S][t][0], src);
+      if (SCAT) cp_async_word<4>(&bring[j % S][t], src + 2);
     }
     cp_async_commit();
   };
@@ -151,7 +158,10 @@ interp2d_kernel(const T* __restrict__ rec, int P,
       for (int jj = 0; jj < W; ++jj) r = fma(g[i][jj], k1[jj], r);
       acc = fma(r, k0[i], acc);
     }
-    out[pn] = acc;
+    if (SCAT)
+      out[bring[s][t]] = acc;
+    else
+      out[pn] = acc;
   }
   cp_async_wait<0>();
 }
@@ -613,7 +623,7 @@ __global__ void __launch_bounds__(256) probe_fill_orig_kernel(int64_t N, T* __re
 
 template <typename T, int W>
 static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* grid, T* out, int64_t ostride,
-                     cudaStream_t st) {
+                     cudaStream_t st, bool scatter = false) {
   ESDev<T> es;
   es_to_dev<T>(k, es);
   const T* rec = (const T*)sp.rec;
@@ -631,9 +641,12 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* grid, T
         const size_t smem = (size_t)kTmaStages * kTmaSteps * kTileThreads * 4 * sizeof(T);
         EFGP_CUDA(cudaFuncSetAttribute(interp2d_tma_kernel<T, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         interp2d_tma_kernel<T, W><<<nt, kTileThreads, smem, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid, out, es);
+      } else if (scatter) {
+        interp2d_kernel<T, W, true><<<nt, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
+                                                                 out, ostride, es);
       } else {
-        interp2d_kernel<T, W><<<nt, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
-                                                           out, ostride, es);
+        interp2d_kernel<T, W, false><<<nt, kTileThreads, 0, st>>>(rec, sp.P, (int)sp.nf[0], (int)sp.nf[1], grid,
+                                                                  out, ostride, es);
       }
     } else {
       interp_direct_kernel<T, W, 2><<<div_up(sp.npos, 256), 256, 0, st>>>(
@@ -655,11 +668,11 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* grid, T
 
 template <typename T>
 static void launch_t(const SortedPoints& sp, const ESKernel& k, const T* grid, T* out, int64_t ostride,
-                     cudaStream_t st) {
+                     cudaStream_t st, bool scatter = false) {
   switch (k.W) {
 #define EFGP_CASE(w) \
   case w:            \
-    launch_w<T, w>(sp, k, grid, out, ostride, st); \
+    launch_w<T, w>(sp, k, grid, out, ostride, st, scatter); \
     break;
     EFGP_CASE(2) EFGP_CASE(3) EFGP_CASE(4) EFGP_CASE(5) EFGP_CASE(6) EFGP_CASE(7) EFGP_CASE(8) EFGP_CASE(9)
     EFGP_CASE(10) EFGP_CASE(11) EFGP_CASE(12) EFGP_CASE(13) EFGP_CASE(14) EFGP_CASE(15) EFGP_CASE(16)
@@ -676,11 +689,17 @@ void launch_interp(const SortedPoints& sp, const ESKernel& k, const void* grid, 
   // the kernels write slot-order results (coalesced); unpermute_output gathers them back to original order
   const size_t esz = sp.dtype == 0 ? 4 : 8;
   void* tmp = pool_alloc(esz * (size_t)sp.npos);
+  // 2-D register-patch kernels: results go straight to bucket order (interp2d_kernel<.., SCAT>), one un-permute level
+  // A/B only (EFGP_INTERP_SCATTER=1).  Measured at N = 1e8: 3.81 ms against 0.61 (interp) + 0.48 (slot -> bucket order):
+  // 1e8 scattered 8-byte partial-sector stores run at ~2.6e10/s, the gathers of the separate pass at ~2e11/s.
+  static const bool scat_env = getenv("EFGP_INTERP_SCATTER") && atoi(getenv("EFGP_INTERP_SCATTER")) != 0;
+  static const bool tma_env = getenv("EFGP_INTERP_TMA") != nullptr && atoi(getenv("EFGP_INTERP_TMA")) != 0;
+  const bool scatter = scat_env && !tma_env && sp.dim == 2 && k.W <= (sp.dtype == 0 ? 10 : 9);
   if (sp.dtype == 0)
-    launch_t<float>(sp, k, (const float*)grid, (float*)tmp, 1, st);
+    launch_t<float>(sp, k, (const float*)grid, (float*)tmp, 1, st, scatter);
   else
-    launch_t<double>(sp, k, (const double*)grid, (double*)tmp, 1, st);
-  unpermute_output(sp, tmp, out, ostride, st);
+    launch_t<double>(sp, k, (const double*)grid, (double*)tmp, 1, st, scatter);
+  unpermute_output(sp, tmp, out, ostride, st, scatter);
   pool_free(tmp);  // stream-ordered reuse
 }
 

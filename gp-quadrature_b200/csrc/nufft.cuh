@@ -101,7 +101,9 @@ void build_sorted_points(SortedPoints& sp, const void* x, const void* payload, i
 // sector-efficient stages (original -> bucket order -> slot order)
 void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, void* cs, cudaStream_t st);
 // out[i * ostride] = r[B[A[i]]]: slot-order results (written coalesced by interp) back to original order
-void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t ostride, cudaStream_t st);
+// r holds slot-order results, or (bucket_order) results already at their level-1 positions
+void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t ostride, cudaStream_t st,
+                      bool bucket_order = false);
 
 // ---- spread.cu : grid (real, nf^d) += sum_n c_n psi(l - X_n).  cs == nullptr means all ones;
 // otherwise cs holds the strengths in SLOT order (permute_strengths).

@@ -627,12 +627,13 @@ void permute_strengths(const SortedPoints& sp, const void* c, int64_t cstride, v
   pool_free(tmp);  // stream-ordered reuse
 }
 
-void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t ostride, cudaStream_t st) {
+void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t ostride, cudaStream_t st,
+                      bool bucket_order) {
   if (sp.N == 0) return;
   const size_t esz = sp.dtype == 0 ? 4 : 8;
-  void* tmp = pool_alloc(esz * (size_t)sp.N);
+  void* tmp = bucket_order ? const_cast<void*>(r) : pool_alloc(esz * (size_t)sp.N);
   const int gsh = run_group_shift(sp.nb1);
-  {
+  if (!bucket_order) {
     ScopedStage stg("unpermute.slot_to_bucket_order", st, 1, sp.N);
     if (sp.dtype == 0)
       slot_to_bucket_order_kernel<float><<<div_up(sp.N, 1024), 256, 0, st>>>((const float*)r, sp.B, sp.N, (float*)tmp);
@@ -649,7 +650,7 @@ void unpermute_output(const SortedPoints& sp, const void* r, void* out, int64_t 
                                                                            sp.ntiles1, sp.nb1, gsh, (double*)out, ostride);
   }
   EFGP_CUDA(cudaGetLastError());
-  pool_free(tmp);  // stream-ordered reuse
+  if (!bucket_order) pool_free(tmp);  // stream-ordered reuse
 }
 
 // ------------------------------------------------------------------ host driver

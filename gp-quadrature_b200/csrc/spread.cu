@@ -15,6 +15,7 @@
 #include "nufft.cuh"
 #include "stream_ring.cuh"
 #include "philox.cuh"
+#include <optional>
 
 namespace efgp {
 
@@ -224,6 +225,170 @@ spread2d_kernel(const T* __restrict__ rec, const T* __restrict__ cs, int P, int 
   if (cur0 >= 0) {
 #pragma unroll
     for (int b = 0; b < NB; ++b) flush2d<T, W>(acc[b], cur0, cur1, nf0, nf1, grid + b * cells);
+  }
+}
+
+// ------------------------------------------------------------------ 2-D, moment accumulation (dense point sets, fp64)
+// The F^*1 spread at W = 9 is bound by the FP64 pipe, not by HBM: per point the register-footprint kernel above spends
+// ~80 DFMA on the two piecewise polynomials and W^2 = 81 on the outer product (163 DFMA in the SASS; 1e8 points at the
+// measured ~37 TFLOP/s DFMA peak are 0.88 ms, the kernel takes 1.25 ms).  The weights of a point are polynomials of
+// its in-cell offsets (s, t) in [-1, 1):  k0_i(s) = sum_a c_i[a] s^a,  k1_j(t) = sum_b c_j[b] t^b,  so the footprint of
+// a run of points that share a cell is
+//     acc[i][j] = sum_p y_p k0_i(s_p) k1_j(t_p) = sum_{a,b} c_i[a] c_j[b] M[a][b],   M[a][b] = sum_p y_p s_p^a t_p^b.
+// The kernel below accumulates the NC x NC MOMENTS M (NC = degree + 1 <= W) instead of the footprint: 2 (NC - 1)
+// multiplications for the powers and NC^2 FMAs per point -- 97 instead of 163 FP64 instructions at W = 9 -- and no
+// polynomial evaluation at all.  On a cell change the moments are added (RED.ADD.F64, NC^2 consecutive doubles) to a
+// per-cell moment grid; moment_to_grid_kernel then applies C (x) C once per CELL (2 NC^2 W FMAs per cell row, ~3e7
+// FMAs for a 144^2 grid against 1.6e10 saved) and adds the footprints to the fine grid.  Monomials on [-1, 1] at
+// degree <= 8 are well conditioned for this purpose (the coefficients are O(1), the weights are in [0, 1]); the
+// transform error stays at the kernel's own aliasing floor (tests/test_ops_gpu.py bars unchanged).
+// Used when the points are dense on the grid (launch_w): >= kMomentMinDensity points per cell on average.
+constexpr int kMomentMinDensity = 48;
+constexpr size_t kMomentMaxBytes = (size_t)192 << 20;
+
+template <int W, int HAS_C, int S>
+__global__ void __launch_bounds__(kTileThreads, 1)
+spread2d_moment_kernel(const double* __restrict__ rec, const double* __restrict__ cs, int P, int nf0, int nf1,
+                       double* __restrict__ mom, int dbg) {
+  using T = double;
+  constexpr int NC = es_degree(W) + 1;
+  __shared__ __align__(16) T ring[S][kTileThreads][2];
+  __shared__ T cring[HAS_C ? S : 1][kTileThreads];
+  const int t = threadIdx.x;
+  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + t;
+  auto issue = [&](int j, int s) {     // point j into ring slot s (= j mod S, tracked by the caller: no division)
+    if (j < P) {
+      const int64_t pos = base + (int64_t)j * kTileThreads;
+      cp_async_word<2 * sizeof(T)>(&ring[s][t][0], rec + pos * 4);
+      if (HAS_C == 1) cp_async_word<sizeof(T)>(&cring[s][t], cs + pos);
+      if (HAS_C == 2) cp_async_word<sizeof(T)>(&cring[s][t], rec + pos * 4 + 3);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int j = 0; j < S; ++j) issue(j, j);
+  T M[NC][NC];
+#pragma unroll
+  for (int a = 0; a < NC; ++a)
+#pragma unroll
+    for (int b = 0; b < NC; ++b) M[a][b] = 0;
+  int cur0 = -1, cur1 = -1;
+  auto flush = [&]() {
+    T* m = mom + ((int64_t)cur0 * nf1 + cur1) * (NC * NC);
+#pragma unroll
+    for (int a = 0; a < NC; ++a)
+#pragma unroll
+      for (int b = 0; b < NC; ++b) {
+        atomicAdd(m + a * NC + b, M[a][b]);
+        M[a][b] = 0;
+      }
+  };
+  // cell and powers of the point in ring slot s (c0 = -1 for the padding sentinel X0 = -1 and past the run's end)
+  auto fetch = [&](int j, int s, int& c0, int& c1, T (&pa)[NC], T (&pb)[NC]) {
+    const T X0 = j < P ? ring[s][t][0] : T(-1);
+    const T X1 = ring[s][t][1];
+    c0 = (int)X0;
+    c1 = (int)X1;
+    const T u = T(2) * (X0 - (T)c0) - T(1), v = T(2) * (X1 - (T)c1) - T(1);
+    // powers with a shallow dependency tree: x^k = x^(k/2) * x^(k - k/2)
+    T up[NC], vp[NC];
+    up[0] = vp[0] = T(1);
+    if (NC > 1) { up[1] = u; vp[1] = v; }
+#pragma unroll
+    for (int k = 2; k < NC; ++k) {
+      up[k] = up[k / 2] * up[k - k / 2];
+      vp[k] = vp[k / 2] * vp[k - k / 2];
+    }
+    pa[0] = HAS_C ? cring[s][t] : T(1);
+    pb[0] = T(1);
+#pragma unroll
+    for (int k = 1; k < NC; ++k) {
+      pa[k] = HAS_C ? pa[0] * up[k] : up[k];
+      pb[k] = vp[k];
+    }
+  };
+  // Software pipeline: the dependent chain of point j + 1 (LDS, conversions, the power tree) is issued in the same
+  // basic block as the NC^2 independent FMAs of point j, so that with only two warps per scheduler (200 registers per
+  // thread) the FP64 pipe does not idle while both warps walk their chains (ncu before this: FP64 pipe 60 % active,
+  // top stall "wait").  Two register sets, the loop is unrolled by hand so that they swap roles without copies.
+  T paA[NC], pbA[NC], paB[NC], pbB[NC];
+  int a0, a1, b0, b1;
+  cp_async_wait<S - 1>();
+  fetch(0, 0, a0, a1, paA, pbA);
+  int sc = 0;    // ring slot of the current point
+  auto step = [&](int j, int c0, int c1, const T (&pa)[NC], const T (&pb)[NC], int& n0, int& n1, T (&npa)[NC],
+                  T (&npb)[NC]) {
+    issue(j + S, sc);                 // the current point's slot is free: its values are in registers
+    cp_async_wait<S - 1>();           // point j + 1 has landed
+    if (c0 != cur0 || c1 != cur1) {
+      if (cur0 >= 0 && !(dbg & 1)) flush();
+      cur0 = c0;
+      cur1 = c1;
+    }
+    sc = sc + 1 == S ? 0 : sc + 1;
+    fetch(j + 1, sc, n0, n1, npa, npb);
+#pragma unroll
+    for (int a = 0; a < NC; ++a)
+#pragma unroll
+      for (int b = 0; b < NC; ++b) M[a][b] = fma(pa[a], pb[b], M[a][b]);
+  };
+  for (int j = 0; j < P; j += 2) {
+    if (a0 < 0) break;
+    step(j, a0, a1, paA, pbA, b0, b1, paB, pbB);
+    if (b0 < 0) break;
+    step(j + 1, b0, b1, paB, pbB, a0, a1, paA, pbA);
+  }
+  cp_async_wait<0>();
+  if (cur0 >= 0) flush();
+}
+
+// One thread per (cell, footprint row i): T_i[b] = sum_a c_i[a] M[a][b], then row i of the footprint,
+// F[i][j] = sum_b T_i[b] c_j[b], added to the fine grid.  c_{W-1-i}[a] = (-1)^a c_i[a] (es_eval's symmetry); the full
+// W x NC coefficient table is expanded into shared memory first (the threads of a warp need different rows i: indexing
+// the constant bank with a per-lane row serialises -- 53 us for 20736 cells before this, measured).
+template <int W>
+__global__ void __launch_bounds__(256)
+moment_to_grid_kernel(const double* __restrict__ mom, int nf0, int nf1, double* __restrict__ grid,
+                      const __grid_constant__ ESDev<double> es) {
+  constexpr int NC = es_degree(W) + 1;
+  constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
+  constexpr int HALF = (W + 1) / 2;
+  __shared__ double cf[W][NC + 1];
+  for (int q = threadIdx.x; q < W * NC; q += blockDim.x) {
+    const int i = q / NC, a = q - i * NC;
+    const int ii = i < HALF ? i : W - 1 - i;
+    const double c = es.c[ii][a];
+    cf[i][a] = (i >= HALF && (a & 1)) ? -c : c;
+  }
+  __syncthreads();
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t cell = idx / W;
+  const int i = (int)(idx - cell * W);
+  if (cell >= (int64_t)nf0 * nf1) return;
+  const double* m = mom + cell * (NC * NC);
+  double Tb[NC];
+#pragma unroll
+  for (int b = 0; b < NC; ++b) Tb[b] = 0;
+  bool any = false;
+#pragma unroll
+  for (int a = 0; a < NC; ++a) {
+    const double ca = cf[i][a];
+#pragma unroll
+    for (int b = 0; b < NC; ++b) {
+      const double mv = m[a * NC + b];
+      any |= mv != 0.0;
+      Tb[b] = fma(ca, mv, Tb[b]);
+    }
+  }
+  if (!any) return;       // an untouched cell: every moment is exactly zero
+  const int c0 = (int)(cell / nf1), c1 = (int)(cell - (int64_t)c0 * nf1);
+  double* row = grid + (int64_t)wrap_idx(c0 - OFF + i, nf0) * nf1;
+#pragma unroll
+  for (int j = 0; j < W; ++j) {
+    double f = 0;
+#pragma unroll
+    for (int b = 0; b < NC; ++b) f = fma(Tb[b], cf[j][b], f);
+    atomicAdd(row + wrap_idx(c1 - OFF + j, nf1), f);
   }
 }
 
@@ -465,7 +630,10 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
   char nm[56];
   snprintf(nm, sizeof(nm), "spread%dd_w%d_%s%s", sp.dim, W, sizeof(T) == 8 ? "f64" : "f32",
            mode == 0 ? "_ones" : (mode == 2 ? "_rec" : (mode == 3 ? (pr.nb == 4 ? "_probes4" : (pr.nb == 2 ? "_probes2" : "_probes1")) : "")));
-  ScopedStage stg(nm, st, 1, sp.N * (mode == 3 ? pr.nb : 1));
+  std::optional<ScopedStage> stg_holder;
+  stg_holder.emplace(nm, st, 1, sp.N * (mode == 3 ? pr.nb : 1));
+  struct { std::optional<ScopedStage>& h; void add_launches(int n) { h->add_launches(n); } void reset() { h.reset(); } }
+      stg{stg_holder};
   const int nf0 = (int)sp.nf[0], nf1 = (int)sp.nf[1], nf2 = (int)sp.nf[2];
   // Deterministic mode: one fixed-point RED per (point, grid cell).  Register / shared-memory footprints would sum a
   // run of points in floating point first, in the (run-dependent) order the sort left them inside a cell; per-point
@@ -492,6 +660,49 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
     else
       spread1d_kernel<T, W, 0><<<nt, kTileThreads, 0, st>>>(rec, cs, sp.P, nf0, grid, es, pr, det);
   } else if (sp.dim == 2) {
+    if constexpr (sizeof(T) == 8 && W >= 5 && W <= 9) {
+      // dense point sets: accumulate per-cell moments, transform once per cell (see spread2d_moment_kernel)
+      static const int mom_env = getenv("EFGP_SPREAD_MOMENTS") ? atoi(getenv("EFGP_SPREAD_MOMENTS")) : -1;
+      constexpr int NC = es_degree(W) + 1;
+      const int64_t cells = (int64_t)nf0 * nf1;
+      const size_t mbytes = sizeof(double) * (size_t)cells * NC * NC;
+      const bool dense = sp.N >= (int64_t)kMomentMinDensity * cells && mbytes <= kMomentMaxBytes;
+      const bool want = mom_env < 0 ? (W >= 7 && dense) : (mom_env > 0 && mom_env <= W && dense);
+      if (mode != 3 && want) {
+        double* mom = (double*)pool_alloc(mbytes);
+        EFGP_CUDA(cudaMemsetAsync(mom, 0, mbytes, st));
+        const double* r8 = (const double*)rec;
+        const double* c8 = (const double*)cs;
+        static const int dbg = getenv("EFGP_MOM_DBG") ? atoi(getenv("EFGP_MOM_DBG")) : 0;
+        static const int stages = getenv("EFGP_MOM_STAGES") ? atoi(getenv("EFGP_MOM_STAGES")) : 6;
+#define EFGP_MOM(S_)                                                                                          \
+        if (mode == 2)                                                                                        \
+          spread2d_moment_kernel<W, 2, S_><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom, dbg);    \
+        else if (mode == 1)                                                                                   \
+          spread2d_moment_kernel<W, 1, S_><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom, dbg);    \
+        else                                                                                                  \
+          spread2d_moment_kernel<W, 0, S_><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom, dbg);
+        if (stages >= 12 && mode == 0) {
+          spread2d_moment_kernel<W, 0, 12><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom, dbg);
+        } else if (stages >= 8) {
+          EFGP_MOM(8)
+        } else {
+          EFGP_MOM(6)
+        }
+#undef EFGP_MOM
+        stg.add_launches(1);
+        stg.reset();      // the per-cell transform is its own line in the stage report
+        {
+          ScopedStage stg2("type1.moment_to_grid", st, 1, 0);
+          ESDev<double> es8;
+          es_to_dev<double>(k, es8);
+          moment_to_grid_kernel<W><<<div_up(cells * W, 256), 256, 0, st>>>(mom, nf0, nf1, (double*)grid, es8);
+          EFGP_CUDA(cudaGetLastError());
+        }
+        pool_free(mom);
+        return;
+      }
+    }
     if constexpr (W <= kRegMaxW) {
       if (mode == 3) {
         if constexpr (W <= 5) {
