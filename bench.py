@@ -367,6 +367,10 @@ def algorithmic_flops(stage, n, d=2):
     point sets (every bench workload) run the moment kernel (spread2d_moment_kernel): 2 (NC - 1) multiplications for the
     powers of the two in-cell offsets and NC^2 FMAs per point, NC = degree + 1."""
     import re
+    mp = re.match(r"spread2d_pair_w(\d+)_w(\d+)_f64", stage)
+    if mp:      # fused generator + right-hand side (spread2d_moment_pair_kernel): powers once, two moment sets
+        ng, nr = int(mp.group(1)), int(mp.group(2))          # NC = W for the odd widths >= 5 (degree W - 1)
+        return n * (2 * (ng - 1) + nr + 2 * (ng * ng + nr * nr) + 4)
     m = re.match(r"(spread|interp)(\d)d_w(\d+)_(f64|f32)(.*)", stage)
     if not m:
         return None

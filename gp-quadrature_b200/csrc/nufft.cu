@@ -635,12 +635,58 @@ void nufft_type1(Nufft& nu, const void* strengths, int is_complex, int batch, co
     type1_t<double>(nu, strengths, is_complex, batch, n, eps, isign, modeord, scale, out, st);
 }
 
+// Generator and right-hand side in ONE pass over the records (spread.cu spread2d_moment_pair_kernel), one batched
+// R2C transform of the two fine grids and two deconvolutions.  Returns false (nothing enqueued besides, possibly, the
+// sort both paths need) when the geometry is not the dense 2-D fp64 case the fused kernel covers.
+static bool type1_pair_fused(Nufft& nu, const int64_t* shape_gen, double eps_gen, const int64_t* shape_rhs,
+                             double eps_rhs, const void* scale, void* out_gen, void* out_rhs, cudaStream_t st) {
+  using T = double;
+  using C = double2;
+  if (nu.dtype != 1 || nu.dim != 2 || nu.N == 0 || deterministic()) return false;
+  GridChoice gg = choose_grid(nu, shape_gen, eps_gen, st);     // sorts with the payload (pending_payload is set)
+  nu.pending_payload = nullptr;
+  GridChoice gr = choose_grid(nu, shape_rhs, eps_rhs, st);
+  if (gg.sp != gr.sp || gg.sp != nu.fresh_payload_sp || !spread_pair_supported(*gg.sp, gg.ker, gr.ker)) return false;
+  const int64_t* nf = gg.nf;
+  const int64_t cells = nf[0] * nf[1], slab = nf[0] * (nf[1] / 2 + 1);
+  ModeGeom geg = make_geom(2, shape_gen, nf, 0, 0), ger = make_geom(2, shape_rhs, nf, 0, 0);
+  void* dg[kMaxDim];
+  void* dr[kMaxDim];
+  upload_dinv(nu, gg.ker, nf, shape_gen, 2, 1, dg, st);
+  upload_dinv(nu, gr.ker, nf, shape_rhs, 2, 1, dr, st);
+  T* fine = (T*)nu.fine.get((size_t)2 * cells * sizeof(T));
+  C* spec = (C*)nu.spec.get((size_t)2 * slab * sizeof(C));
+  {
+    ScopedStage stg("type1.memset_fine", st, 0);
+    EFGP_CUDA(cudaMemsetAsync(fine, 0, (size_t)2 * cells * sizeof(T), st));
+  }
+  launch_spread_pair(*gg.sp, gg.ker, gr.ker, fine, fine + cells, st);
+  cufftHandle plan = global_fft().get(2, nf, CUFFT_D2Z, 2, st);
+  {
+    ScopedStage stg("type1.cufft_r2c", st, 0);
+    EFGP_CUFFT(cufftExecD2Z(plan, (cufftDoubleReal*)fine, (cufftDoubleComplex*)spec));
+  }
+  ScopedStage stg("type1.deconv_kernel", st, 2);
+  deconv_kernel<T><<<div_up(geg.M, 256), 256, 0, st>>>(spec, 1, 1, geg, (const T*)dg[0], (const T*)dg[1], (const T*)dg[2],
+                                                       (const T*)nullptr, (C*)out_gen);
+  deconv_kernel<T><<<div_up(ger.M, 256), 256, 0, st>>>(spec + slab, 1, 1, ger, (const T*)dr[0], (const T*)dr[1],
+                                                       (const T*)dr[2], (const T*)scale, (C*)out_rhs);
+  EFGP_CUDA(cudaGetLastError());
+  return true;
+}
+
 void nufft_type1_pair(Nufft& nu, const void* y, const int64_t* shape_gen, double eps_gen, const int64_t* shape_rhs,
                       double eps_rhs, const void* scale, void* out_gen, void* out_rhs, cudaStream_t st) {
   for (int a = 0; a < nu.dim; ++a) EFGP_CHECK(shape_gen[a] >= 1 && shape_rhs[a] >= 1, "mode counts must be >= 1");
   nu.pending_payload = nu.dim == 2 ? y : nullptr;
   nu.fresh_payload_sp = nullptr;
   try {
+    if (type1_pair_fused(nu, shape_gen, eps_gen, shape_rhs, eps_rhs, scale, out_gen, out_rhs, st)) {
+      nu.pending_payload = nullptr;
+      nu.fresh_payload_sp = nullptr;
+      return;
+    }
+    // (a declined fused attempt may already have built the payload-carrying sort: the two passes below find it)
     if (nu.dtype == 0)
       type1_t<float>(nu, nullptr, 0, 1, shape_gen, eps_gen, -1, 0, nullptr, out_gen, st);
     else

@@ -119,6 +119,9 @@ bool deterministic();
 // grids, interpolation with the fused sum_n Z * (.) epilogue, and Z itself in original order (tests)
 struct ProbeSpec;
 int spread_probe_batch(int dim, int W, int dtype);
+bool spread_pair_supported(const SortedPoints& sp, const ESKernel& kg, const ESKernel& kr);
+void launch_spread_pair(const SortedPoints& sp, const ESKernel& kg, const ESKernel& kr, void* gridG, void* gridR,
+                        cudaStream_t st);
 void launch_spread_probes(const SortedPoints& sp, const ESKernel& k, void* grid, const ProbeSpec& pr, cudaStream_t st,
                           void* igrid = nullptr, double iscale = 0.0);
 void launch_interp_probe_dots(const SortedPoints& sp, const ESKernel& k, const void* grid, double* out,

@@ -342,53 +342,170 @@ spread2d_moment_kernel(const double* __restrict__ rec, const double* __restrict_
   if (cur0 >= 0) flush();
 }
 
-// One thread per (cell, footprint row i): T_i[b] = sum_a c_i[a] M[a][b], then row i of the footprint,
-// F[i][j] = sum_b T_i[b] c_j[b], added to the fine grid.  c_{W-1-i}[a] = (-1)^a c_i[a] (es_eval's symmetry); the full
-// W x NC coefficient table is expanded into shared memory first (the threads of a warp need different rows i: indexing
-// the constant bank with a per-lane row serialises -- 53 us for 20736 cells before this, measured).
+// The generator F^*1 (width WG, all-ones strengths) and the right-hand side F^*y (width WR <= WG, strengths in the
+// records' payload word) in ONE pass over the records: both kernels are polynomials of the SAME in-cell offsets
+// (odd widths share the cell and its centre), so the powers are computed once and feed two moment sets,
+// MG[a][b] += u^a v^b (NCG^2) and MR[a][b] += y u^a v^b (NCR^2).  The record stream (3.2 GB at N = 1e8) is read once
+// instead of twice, and F^*y costs NCR^2 + NCR extra FP64 instructions per point instead of its own HBM-bound pass
+// (0.54 ms).  106 accumulators at (9, 5): the powers of u are produced row by row to stay inside 255 registers.
+template <int WG, int WR, int S>
+__global__ void __launch_bounds__(kTileThreads, 1)
+spread2d_moment_pair_kernel(const double* __restrict__ rec, int P, int nf1, double* __restrict__ momG,
+                            double* __restrict__ momR) {
+  using T = double;
+  constexpr int NG = es_degree(WG) + 1, NR = es_degree(WR) + 1;
+  static_assert(NR <= NG, "the right-hand-side kernel is the narrower one");
+  __shared__ __align__(16) T ring[S][kTileThreads][2];
+  __shared__ T yring[S][kTileThreads];
+  const int t = threadIdx.x;
+  const int64_t base = (int64_t)blockIdx.x * kTileThreads * P + t;
+  auto issue = [&](int j, int s) {
+    if (j < P) {
+      const int64_t pos = base + (int64_t)j * kTileThreads;
+      cp_async_word<2 * sizeof(T)>(&ring[s][t][0], rec + pos * 4);
+      cp_async_word<sizeof(T)>(&yring[s][t], rec + pos * 4 + 3);
+    }
+    cp_async_commit();
+  };
+#pragma unroll
+  for (int j = 0; j < S - 1; ++j) issue(j, j);
+  T MG[NG][NG], MR[NR][NR];
+#pragma unroll
+  for (int a = 0; a < NG; ++a)
+#pragma unroll
+    for (int b = 0; b < NG; ++b) MG[a][b] = 0;
+#pragma unroll
+  for (int a = 0; a < NR; ++a)
+#pragma unroll
+    for (int b = 0; b < NR; ++b) MR[a][b] = 0;
+  int cur0 = -1, cur1 = -1;
+  auto flush = [&]() {
+    const int64_t cell = (int64_t)cur0 * nf1 + cur1;
+    T* mg = momG + cell * (NG * NG);
+#pragma unroll
+    for (int a = 0; a < NG; ++a)
+#pragma unroll
+      for (int b = 0; b < NG; ++b) {
+        atomicAdd(mg + a * NG + b, MG[a][b]);
+        MG[a][b] = 0;
+      }
+    T* mr = momR + cell * (NR * NR);
+#pragma unroll
+    for (int a = 0; a < NR; ++a)
+#pragma unroll
+      for (int b = 0; b < NR; ++b) {
+        atomicAdd(mr + a * NR + b, MR[a][b]);
+        MR[a][b] = 0;
+      }
+  };
+  int s = 0, sn = S - 1;     // ring slots of point j and of point j + S - 1
+  for (int j = 0; j < P; ++j) {
+    issue(j + S - 1, sn);
+    cp_async_wait<S - 1>();
+    const T X0 = ring[s][t][0];
+    if (X0 < T(0)) break;
+    const T X1 = ring[s][t][1];
+    const T y = yring[s][t];
+    s = s + 1 == S ? 0 : s + 1;
+    sn = sn + 1 == S ? 0 : sn + 1;
+    const int c0 = (int)X0, c1 = (int)X1;
+    if (c0 != cur0 || c1 != cur1) {
+      if (cur0 >= 0) flush();
+      cur0 = c0;
+      cur1 = c1;
+    }
+    const T u = T(2) * (X0 - (T)c0) - T(1), v = T(2) * (X1 - (T)c1) - T(1);
+    T vp[NG];
+    vp[0] = T(1);
+    vp[1] = v;
+#pragma unroll
+    for (int k = 2; k < NG; ++k) vp[k] = vp[k / 2] * vp[k - k / 2];
+    T ua = T(1);
+#pragma unroll
+    for (int a = 0; a < NG; ++a) {
+      if (a == 1) ua = u;
+      if (a > 1) ua *= u;
+#pragma unroll
+      for (int b = 0; b < NG; ++b) MG[a][b] = fma(ua, vp[b], MG[a][b]);
+      if (a < NR) {
+        const T ya = y * ua;
+#pragma unroll
+        for (int b = 0; b < NR; ++b) MR[a][b] = fma(ya, vp[b], MR[a][b]);
+      }
+    }
+  }
+  cp_async_wait<0>();
+  if (cur0 >= 0) flush();
+}
+
+// Per-cell moments -> fine grid.  A CTA takes a segment of kM2GCells consecutive cells of one grid row c0:
+//  (1) their moments (NC^2 contiguous doubles per cell) are staged into shared memory with coalesced loads;
+//  (2) warp i computes footprint row i of every cell of the segment: T_i[b] = sum_a c_i[a] M[a][b], then
+//      F[i][j] = sum_b T_i[b] c_j[b]  (c_{W-1-i}[a] = (-1)^a c_i[a]: es_eval's symmetry, table expanded in shared memory);
+//  (3) the footprints of neighbouring cells overlap in all but one column, so they are summed inside the CTA first:
+//      out[i][col] = sum_j F_{cell = col - j}[i][j], and ONE RED per (row, column) of the segment goes to the grid --
+//      (kM2GCells + W - 1) W REDs per CTA instead of kM2GCells W^2.  (The first version issued every footprint entry as
+//      its own RED: 6.7e6 REDs, 81 per grid address, 51 us for a 288^2 grid, whatever the load path.)
+constexpr int kM2GCells = 32;
+
 template <int W>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kM2GCells * W)
 moment_to_grid_kernel(const double* __restrict__ mom, int nf0, int nf1, double* __restrict__ grid,
                       const __grid_constant__ ESDev<double> es) {
   constexpr int NC = es_degree(W) + 1;
+  constexpr int NM = NC * NC;
+  constexpr int PM = (NM & 1) ? NM : NM + 1;     // odd pitch: the 32 cells of a warp land on different banks
   constexpr int OFF = W / 2 - ((W & 1) ? 0 : 1);
   constexpr int HALF = (W + 1) / 2;
+  constexpr int NT = kM2GCells * W;
   __shared__ double cf[W][NC + 1];
-  for (int q = threadIdx.x; q < W * NC; q += blockDim.x) {
+  __shared__ double sm[kM2GCells * PM];
+  __shared__ double Fs[W * W][kM2GCells + 1];
+  const int segs = (nf1 + kM2GCells - 1) / kM2GCells;
+  const int c0 = blockIdx.x / segs, c1b = (blockIdx.x - c0 * segs) * kM2GCells;
+  const int nc = nf1 - c1b < kM2GCells ? nf1 - c1b : kM2GCells;
+  for (int q = threadIdx.x; q < W * NC; q += NT) {
     const int i = q / NC, a = q - i * NC;
     const int ii = i < HALF ? i : W - 1 - i;
     const double c = es.c[ii][a];
     cf[i][a] = (i >= HALF && (a & 1)) ? -c : c;
   }
+  const double* src = mom + ((int64_t)c0 * nf1 + c1b) * NM;
+  for (int q = threadIdx.x; q < nc * NM; q += NT) {
+    const int lc = q / NM;
+    sm[lc * PM + (q - lc * NM)] = src[q];
+  }
   __syncthreads();
-  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t cell = idx / W;
-  const int i = (int)(idx - cell * W);
-  if (cell >= (int64_t)nf0 * nf1) return;
-  const double* m = mom + cell * (NC * NC);
-  double Tb[NC];
+  const int i = threadIdx.x >> 5, lc = threadIdx.x & 31;      // warp i: footprint row i
+  if (lc < nc) {
+    const double* m = sm + lc * PM;
+    double Tb[NC];
 #pragma unroll
-  for (int b = 0; b < NC; ++b) Tb[b] = 0;
-  bool any = false;
+    for (int b = 0; b < NC; ++b) Tb[b] = 0;
 #pragma unroll
-  for (int a = 0; a < NC; ++a) {
-    const double ca = cf[i][a];
+    for (int a = 0; a < NC; ++a) {
+      const double ca = cf[i][a];
 #pragma unroll
-    for (int b = 0; b < NC; ++b) {
-      const double mv = m[a * NC + b];
-      any |= mv != 0.0;
-      Tb[b] = fma(ca, mv, Tb[b]);
+      for (int b = 0; b < NC; ++b) Tb[b] = fma(ca, m[a * NC + b], Tb[b]);
+    }
+#pragma unroll
+    for (int j = 0; j < W; ++j) {
+      double f = 0;
+#pragma unroll
+      for (int b = 0; b < NC; ++b) f = fma(Tb[b], cf[j][b], f);
+      Fs[i * W + j][lc] = f;
     }
   }
-  if (!any) return;       // an untouched cell: every moment is exactly zero
-  const int c0 = (int)(cell / nf1), c1 = (int)(cell - (int64_t)c0 * nf1);
+  __syncthreads();
   double* row = grid + (int64_t)wrap_idx(c0 - OFF + i, nf0) * nf1;
+  for (int col = lc; col < nc + W - 1; col += 32) {
+    double v = 0;
 #pragma unroll
-  for (int j = 0; j < W; ++j) {
-    double f = 0;
-#pragma unroll
-    for (int b = 0; b < NC; ++b) f = fma(Tb[b], cf[j][b], f);
-    atomicAdd(row + wrap_idx(c1 - OFF + j, nf1), f);
+    for (int j = 0; j < W; ++j) {
+      const int cc = col - j;
+      if (cc >= 0 && cc < nc) v += Fs[i * W + j][cc];
+    }
+    if (v != 0.0) atomicAdd(row + wrap_idx(c1b - OFF + col, nf1), v);
   }
 }
 
@@ -696,7 +813,7 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
           ScopedStage stg2("type1.moment_to_grid", st, 1, 0);
           ESDev<double> es8;
           es_to_dev<double>(k, es8);
-          moment_to_grid_kernel<W><<<div_up(cells * W, 256), 256, 0, st>>>(mom, nf0, nf1, (double*)grid, es8);
+          moment_to_grid_kernel<W><<<nf0 * div_up(nf1, kM2GCells), kM2GCells * W, 0, st>>>(mom, nf0, nf1, (double*)grid, es8);
           EFGP_CUDA(cudaGetLastError());
         }
         pool_free(mom);
@@ -794,6 +911,56 @@ void launch_spread(const SortedPoints& sp, const ESKernel& k, const void* cs, vo
     launch_t<float>(sp, k, (const float*)cs, (float*)grid, st, mode, pr, det);
   else
     launch_t<double>(sp, k, (const double*)cs, (double*)grid, st, mode, pr, det);
+}
+
+// ---- fused generator + right-hand side (nufft_type1_pair)
+bool spread_pair_supported(const SortedPoints& sp, const ESKernel& kg, const ESKernel& kr) {
+  static const bool off = getenv("EFGP_PAIR_FUSED") && atoi(getenv("EFGP_PAIR_FUSED")) == 0;
+  if (off || sp.dim != 2 || sp.dtype != 1 || !sp.has_payload || !sp.odd || sp.N == 0) return false;
+  if (!((kg.W == 9 || kg.W == 7) && kr.W == 5)) return false;
+  const int64_t cells = sp.nf[0] * sp.nf[1];
+  const int ng = es_degree(kg.W) + 1;
+  return sp.N >= (int64_t)kMomentMinDensity * cells && sizeof(double) * (size_t)cells * ng * ng <= kMomentMaxBytes;
+}
+
+template <int WG, int WR>
+static void launch_pair_w(const SortedPoints& sp, const ESKernel& kg, const ESKernel& kr, double* gridG, double* gridR,
+                          cudaStream_t st) {
+  constexpr int NG = es_degree(WG) + 1, NR = es_degree(WR) + 1;
+  const int nf0 = (int)sp.nf[0], nf1 = (int)sp.nf[1];
+  const int64_t cells = (int64_t)nf0 * nf1;
+  const size_t bg = sizeof(double) * (size_t)cells * NG * NG, br = sizeof(double) * (size_t)cells * NR * NR;
+  double* mom = (double*)pool_alloc(bg + br);
+  double* momR = mom + (size_t)cells * NG * NG;
+  {
+    char nm[56];
+    snprintf(nm, sizeof(nm), "spread2d_pair_w%d_w%d_f64", WG, WR);
+    ScopedStage stg(nm, st, 2, sp.N);
+    EFGP_CUDA(cudaMemsetAsync(mom, 0, bg + br, st));
+    spread2d_moment_pair_kernel<WG, WR, kRingStages><<<(int)sp.ntiles, kTileThreads, 0, st>>>(
+        (const double*)sp.rec, sp.P, nf1, mom, momR);
+    EFGP_CUDA(cudaGetLastError());
+  }
+  {
+    ScopedStage stg("type1.moment_to_grid", st, 2, 0);
+    ESDev<double> eg, er;
+    es_to_dev<double>(kg, eg);
+    es_to_dev<double>(kr, er);
+    moment_to_grid_kernel<WG><<<nf0 * div_up(nf1, kM2GCells), kM2GCells * WG, 0, st>>>(mom, nf0, nf1, gridG, eg);
+    moment_to_grid_kernel<WR><<<nf0 * div_up(nf1, kM2GCells), kM2GCells * WR, 0, st>>>(momR, nf0, nf1, gridR, er);
+    EFGP_CUDA(cudaGetLastError());
+  }
+  pool_free(mom);
+}
+
+// gridG += F^*1 footprints (kernel kg), gridR += F^*y footprints (kernel kr, y = the records' payload): one pass
+void launch_spread_pair(const SortedPoints& sp, const ESKernel& kg, const ESKernel& kr, void* gridG, void* gridR,
+                        cudaStream_t st) {
+  EFGP_CHECK(spread_pair_supported(sp, kg, kr), "fused pair spreading does not support this geometry");
+  if (kg.W == 9)
+    launch_pair_w<9, 5>(sp, kg, kr, (double*)gridG, (double*)gridR, st);
+  else
+    launch_pair_w<7, 5>(sp, kg, kr, (double*)gridG, (double*)gridR, st);
 }
 
 // grids b = 0 .. pr.nb-1 (contiguous, nf^d each) += sum over points of Rademacher(seed, pr.t0 + b, slot) psi(l - X)

@@ -1,18 +1,6 @@
 #!/bin/bash
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
-O=gpurun_out/q
+O=gpurun_out/final
 mkdir -p $O
-timeout 2400 python -m pytest tests -q -m gpu --timeout=900 > $O/pytest.log 2>&1
-grep -E "^FAILED|^E  |passed|failed" $O/pytest.log | head -20
-B="--steps 5 --warmup 3 --no-cpu-baseline --no-parity --no-e2e"
-run() { tag=$1; shift; env "$@" timeout 300 python bench.py $B > $O/bench_$tag.json 2> $O/bench_$tag.err; }
-run base A=1
-B="--steps 20 --warmup 5 --npts 1.25e7 --no-cpu-baseline --no-parity --no-e2e"
-run shard A=1
-python - <<'PY'
-import json
-for t in ["base","shard"]:
-    try:
-        d=json.load(open(f"gpurun_out/q/bench_{t}.json")); print(t, round(d["ms_per_step"],3), d["result_rms"], {k: round(v["ms_per_step"],3) for k,v in d["stages"].items() if "spread" in k or "moment" in k or "bbox" in k})
-    except Exception as e: print(t, "ERR", e)
-PY
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:"efgp::|regular_fft|vector_fft|cub::" -c 900 --csv --log-file $O/ncu_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-parity --no-e2e --no-f32 > $O/ncu_launches.out 2>&1; echo "rc=$?"
+tail -c 300 $O/ncu_launches.out

@@ -34,16 +34,21 @@ for src, dst in (("bench.json", "bench_r02_1gpu.json"), ("bench_shard.json", "be
         json.dump(last_json(os.path.join(G, src)), open(os.path.join(P, dst), "w"), indent=1)
 
 rep = os.path.join(G, "ncu_full.ncu-rep")
+if not os.path.exists(rep):
+    rep = os.path.join(G, "ncu_full_raw.csv")      # the raw page exported on the box (the report itself is > 64 MiB)
 tab = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "ncu_summary.py"), rep], capture_output=True, text=True).stdout
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+raw = (open(rep).read() if rep.endswith(".csv") else
+       subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout)
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units = rows[0], rows[1]
 ki, ri, wi = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
 scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
 stage_of = [("bucket_hist", "sort.bucket_hist_kernel"), ("bucket_scatter", "sort.bucket_scatter_kernel_pay"),
             ("bin_hist", "sort.bin_hist_kernel"), ("bin_scatter", "sort.bin_scatter_kernel_pay"),
+            ("spread2d_moment_pair_kernel<9, 5", "spread2d_pair_w9_w5_f64"),
+            ("spread2d_moment_kernel<9, 0", "spread2d_w9_f64_ones"), ("moment_to_grid_kernel", "type1.moment_to_grid"),
             ("spread2d_kernel<double, 9, 0", "spread2d_w9_f64_ones"), ("spread2d_kernel<double, 7, 0", "spread2d_w7_f64_ones"),
-            ("spread2d_kernel<double, 5, 2", "spread2d_w5_f64_rec"), ("interp2d_kernel<double, 5>", "interp2d_w5_f64"),
+            ("spread2d_kernel<double, 5, 2", "spread2d_w5_f64_rec"), ("interp2d_kernel<double, 5", "interp2d_w5_f64"),
             ("slot_to_bucket", "unpermute.slot_to_bucket_order"), ("from_bucket", "unpermute.from_bucket_order"),
             ("bbox_partial", "fit.bbox"), ("cg_conv_kernel", "cg.iterations"), ("cg_persist_kernel", "cg.iterations")]
 bench = last_json(os.path.join(G, "bench.json"))
@@ -86,8 +91,8 @@ Commands (B200_PROFILING.md recipe, run under gpurun after the same bench comman
 `scripts/make_profiles_r02.py` from what the call brought back:
 
 ```
-ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file ncu_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-parity --no-e2e
-ncu --set full --clock-control none --import-source on -k regex:"spread2d_kernel|interp2d_kernel|bucket_|bin_|cg_conv|cg_persist|from_bucket|slot_to_bucket|bbox_partial" --launch-skip 60 -c 14 -o ncu_full python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-parity --no-e2e
+ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:"efgp::|regular_fft|vector_fft|cub::" -c 900 --csv --log-file ncu_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-parity --no-e2e
+ncu --set full --clock-control none --import-source on -k regex:"spread2d_|moment_to_grid|interp2d_kernel|bucket_|bin_|cg_conv|cg_persist|from_bucket|slot_to_bucket|bbox_partial" --launch-skip 36 -c 14 -o /tmp/ncu_full python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-parity --no-e2e
 ```
 
 ## Per-launch counters of one whole solve (`ncu --set full`, raw page)
@@ -97,7 +102,7 @@ ncu --set full --clock-control none --import-source on -k regex:"spread2d_kernel
 ## Launch list (`gpu__time_duration.sum`, cold-cache and serialised: compare SHARES, not absolutes)
 
 {ll}
-total {tot:.2f} ms over the profiled process (warm-up + timed + refit steps and the synthetic-data kernels)
+total {tot:.2f} ms over the profiled launches (library, cuFFT and CUB kernels of the warm-up, timed and refit steps; the\nsynthetic-data ATen kernels are filtered out with -k)
 
 ## Live CUDA-event stage times of the same build (`profiles/bench_r02_1gpu.json`, `stages`)
 

@@ -1,7 +1,9 @@
-"""Summarise an .ncu-rep (raw page) into a per-launch table: python scripts/ncu_summary.py file.ncu-rep"""
+"""Summarise an .ncu-rep (or its `--page raw --csv` export) into a per-launch table:
+    python scripts/ncu_summary.py file.ncu-rep | file_raw.csv"""
 import csv, subprocess, sys, io
 rep = sys.argv[1]
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+raw = (open(rep).read() if rep.endswith(".csv") else
+       subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout)
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units = rows[0], rows[1]
 want = [("gpu__time_duration.sum", "time"), ("dram__bytes_read.sum", "dram_rd"), ("dram__bytes_write.sum", "dram_wr"),
