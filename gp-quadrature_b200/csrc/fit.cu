@@ -156,6 +156,8 @@ void fit_run(Nufft& nu, Toeplitz& t, const void* y, const FitArgs& a, void* ws, 
       ws_kernel<double><<<div_up(M, 256), 256, 0, st>>>((double*)ws, dim, a.mtot, M, a);
     EFGP_CUDA(cudaGetLastError());
   }
+  // sharded: all ranks choose the fine grid as one rank holding every point would (the rank counts differ by at most one point)
+  nu.cost_npts = a.sharded ? nu.N * (int64_t)std::max(1, comm_world()) : 0;
   nufft_type1_pair(nu, y, shape_gen, a.gen_eps, shape_rhs, a.nufft_eps, ws, v, rhs, st);
   if (a.sharded) {
     ScopedStage stg("fit.allreduce_grids", st, 0, Lg + M);

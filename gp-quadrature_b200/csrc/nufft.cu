@@ -387,6 +387,11 @@ static double transform_cost(int dim, double npts, int W, double cells) {
 // factor (narrower kernel: fewer FMAs per point) is nearly free -- e.g. the Toeplitz generator of the headline
 // solve (141^2 modes, eps 6e-8, 1e8 points) takes W = 7 on a 720^2 grid instead of W = 9 on 288^2 (measured
 // 1.6 -> see DESIGN.md section 4).  EFGP_SIGMA pins the factor (A/B measurements).
+// Point count the grid-choice cost model sees.  Point-sharded fits set Nufft::cost_npts to the GLOBAL count: every rank
+// (and a one-rank run on all the points) then picks the same fine grid and kernel, so the all-reduced sum of the shard
+// transforms is the one-rank transform to rounding, not merely to the NUFFT tolerance.
+static double cost_points(const Nufft& nu) { return (double)(nu.cost_npts > 0 ? nu.cost_npts : nu.N); }
+
 static double pick_sigma(const Nufft& nu, const int64_t* n, double eps, int64_t* nf_out, int* w_out) {
   static const double sigma_env = [] {
     const char* e = std::getenv("EFGP_SIGMA");
@@ -414,14 +419,14 @@ static double pick_sigma(const Nufft& nu, const int64_t* n, double eps, int64_t*
     const size_t esz = nu.dtype == 0 ? 4 : 8;
     const bool fits = cells < 3.9e9 && cells * esz <= (double)((size_t)2 << 30);
     if (!fits && best_sigma > 0) break;
-    double cost = transform_cost(nu.dim, (double)nu.N, w, cells);
+    double cost = transform_cost(nu.dim, cost_points(nu), w, cells);
     if (nu.dim <= 2) {
       // this grid also keys the cell sort: the level-2 counting sort pays per (2048-point tile, bin) pair, measured at
       // N = 1e8 as 1.2 ms + 1.35e-6 ms per cell (288^2 .. 864^2 cells) = 1.6e-4 FMA-times per point and cell
-      cost += 1.6e-4 * cells * (double)nu.N;
+      cost += 1.6e-4 * cells * cost_points(nu);
       // an even width fixes the parity of every later transform on these sorted points: the narrow F*y / type-2
       // kernels (odd W = 5 at the reference's default eps) would be forced one step wider
-      if (nu.dim == 2 && (w % 2) == 0) cost += 40.0 * (double)nu.N;
+      if (nu.dim == 2 && (w % 2) == 0) cost += 40.0 * cost_points(nu);
     }
     if (best_sigma == 0 || cost < best_cost) {
       best_cost = cost;
@@ -443,7 +448,7 @@ static GridChoice choose_grid(Nufft& nu, const int64_t* n, double eps, cudaStrea
   pick_sigma(nu, n, eps, own, &w_own);
   double own_cells = 1;
   for (int a = 0; a < nu.dim; ++a) own_cells *= (double)own[a];
-  const double own_cost = transform_cost(nu.dim, (double)nu.N, w_own, own_cells);
+  const double own_cost = transform_cost(nu.dim, cost_points(nu), w_own, own_cells);
   // An existing sorted set on a grid at least 2x the mode count can serve this transform without another sort
   // (larger effective upsampling -> narrower kernel): this is how F*y and the type-2 share the generator's grid.
   SortedPoints* best = nullptr;
@@ -464,8 +469,8 @@ static GridChoice choose_grid(Nufft& nu, const int64_t* n, double eps, cudaStrea
     for (int a = 0; a < nu.dim; ++a) ok = ok && sp->nf[a] >= 2 * w;
     if (!ok) continue;
     // a second sort costs about as much as three narrow transforms and holds another copy of the points
-    const double cost = transform_cost(nu.dim, (double)nu.N, w, cells);
-    if (cost > 4.0 * own_cost + 100.0 * (double)nu.N) continue;
+    const double cost = transform_cost(nu.dim, cost_points(nu), w, cells);
+    if (cost > 4.0 * own_cost + 100.0 * cost_points(nu)) continue;
     if (!best || cost < best_cost) {
       best = sp.get();
       best_w = w;

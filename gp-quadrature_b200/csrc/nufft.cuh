@@ -87,6 +87,7 @@ struct Nufft {
   std::vector<std::unique_ptr<SortedPoints>> sorted;  // small LRU cache
   DevBuf fine, spec, tmp, dec, cperm;
   bool carry_index = false;                    // sorted sets carry the original point index (probe streaming)
+  int64_t cost_npts = 0;                       // > 0: point count used by the grid-choice cost model (sharded fits)
   const void* pending_payload = nullptr;       // set by nufft_type1_pair: next sort carries these strengths
   const SortedPoints* fresh_payload_sp = nullptr;  // the sorted set built with them during this call
 };

@@ -249,7 +249,7 @@ constexpr size_t kMomentMaxBytes = (size_t)192 << 20;
 template <int W, int HAS_C, int S>
 __global__ void __launch_bounds__(kTileThreads, 1)
 spread2d_moment_kernel(const double* __restrict__ rec, const double* __restrict__ cs, int P, int nf0, int nf1,
-                       double* __restrict__ mom, int dbg) {
+                       double* __restrict__ mom) {
   using T = double;
   constexpr int NC = es_degree(W) + 1;
   __shared__ __align__(16) T ring[S][kTileThreads][2];
@@ -321,7 +321,7 @@ spread2d_moment_kernel(const double* __restrict__ rec, const double* __restrict_
     issue(j + S, sc);                 // the current point's slot is free: its values are in registers
     cp_async_wait<S - 1>();           // point j + 1 has landed
     if (c0 != cur0 || c1 != cur1) {
-      if (cur0 >= 0 && !(dbg & 1)) flush();
+      if (cur0 >= 0) flush();
       cur0 = c0;
       cur1 = c1;
     }
@@ -790,23 +790,12 @@ static void launch_w(const SortedPoints& sp, const ESKernel& k, const T* cs, T* 
         EFGP_CUDA(cudaMemsetAsync(mom, 0, mbytes, st));
         const double* r8 = (const double*)rec;
         const double* c8 = (const double*)cs;
-        static const int dbg = getenv("EFGP_MOM_DBG") ? atoi(getenv("EFGP_MOM_DBG")) : 0;
-        static const int stages = getenv("EFGP_MOM_STAGES") ? atoi(getenv("EFGP_MOM_STAGES")) : 6;
-#define EFGP_MOM(S_)                                                                                          \
-        if (mode == 2)                                                                                        \
-          spread2d_moment_kernel<W, 2, S_><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom, dbg);    \
-        else if (mode == 1)                                                                                   \
-          spread2d_moment_kernel<W, 1, S_><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom, dbg);    \
-        else                                                                                                  \
-          spread2d_moment_kernel<W, 0, S_><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom, dbg);
-        if (stages >= 12 && mode == 0) {
-          spread2d_moment_kernel<W, 0, 12><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom, dbg);
-        } else if (stages >= 8) {
-          EFGP_MOM(8)
-        } else {
-          EFGP_MOM(6)
-        }
-#undef EFGP_MOM
+        if (mode == 2)
+          spread2d_moment_kernel<W, 2, kRingStages><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom);
+        else if (mode == 1)
+          spread2d_moment_kernel<W, 1, kRingStages><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom);
+        else
+          spread2d_moment_kernel<W, 0, kRingStages><<<nt, kTileThreads, 0, st>>>(r8, c8, sp.P, nf0, nf1, mom);
         stg.add_launches(1);
         stg.reset();      // the per-cell transform is its own line in the stage report
         {

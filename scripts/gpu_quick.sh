@@ -1,6 +1,5 @@
 #!/bin/bash
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
-O=gpurun_out/final
-mkdir -p $O
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:"efgp::|regular_fft|vector_fft|cub::" -c 900 --csv --log-file $O/ncu_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-parity --no-e2e --no-f32 > $O/ncu_launches.out 2>&1; echo "rc=$?"
-tail -c 300 $O/ncu_launches.out
+mkdir -p gpurun_out/q2
+timeout 900 python -m pytest tests/test_nccl_sharding_gpu.py tests/test_probe_sharding_gpu.py -q -m gpu --timeout=600 > gpurun_out/q2/pytest.log 2>&1
+echo "pytest rc=$?"; grep -E "^E  |passed|failed" gpurun_out/q2/pytest.log | head

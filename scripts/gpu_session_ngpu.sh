@@ -6,7 +6,7 @@ O=gpurun_out/g$N
 mkdir -p $O
 nvidia-smi -L > $O/gpus.txt
 TR="python -m torch.distributed.run --nnodes=1 --master-addr 127.0.0.1"
-if [ "$N" = "2" ]; then
+if [ "$N" -ge 2 ]; then
   echo "== NCCL sharding tests"; date
   timeout 900 python -m pytest tests/test_nccl_sharding_gpu.py tests/test_probe_sharding_gpu.py -q -m gpu --timeout=600 > $O/pytest.log 2>&1
   echo "pytest rc=$?"; tail -4 $O/pytest.log

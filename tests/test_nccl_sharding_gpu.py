@@ -2,8 +2,8 @@
 `gpurun --gpus 2 -- python -m pytest tests/test_nccl_sharding_gpu.py`):
 
   * points sharded (opts["shard_points"]): rank r holds a slice of ONE seeded data set; the all-reduced system must
-    give every rank the beta one rank computes from all points (1e-10), and the sharded means must be the slices of
-    the one-rank mean;
+    give every rank the system one rank builds from all points (1e-12) and its beta up to what fp64 CG can attain,
+    and the sharded means must be the slices of the one-rank mean (1e-8);
   * probes sharded (opts["shard_probes"]): the NCCL variant of tests/test_probe_sharding_gpu.py.
 """
 import os
@@ -56,7 +56,8 @@ def _worker(rank, world, port, out_dir, mode):
                           opts={"cg_tolerance": 1e-12, "shard_points": world > 1}, estimate_params=False)
         mean, _ = m.predict(xs, return_variance=False)
         torch.save({"beta": m._beta.detach().cpu(), "mean": mean.detach().cpu(), "lo": lo, "hi": hi,
-                    "mtot": m.last_fit_stats["mtot"]}, os.path.join(out_dir, f"{mode}_w{world}_r{rank}.pt"))
+                    "mtot": m.last_fit_stats["mtot"], "system": m._fit_buffers[0].detach().cpu()},
+                   os.path.join(out_dir, f"{mode}_w{world}_r{rank}.pt"))
     else:
         m = efgpnd.EFGPND(x.to(dev), y.to(dev), kern, sigmasq=1.0, eps=1e-4, opts={"shard_probes": True},
                           estimate_params=False)
@@ -80,11 +81,18 @@ def test_point_sharded_beta_equals_one_rank_beta(tmp_path):
     for r in range(2):
         two = torch.load(os.path.join(str(tmp_path), f"points_w2_r{r}.pt"))
         assert two["mtot"] == one["mtot"]
+        # the all-reduced system [F^*1 ; ws F^*y] IS the one-rank system (rounding of a different summation order)
+        rs = float((two["system"] - one["system"]).norm() / one["system"].norm())
+        assert rs < 1e-12, rs
+        # beta: two CG runs on systems equal to 1e-15 end at the accuracy fp64 CG can attain, ~ cond(A) * 1e-16 on
+        # the residual (here N ws^2 / sigma^2 ~ 1e4: both runs stall near 1e-11 before the 1e-12 request), i.e.
+        # cond(A) * 1e-11 ~ 1e-7 on beta itself (measured 7.8e-8); the directions that carry this difference have small
+        # ws and barely reach the posterior mean, which is the quantity the model returns
         rb = float((two["beta"] - one["beta"]).norm() / one["beta"].norm())
-        assert rb < 1e-9, rb
+        assert rb < 1e-6, rb
         ref = one["mean"][two["lo"]:two["hi"]]
         rm = float((two["mean"] - ref).norm() / ref.norm())
-        assert rm < 1e-9, rm
+        assert rm < 1e-8, rm
 
 
 @needs2
