@@ -383,15 +383,16 @@ static double transform_cost(int dim, double npts, int W, double cells) {
   return npts * (foot + horner) + 200.0 * cells;
 }
 
-// Fine grid of a transform that builds its OWN sorted set: EFGP grids are tiny next to N, so a larger upsampling
-// factor (narrower kernel: fewer FMAs per point) is nearly free -- e.g. the Toeplitz generator of the headline
-// solve (141^2 modes, eps 6e-8, 1e8 points) takes W = 7 on a 720^2 grid instead of W = 9 on 288^2 (measured
-// 1.6 -> see DESIGN.md section 4).  EFGP_SIGMA pins the factor (A/B measurements).
 // Point count the grid-choice cost model sees.  Point-sharded fits set Nufft::cost_npts to the GLOBAL count: every rank
 // (and a one-rank run on all the points) then picks the same fine grid and kernel, so the all-reduced sum of the shard
 // transforms is the one-rank transform to rounding, not merely to the NUFFT tolerance.
 static double cost_points(const Nufft& nu) { return (double)(nu.cost_npts > 0 ? nu.cost_npts : nu.N); }
 
+// Fine grid of a transform that builds its OWN sorted set: EFGP grids are tiny next to N, so a larger upsampling
+// factor (narrower kernel: fewer FMAs per point) is nearly free for SMALL mode counts.  For the Toeplitz generator of
+// the headline solve (141^2 modes, eps 6e-8, 1e8 points) it is not: W = 7 on a 720^2 grid saves 0.36 ms of spreading
+// and costs 0.72 ms of level-2 sort (profiles/ab_sigma_r02.md), which is what the sort term below encodes; the model
+// keeps sigma = 2 / W = 9 there.  EFGP_SIGMA pins the factor (A/B measurements).
 static double pick_sigma(const Nufft& nu, const int64_t* n, double eps, int64_t* nf_out, int* w_out) {
   static const double sigma_env = [] {
     const char* e = std::getenv("EFGP_SIGMA");
