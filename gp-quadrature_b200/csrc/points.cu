@@ -170,12 +170,17 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
                       uint32_t* __restrict__ RI) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* S = (T*)smem_raw;                                   // [NS][kSortTile]
-  uint16_t* SK = (uint16_t*)(S + NS * kSortTile);        // level-2 bin
-  uint16_t* SB = SK + kSortTile;                         // level-1 bucket
-  uint32_t* cnt = (uint32_t*)(SB + kSortTile);           // [kMaxBuckets]
+  uint32_t* SKB = (uint32_t*)(S + NS * kSortTile);       // [kSortTile] level-1 bucket | level-2 bin << 16 (one word:
+                                                         // one scattered store and one load instead of two 16-bit ones)
+  uint32_t* cnt = SKB + kSortTile;                       // [kMaxBuckets]
   uint32_t* lstart = cnt + kMaxBuckets;
   uint32_t* gstart = lstart + kMaxBuckets;
   uint32_t* SI = gstart + kMaxBuckets;                    // [kSortTile] original indices (only when RI != nullptr)
+  // per input slot (k * kL1Threads + tid): bucket | level-2 bin << 16.  Held in shared memory across the scan instead
+  // of registers: at 3 CTAs of 512 threads per SM (42 registers) they were spilled to local memory, whose reloads
+  // missed L1 (ncu round 2: 4.3e6 LDL, 1.35 GB of local-memory sectors through L2, "long scoreboard" the top stall)
+  __shared__ uint32_t slotkey[kSortTile];
+  __shared__ uint16_t slotrank[kSortTile];   // rank of the point inside its bucket within this tile
   __shared__ uint32_t wtot[kMaxBuckets / 32];
   const int tid = threadIdx.x;
   const int64_t tile = blockIdx.x;
@@ -184,20 +189,18 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
   if (tid < kMaxBuckets) cnt[tid] = 0;
   __syncthreads();
   T X[kL1Per][NS];
-  uint32_t bk[kL1Per], lr[kL1Per];
-  uint16_t k2[kL1Per];
 #pragma unroll
   for (int k = 0; k < kL1Per; ++k) {
     int64_t i = tile * kSortTile + k * kL1Threads + tid;
-    bk[k] = 0xffffffffu;
+    uint32_t sk = 0xffffffffu;
     if (i < N) {
       uint32_t key = fold_point<T, D>(x, i, p, X[k]);
       if (NS > D) X[k][D] = ypay[i];
       uint32_t b = key / g.cpb;
-      bk[k] = b;
-      k2[k] = (uint16_t)((key - b * g.cpb) / g.g);
-      lr[k] = atomicAdd(&cnt[b], 1u);
+      sk = b | (((key - b * g.cpb) / g.g) << 16);
+      slotrank[k * kL1Threads + tid] = (uint16_t)atomicAdd(&cnt[b], 1u);
     }
+    slotkey[k * kL1Threads + tid] = sk;
   }
   __syncthreads();
   uint32_t c = 0, v = 0;
@@ -221,13 +224,14 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < kL1Per; ++k) {
-    if (bk[k] != 0xffffffffu) {
+    const uint32_t sk = slotkey[k * kL1Threads + tid];
+    if (sk != 0xffffffffu) {
       int64_t i = tile * kSortTile + k * kL1Threads + tid;
-      uint32_t lp = lstart[bk[k]] + lr[k];
+      const uint32_t bkk = sk & 0xffffu;
+      uint32_t lp = lstart[bkk] + slotrank[k * kL1Threads + tid];
 #pragma unroll
       for (int a = 0; a < NS; ++a) S[a * kSortTile + lp] = X[k][a];
-      SK[lp] = k2[k];
-      SB[lp] = (uint16_t)bk[k];
+      SKB[lp] = sk;
       if (RI) SI[lp] = (uint32_t)i;
       A[i] = (uint16_t)lp;      // tile-local position in bucket-major order (< kSortTile)
     }
@@ -237,11 +241,12 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
   const int n_tile = rem < kSortTile ? (int)rem : kSortTile;
   T* R[4] = {R0, R1, R2, R3};
   for (int lp = tid; lp < n_tile; lp += kL1Threads) {
-    uint32_t b = SB[lp];
+    const uint32_t skb = SKB[lp];
+    const uint32_t b = skb & 0xffffu;
     uint32_t a = gstart[b] + ((uint32_t)lp - lstart[b]);
 #pragma unroll
     for (int d = 0; d < NS; ++d) R[d][a] = S[d * kSortTile + lp];
-    K2[a] = SK[lp];
+    K2[a] = (uint16_t)(skb >> 16);
     if (RI) RI[a] = SI[lp];
   }
 }
@@ -342,29 +347,33 @@ bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* 
   const T* R[3] = {R0, R1, R2};
   constexpr int RW = rec_words(D);
   constexpr uint32_t kNone = 0xffffffffu;
-  uint32_t q[kSortPer];
-  uint32_t oi[kSortPer];
+  // level-2 bin and original index of every input slot (k * kSortThreads + tid): in shared memory, not registers --
+  // with the 8 records (64 registers) they exceeded the 85-register budget of 3 CTAs per SM and were spilled
+  __shared__ uint32_t sq[kSortTile];
+  __shared__ uint32_t soi[kSortTile];
   T w[kSortPer][RW];
 #pragma unroll
   for (int k = 0; k < kSortPer; ++k) {
     const uint32_t a = s + k * kSortThreads + threadIdx.x;
-    q[k] = kNone;
-    oi[k] = 0;
+    uint32_t qk = kNone;
 #pragma unroll
     for (int d = 0; d < RW; ++d) w[k][d] = T(0);
     if (a < e) {
-      q[k] = K2[a];
-      if (RI) oi[k] = RI[a];
+      qk = K2[a];
+      if (RI) soi[k * kSortThreads + threadIdx.x] = RI[a];
 #pragma unroll
       for (int d = 0; d < D; ++d) w[k][d] = R[d][a];
       if (D == 2 && RY) w[k][3] = RY[a];     // payload rides in the record's spare word
     }
+    sq[k * kSortThreads + threadIdx.x] = qk;
   }
   for (int i = threadIdx.x; i < g.nbins2; i += kSortThreads) cnt[i] = 0;
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < kSortPer; ++k)
-    if (q[k] != kNone) atomicAdd(&cnt[q[k]], 1u);
+  for (int k = 0; k < kSortPer; ++k) {
+    const uint32_t qk = sq[k * kSortThreads + threadIdx.x];
+    if (qk != kNone) atomicAdd(&cnt[qk], 1u);
+  }
   __syncthreads();
   for (int i = threadIdx.x; i < g.nbins2; i += kSortThreads) {
     uint32_t c = cnt[i];
@@ -377,14 +386,15 @@ bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* 
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < kSortPer; ++k) {
-    if (q[k] == kNone) continue;
+    const uint32_t qk = sq[k * kSortThreads + threadIdx.x];
+    if (qk == kNone) continue;
     const uint32_t a = s + k * kSortThreads + threadIdx.x;
-    uint32_t r = base[q[k]] + atomicAdd(&cnt[q[k]], 1u);
+    uint32_t r = base[qk] + atomicAdd(&cnt[qk], 1u);
     int64_t slot = slot_of_rank((int64_t)r, g.P);
     *reinterpret_cast<uint32_t*>(&w[k][D]) = a;
     // 64-bit words have room for the ORIGINAL index next to the level-1 position: the regenerated Hutchinson probes
     // are a function of (seed, probe, original index), independent of the (run-dependent) order inside a cell
-    if constexpr (sizeof(T) == 8) reinterpret_cast<uint32_t*>(&w[k][D])[1] = oi[k];
+    if constexpr (sizeof(T) == 8) reinterpret_cast<uint32_t*>(&w[k][D])[1] = RI ? soi[k * kSortThreads + threadIdx.x] : 0u;
     store_record<T, RW>(rec + slot * RW, w[k]);
     B[a] = (uint32_t)slot;
   }

@@ -1,5 +1,19 @@
 #!/bin/bash
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
-mkdir -p gpurun_out/q
-timeout 900 python -m pytest tests/test_moment_spread_gpu.py -q -m gpu --timeout=600 > gpurun_out/q/pytest_mom.log 2>&1
-echo "rc=$?"; grep -E "^E  |^FAILED|passed|failed" gpurun_out/q/pytest_mom.log | head -30
+O=gpurun_out/q
+mkdir -p $O
+timeout 2400 python -m pytest tests -q -m gpu --timeout=900 > $O/pytest.log 2>&1
+grep -E "^FAILED|^E  |passed|failed" $O/pytest.log | head -20
+B="--steps 5 --warmup 3 --no-cpu-baseline --no-parity --no-e2e --no-f32"
+run() { tag=$1; shift; env "$@" timeout 300 python bench.py $B > $O/bench_$tag.json 2> $O/bench_$tag.err; }
+run base A=1
+run config4 A=1 
+B="--steps 20 --warmup 5 --npts 1.25e7 --no-cpu-baseline --no-parity --no-e2e --no-f32"
+run shard A=1
+python - <<'PY'
+import json
+for t in ["base","shard"]:
+    try:
+        d=json.load(open(f"gpurun_out/q/bench_{t}.json")); print(t, round(d["ms_per_step"],3), d["result_rms"], {k: round(v["ms_per_step"],3) for k,v in d["stages"].items() if "sort" in k})
+    except Exception as e: print(t, "ERR", e)
+PY
