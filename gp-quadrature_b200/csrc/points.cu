@@ -293,10 +293,9 @@ level2_tiles_kernel(const uint32_t* __restrict__ tileStart, int ntiles1, int nb1
   }
 }
 
-__device__ __forceinline__ bool level2_tile_range(const uint32_t* __restrict__ bucketStart,
-                                                  const uint32_t* __restrict__ tile2Base, int nb1, int& b,
-                                                  uint32_t& s, uint32_t& e) {
-  const uint32_t tile = blockIdx.x;
+__device__ __forceinline__ bool level2_tile_range_of(uint32_t tile, const uint32_t* __restrict__ bucketStart,
+                                                     const uint32_t* __restrict__ tile2Base, int nb1, int& b,
+                                                     uint32_t& s, uint32_t& e) {
   if (tile >= tile2Base[nb1]) return false;
   int lo = 0, hi = nb1;                 // last b with tile2Base[b] <= tile
   while (hi - lo > 1) {
@@ -309,22 +308,50 @@ __device__ __forceinline__ bool level2_tile_range(const uint32_t* __restrict__ b
   e = s + kSortTile < be ? s + kSortTile : be;
   return true;
 }
+__device__ __forceinline__ bool level2_tile_range(const uint32_t* __restrict__ bucketStart,
+                                                  const uint32_t* __restrict__ tile2Base, int nb1, int& b,
+                                                  uint32_t& s, uint32_t& e) {
+  return level2_tile_range_of(blockIdx.x, bucketStart, tile2Base, nb1, b, s, e);
+}
+
+// Per-(bucket, bin) point counts.  A CTA walks kHistTiles CONSECUTIVE level-2 tiles (tiles are ordered by bucket, a
+// bucket has hundreds of them) and adds its shared-memory counts to the global ones only when the bucket changes or
+// at the end: one global atomic per (CTA, non-empty bin) instead of one per (tile, non-empty bin) -- 3e7 -> 4e6 at
+// N = 1e8, which is what the one-tile version spent its 0.17 ms on (it reads 2 bytes per point).
+constexpr int kHistTiles = 16;
 
 __global__ void __launch_bounds__(kSortThreads)
 bin_hist_kernel(const uint16_t* __restrict__ K2, const uint32_t* __restrict__ bucketStart,
                 const uint32_t* __restrict__ tile2Base, SortGeom g, uint32_t* __restrict__ binCount) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint32_t* cnt = (uint32_t*)smem_raw;  // [nbins2]
-  int b;
-  uint32_t s, e;
-  if (!level2_tile_range(bucketStart, tile2Base, g.nb1, b, s, e)) return;
   for (int q = threadIdx.x; q < g.nbins2; q += kSortThreads) cnt[q] = 0;
-  __syncthreads();
-  for (uint32_t a = s + threadIdx.x; a < e; a += kSortThreads) atomicAdd(&cnt[K2[a]], 1u);
+  int cur = -1;
+  for (int k = 0; k < kHistTiles; ++k) {
+    int b;
+    uint32_t s, e;
+    const bool ok = level2_tile_range_of(blockIdx.x * kHistTiles + k, bucketStart, tile2Base, g.nb1, b, s, e);
+    if (!ok || b != cur) {                     // (uniform over the CTA) publish and clear the finished bucket
+      __syncthreads();
+      if (cur >= 0) {
+        for (int q = threadIdx.x; q < g.nbins2; q += kSortThreads) {
+          const uint32_t c = cnt[q];
+          if (c) {
+            atomicAdd(&binCount[(int64_t)cur * g.nbins2 + q], c);
+            cnt[q] = 0;
+          }
+        }
+      }
+      __syncthreads();
+      if (!ok) return;
+      cur = b;
+    }
+    for (uint32_t a = s + threadIdx.x; a < e; a += kSortThreads) atomicAdd(&cnt[K2[a]], 1u);
+  }
   __syncthreads();
   for (int q = threadIdx.x; q < g.nbins2; q += kSortThreads) {
-    uint32_t c = cnt[q];
-    if (c) atomicAdd(&binCount[(int64_t)b * g.nbins2 + q], c);
+    const uint32_t c = cnt[q];
+    if (c) atomicAdd(&binCount[(int64_t)cur * g.nbins2 + q], c);
   }
 }
 
@@ -771,8 +798,8 @@ static void build_td(SortedPoints& sp, const T* x, const T* ypay, int64_t N, con
   {
     ScopedStage stg("sort.bin_hist_kernel", st, 2, N);
     level2_tiles_kernel<<<1, kMaxBuckets, 0, st>>>(tileStart, ntiles1, g.nb1, N, bucketStart, tile2Base);
-    bin_hist_kernel<<<ntiles2_max, kSortThreads, g.nbins2 * sizeof(uint32_t), st>>>(K2, bucketStart, tile2Base, g,
-                                                                                    binCount);
+    bin_hist_kernel<<<div_up(ntiles2_max, kHistTiles), kSortThreads, g.nbins2 * sizeof(uint32_t), st>>>(
+        K2, bucketStart, tile2Base, g, binCount);
   }
   {
     ScopedStage stg("sort.scans", st, 0, 0);
