@@ -23,7 +23,7 @@
 namespace efgp {
 
 constexpr int kConvThreads = 256;
-constexpr int kConvR = 3;            // outputs per thread (sliding window of generator values)
+// outputs per thread (sliding window of generator values): template parameter kConvR in {3, 4, 6}, see cg_conv_launch
 constexpr int kConvMaxM = 6400;      // shared memory: 32 M bytes for q, p, r (+ partial sums)
 
 template <typename T>
@@ -68,7 +68,7 @@ __device__ __forceinline__ double cta_allsum(double v, double* sh) {
   return s;
 }
 
-template <typename T>
+template <typename T, int kConvR>
 __global__ void __launch_bounds__(kConvThreads) cg_conv_kernel(const ConvArgs<T> a) {
   using C = typename cplx_of<T>::type;
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
@@ -252,18 +252,38 @@ bool cg_conv_launch(Toeplitz& t, const T* ws, const T* minv, void* x, const void
   a.chunks = std::max(1, std::min(n1, sms / rows));
   a.cper = (n1 + a.chunks - 1) / a.chunks;
   a.chunks = (n1 + a.cper - 1) / a.cper;
-  a.L = (a.cper + kConvR - 1) / kConvR;
-  a.G = std::min(kConvThreads / a.L, 2 * n0);
+  // outputs per thread: fatter threads amortise the q loads and the window shifts over more MACs (measured at 71^2,
+  // cper = 18: R = 3 / 4 / 6 / 9 / 12 / 18 -> 0.206 / 0.203 / 0.178 / 0.206 / 0.244 / 0.214 ms for 10 iterations); among
+  // {3, 4, 6} take the one that wastes the fewest lanes on the column chunk, the larger one on a tie
+  static const int r_env = std::getenv("EFGP_CG_CONV_R") ? std::atoi(std::getenv("EFGP_CG_CONV_R")) : 0;
+  int kConvR = 3;
+  if (r_env == 3 || r_env == 4 || r_env == 6) {
+    kConvR = r_env;
+  } else {
+    int best_waste = 1 << 30;
+    for (int r : {3, 4, 6}) {
+      const int waste = (a.cper + r - 1) / r * r - a.cper;
+      if (waste <= best_waste) {
+        best_waste = waste;
+        kConvR = r;
+      }
+    }
+  }
   if (a.cper > kConvThreads) return false;
   const int ctas = rows * a.chunks;
-  const size_t smem = sizeof(C) * ((size_t)M + 2 * (size_t)a.H + (size_t)a.G * a.cper);
-  static size_t attr_set = 0;
-  if (smem > attr_set) {
-    EFGP_CUDA(cudaFuncSetAttribute(cg_conv_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = smem;
+  size_t smem = 0;
+  for (int attempt = 0; attempt < 2; ++attempt) {        // more lane groups mean more partial sums: fall back to R = 3
+    a.L = (a.cper + kConvR - 1) / kConvR;
+    a.G = std::min(kConvThreads / a.L, 2 * n0);
+    smem = sizeof(C) * ((size_t)M + 2 * (size_t)a.H + (size_t)a.G * a.cper);
+    if (smem <= 220 * 1024 || kConvR == 3) break;
+    kConvR = 3;
   }
+  void* fn = kConvR == 6 ? (void*)cg_conv_kernel<T, 6> : (kConvR == 4 ? (void*)cg_conv_kernel<T, 4> : (void*)cg_conv_kernel<T, 3>);
+  if (smem > 220 * 1024) return false;
+  EFGP_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  EFGP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cg_conv_kernel<T>, kConvThreads, smem));
+  EFGP_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kConvThreads, smem));
   if (per_sm < 1 || ctas > per_sm * sms) return false;
   a.v = (const C*)t.v_raw;
   a.ws = ws;
@@ -282,7 +302,7 @@ bool cg_conv_launch(Toeplitz& t, const T* ws, const T* minv, void* x, const void
   a.early = early;
   a.max_iter = max_iter;
   void* args[] = {(void*)&a};
-  EFGP_CUDA(cudaLaunchCooperativeKernel((void*)cg_conv_kernel<T>, dim3(ctas), dim3(kConvThreads), args, smem, st));
+  EFGP_CUDA(cudaLaunchCooperativeKernel(fn, dim3(ctas), dim3(kConvThreads), args, smem, st));
   return true;
 }
 
