@@ -62,11 +62,32 @@ struct FoldParams {
 
 struct SortGeom {
   uint32_t cpb;     // cells per level-1 bucket (contiguous range of flattened cell indices)
+  uint32_t cpb_inv; // floor(2^32 / cpb) (0 for cpb == 1), g_inv likewise: the per-point divisions by these run-time
+  uint32_t g_inv;   // constants are a multiply-high and one fix-up instead of ~20-instruction 32-bit divisions
+  uint32_t P_inv, tile_inv;   // the same for P and for the tile length kTileThreads * P (slot_of_rank)
   uint32_t g;       // cells per level-2 bin (1 = exact cell sort)
   int nb1;          // level-1 buckets (<= kMaxBuckets)
   int nbins2;       // level-2 bins per bucket (<= kMaxBins2)
   int P;            // points per thread of the tile-transposed layout (any value in 1..kMaxP)
 };
+
+// n / d for a run-time d with inv = floor(2^32 / d) (inv == 0 means d == 1): the multiply-high underestimates the
+// quotient by at most one for every 32-bit n, one comparison fixes it.  Exact.
+__device__ __forceinline__ uint32_t fast_div(uint32_t n, uint32_t d, uint32_t inv) {
+  if (inv == 0) return n;
+  uint32_t q = __umulhi(n, inv);
+  if (n - q * d >= d) ++q;
+  return q;
+}
+
+// slot_of_rank with the divisions by the tile length and by P done through their reciprocals (SortGeom)
+__device__ __forceinline__ int64_t slot_of_rank_fast(uint32_t r32, uint32_t P, uint32_t P_inv, uint32_t tile_inv) {
+  const uint32_t tile_len = (uint32_t)kTileThreads * P;
+  const uint32_t tile = fast_div(r32, tile_len, tile_inv);
+  const uint32_t rr = r32 - tile * tile_len;
+  const uint32_t t = fast_div(rr, P, P_inv), j = rr - t * P;
+  return (int64_t)tile * tile_len + (int64_t)j * kTileThreads + t;
+}
 
 constexpr int kMaxBuckets = 256;
 constexpr int kDefaultBuckets = 128;
@@ -153,7 +174,7 @@ bucket_hist_kernel(const T* __restrict__ x, int64_t N, FoldParams<T> p, SortGeom
     if (i < N) {
       T X[D];
       uint32_t key = fold_point<T, D>(x, i, p, X);
-      atomicAdd(&cnt[key / g.cpb], 1u);
+      atomicAdd(&cnt[fast_div(key, g.cpb, g.cpb_inv)], 1u);
     }
   }
   __syncthreads();
@@ -196,8 +217,8 @@ bucket_scatter_kernel(const T* __restrict__ x, const T* __restrict__ ypay, int64
     if (i < N) {
       uint32_t key = fold_point<T, D>(x, i, p, X[k]);
       if (NS > D) X[k][D] = ypay[i];
-      uint32_t b = key / g.cpb;
-      sk = b | (((key - b * g.cpb) / g.g) << 16);
+      uint32_t b = fast_div(key, g.cpb, g.cpb_inv);
+      sk = b | (fast_div(key - b * g.cpb, g.g, g.g_inv) << 16);
       slotrank[k * kL1Threads + tid] = (uint16_t)atomicAdd(&cnt[b], 1u);
     }
     slotkey[k * kL1Threads + tid] = sk;
@@ -417,7 +438,7 @@ bin_scatter_kernel(const T* __restrict__ R0, const T* __restrict__ R1, const T* 
     if (qk == kNone) continue;
     const uint32_t a = s + k * kSortThreads + threadIdx.x;
     uint32_t r = base[qk] + atomicAdd(&cnt[qk], 1u);
-    int64_t slot = slot_of_rank((int64_t)r, g.P);
+    int64_t slot = slot_of_rank_fast(r, (uint32_t)g.P, g.P_inv, g.tile_inv);
     *reinterpret_cast<uint32_t*>(&w[k][D]) = a;
     // 64-bit words have room for the ORIGINAL index next to the level-1 position: the regenerated Hutchinson probes
     // are a function of (seed, probe, original index), independent of the (run-dependent) order inside a cell
@@ -884,7 +905,11 @@ static void build_t(SortedPoints& sp, const T* x, const T* ypay, int64_t N, int 
     }
   }
   g.nbins2 = (int)((g.cpb + g.g - 1) / g.g);
+  g.cpb_inv = g.cpb > 1 ? (uint32_t)((1ull << 32) / g.cpb) : 0u;
+  g.g_inv = g.g > 1 ? (uint32_t)((1ull << 32) / g.g) : 0u;
   g.P = sp.P;
+  g.P_inv = sp.P > 1 ? (uint32_t)((1ull << 32) / (uint32_t)sp.P) : 0u;
+  g.tile_inv = (uint32_t)((1ull << 32) / ((uint32_t)kTileThreads * (uint32_t)sp.P));
   if (dim == 1) build_td<T, 1>(sp, x, ypay, N, p, g, st, carry);
   if (dim == 2) build_td<T, 2>(sp, x, ypay, N, p, g, st, carry);
   if (dim == 3) build_td<T, 3>(sp, x, ypay, N, p, g, st, carry);
