@@ -119,6 +119,9 @@ def shard_bounds(n_total, world, rank):
 # identity AND version counter (any in-place write changes the key): the one host synchronisation of a fit -- every
 # grid size depends on L -- is paid once per data set, not once per hyperparameter step on the same data.
 _BBOX_CACHE: "OrderedDict[tuple, float]" = OrderedDict()
+# Grid size of the last fit with the same (dimension, dtype, eps, device): a guess that lets the
+# fused fit allocate its buffers while the bounding box is still being reduced (checked against the real value).
+_MTOT_HINT: dict = {}
 
 
 def _fit_domain_length(x, group, kernel, eps, use_cache=True):
@@ -164,19 +167,23 @@ def _shared_plan(x, h, xcen):
     if x.ndim == 1:
         x = x[:, None]
     xc = _xcen_tuple(xcen, x.shape[1])
+    # h = None: "the spacing is not known yet" (the fused fit fetches the handle while the bounding box is still being
+    # reduced and calls plan.ensure(h) afterwards): a cached handle is returned untouched, a new one gets a placeholder
+    h_new = 1.0 if h is None else float(h)
     if not x.is_contiguous():
         # the plan would own a contiguous COPY while the key names the caller's storage: do not cache
-        return _ops.NufftPlan(x, float(h), xc)
+        return _ops.NufftPlan(x, h_new, xc)
     key = (x.data_ptr(), tuple(x.shape), x.dtype, x.device, x._version)
     plan = _PLAN_CACHE.get(key)
     if plan is None:
-        plan = _ops.NufftPlan(x, float(h), xc)
+        plan = _ops.NufftPlan(x, h_new, xc)
         _PLAN_CACHE[key] = plan
         while len(_PLAN_CACHE) > _PLAN_CACHE_SIZE:
             _PLAN_CACHE.popitem(last=False)
     else:
         _PLAN_CACHE.move_to_end(key)
-        plan.ensure(h, xc)
+        if h is not None:
+            plan.ensure(h, xc)
     return plan
 
 
@@ -1030,36 +1037,74 @@ class EFGPND(nn.Module):
         self.__dict__["_ws_val"] = v
 
     def _fit_fused(self, x, y, now, s2, nufft_eps, group, fam):
-        """The whole fit as two library calls (efgp_bbox_async, efgp_fit): see csrc/fit.cu."""
+        """The whole fit as two library calls (efgp_bbox_async, efgp_fit): see csrc/fit.cu.
+
+        The bounding-box read-back is the one host synchronisation of a cold fit and the GPU idles from the end of
+        that reduction until the first sort kernel is launched, so everything the host can do WITHOUT L is done
+        while the reduction runs: the two truncation bisections, the library handle of the points, and -- on the
+        guess that the grid has the size it had the last time the same kernel, tolerance and precision were fitted
+        (_MTOT_HINT) -- the output buffers and the zero start vector.  After the read-back only h and mtot are
+        computed (the arithmetic of get_xis(use_integral=True), utils/kernels.py:99-104), the buffers are re-made if
+        the guess was wrong, and efgp_fit is called."""
         device, rdtype = x.device, x.dtype
         cdtype = _cmplx(rdtype)
         N, d = x.shape
         if group is not None:
             _ops.ensure_comm(group)
-        L, bounds = _fit_domain_length(x, group, self.kernel, self.eps, self.opts.get("cache_bbox", True))
+        use_cache = self.opts.get("cache_bbox", True)
+        bkey = (x.data_ptr(), tuple(x.shape), x.dtype, x.device, x._version, 0 if group is None else id(group))
+        L = _BBOX_CACHE.get(bkey) if use_cache else None
+        pending = None
+        if L is None:
+            pending = _ops.bbox_async(x, sharded=group is not None)          # enqueued; read below
+        Ltime, Lfreq = truncation_bounds(self.kernel, self.eps)              # host bisections, L-independent
+        family, c, a, b, p = fam
+        precond = bool(self.opts.get("mean_cg_preconditioner", True))
+        prev = self._beta
+        hkey = (d, rdtype, float(self.eps), device)      # coarse on purpose: neighbouring hyper-parameters share a size
+
+        def make_buffers(mtot):
+            M, Lg = mtot ** d, (2 * (mtot - 1) + 1) ** d
+            # one allocation: [vr (Lg + M) | beta (M) | ws, minv as the real view of M more complex entries]
+            buf = torch.empty(Lg + 3 * M, device=device, dtype=cdtype)
+            vr, beta = buf[:Lg + M], buf[Lg + M:Lg + 2 * M]
+            wm = torch.view_as_real(buf[Lg + 2 * M:]).reshape(-1)
+            warm = bool(self.opts.get("mean_cg_warm_start", True)) and prev is not None and prev.numel() == M
+            if warm:
+                beta.copy_(prev.to(device=device, dtype=cdtype).reshape(M))
+            else:
+                beta.zero_()
+            return mtot, M, Lg, vr, beta, wm[:M], (wm[M:2 * M] if precond else None), warm
+
+        plan = _shared_plan(x, None, [0.0] * d)                              # (h is set below)
+        hint = _MTOT_HINT.get(hkey)
+        bufs = make_buffers(hint) if hint is not None else None
+        if pending is not None:
+            ext, ev = pending
+            ev.synchronize()
+            e = ext.tolist()
+            L = max(e[k] + e[d + k] for k in range(d))
+            if use_cache:
+                _BBOX_CACHE[bkey] = L
+                while len(_BBOX_CACHE) > 8:
+                    _BBOX_CACHE.popitem(last=False)
         if L <= 1e-9:
             L = 1.0
-        _, h_float, mtot = get_xis(kernel_obj=self.kernel, eps=self.eps, L=L, use_integral=True, l2scaled=False,
-                                   bounds=bounds)
-        M, lg = mtot ** d, 2 * (mtot - 1) + 1
-        Lg = lg ** d
-        precond = bool(self.opts.get("mean_cg_preconditioner", True))
-        ws_r = torch.empty(M, device=device, dtype=rdtype)
-        vr = torch.empty(Lg + M, device=device, dtype=cdtype)
-        minv = torch.empty(M, device=device, dtype=rdtype) if precond else None
-        prev = self._beta
-        warm = bool(self.opts.get("mean_cg_warm_start", True)) and prev is not None and prev.numel() == M
-        beta = prev.to(device=device, dtype=cdtype).reshape(M).clone() if warm else \
-            torch.zeros(M, device=device, dtype=cdtype)
+        h_float = 1 / (L + Ltime)
+        mtot = 2 * math.ceil(Lfreq / h_float) + 1
+        if bufs is None or bufs[0] != mtot:
+            bufs = make_buffers(mtot)
+        _MTOT_HINT[hkey] = mtot
+        _, M, Lg, vr, beta, ws_r, minv, warm = bufs
+        lg = 2 * (mtot - 1) + 1
         # h^d in the model's dtype, as the reference's torch.tensor(h, dtype=rdtype) ** d (efgpnd.py:763-780)
         hd = h_float ** d if rdtype == torch.float64 else float(torch.tensor(h_float, dtype=rdtype) ** d)
-        family, c, a, b, p = fam
         max_iter = 2 * M
         args = _ops._lib.FitArgs(int(family), float(c), float(a), float(b), float(p), float(h_float), float(hd), int(mtot),
                                  float(s2), float(nufft_eps), 6e-8, float(self.opts.get("cg_tolerance", 1e-4)),
                                  int(max_iter), 1 if precond else 0, 1 if _TOEPLITZ_POW2 else 0,
                                  1 if group is not None else 0, 1 if warm else 0)
-        plan = _shared_plan(x, h_float, [0.0] * d)
+        plan.ensure(h_float, (0.0,) * d)
         lazy = _ops.LazyIters(device, max_iter, False, True)
         handle = _ops.fit(plan, y, args, ws_r, vr, minv, beta, lazy)
         v_kernel = vr[:Lg].view((lg,) * d)
