@@ -1076,9 +1076,20 @@ class EFGPND(nn.Module):
                 beta.zero_()
             return mtot, M, Lg, vr, beta, wm[:M], (wm[M:2 * M] if precond else None), warm
 
-        plan = _shared_plan(x, None, [0.0] * d)                              # (h is set below)
+        plan = _shared_plan(x, None, [0.0] * d)                              # (efgp_fit re-scales the handle to h)
+        if plan.xcen != (0.0,) * d:
+            plan.ensure(plan.h, (0.0,) * d)
         hint = _MTOT_HINT.get(hkey)
         bufs = make_buffers(hint) if hint is not None else None
+        cg_tol = float(self.opts.get("cg_tolerance", 1e-4))
+
+        def make_args(mtot, M, warm):        # h, hd are filled in once L is known
+            return _ops._lib.FitArgs(int(family), float(c), float(a), float(b), float(p), 0.0, 0.0, int(mtot),
+                                     float(s2), float(nufft_eps), 6e-8, cg_tol, int(2 * M), 1 if precond else 0,
+                                     1 if _TOEPLITZ_POW2 else 0, 1 if group is not None else 0, 1 if warm else 0)
+
+        args = make_args(bufs[0], bufs[1], bufs[7]) if bufs is not None else None
+        lazy = _ops.LazyIters(device, 2 * bufs[1], False, True) if bufs is not None else None
         if pending is not None:
             ext, ev = pending
             ev.synchronize()
@@ -1094,18 +1105,16 @@ class EFGPND(nn.Module):
         mtot = 2 * math.ceil(Lfreq / h_float) + 1
         if bufs is None or bufs[0] != mtot:
             bufs = make_buffers(mtot)
+            args = make_args(bufs[0], bufs[1], bufs[7])
+            if lazy is not None:
+                lazy.set(0)                  # (releases the ring slot of the unused counter)
+            lazy = _ops.LazyIters(device, 2 * bufs[1], False, True)
         _MTOT_HINT[hkey] = mtot
         _, M, Lg, vr, beta, ws_r, minv, warm = bufs
         lg = 2 * (mtot - 1) + 1
         # h^d in the model's dtype, as the reference's torch.tensor(h, dtype=rdtype) ** d (efgpnd.py:763-780)
-        hd = h_float ** d if rdtype == torch.float64 else float(torch.tensor(h_float, dtype=rdtype) ** d)
-        max_iter = 2 * M
-        args = _ops._lib.FitArgs(int(family), float(c), float(a), float(b), float(p), float(h_float), float(hd), int(mtot),
-                                 float(s2), float(nufft_eps), 6e-8, float(self.opts.get("cg_tolerance", 1e-4)),
-                                 int(max_iter), 1 if precond else 0, 1 if _TOEPLITZ_POW2 else 0,
-                                 1 if group is not None else 0, 1 if warm else 0)
-        plan.ensure(h_float, (0.0,) * d)
-        lazy = _ops.LazyIters(device, max_iter, False, True)
+        args.h = h_float
+        args.hd = h_float ** d if rdtype == torch.float64 else float(torch.tensor(h_float, dtype=rdtype) ** d)
         handle = _ops.fit(plan, y, args, ws_r, vr, minv, beta, lazy)
         v_kernel = vr[:Lg].view((lg,) * d)
         toeplitz = ToeplitzND(v_kernel, force_pow2=_TOEPLITZ_POW2,
