@@ -59,6 +59,9 @@ def _scalar_bound(eps, f):
     return g.find_truncation_bound()
 
 
+_BOUNDS_MEMO: dict = {}
+
+
 def truncation_bounds(kernel_obj, eps, dtype=torch.float64, trunc_eps=None):
     """(Ltime, Lfreq): the eps-supports of k(r) and of |r|^(d-1) S(r)/S(0) (utils/kernels.py:91-104).  They do
     not depend on the domain size L, so a caller can run the two bisections while the device still reduces
@@ -67,10 +70,26 @@ def truncation_bounds(kernel_obj, eps, dtype=torch.float64, trunc_eps=None):
     if trunc_eps is None:
         trunc_eps = eps
     if hasattr(kernel_obj, "_scalar_closures"):
+        # the two bisections are ~120 Python-level evaluations of the kernel (~60 us): a pure function of the kernel's
+        # closed-form parameters, remembered for repeated fits with the same hyper-parameters (the shard-size step of a
+        # multi-GPU fit is short enough for this host time to show)
+        key = None
+        if hasattr(kernel_obj, "_spectral_family"):
+            try:
+                key = (type(kernel_obj).__name__, dim, float(eps), float(trunc_eps),
+                       tuple(float(v) for v in kernel_obj._spectral_family()))
+            except Exception:
+                key = None
+        if key is not None and key in _BOUNDS_MEMO:
+            return _BOUNDS_MEMO[key]
         kf, sf = kernel_obj._scalar_closures()
         Ltime = _scalar_bound(eps, kf)
         s0 = sf(0.0)
         Lfreq = _scalar_bound(trunc_eps, lambda r: abs(r ** (dim - 1)) * sf(r) / s0)
+        if key is not None:
+            if len(_BOUNDS_MEMO) >= 64:
+                _BOUNDS_MEMO.clear()
+            _BOUNDS_MEMO[key] = (Ltime, Lfreq)
     else:  # any object with tensor-valued kernel / spectral_density, exactly as the reference does it
         Ltime = GetTruncationBound(eps, kernel_obj.kernel, dtype=dtype).find_truncation_bound()
         zero = torch.tensor(0, device="cpu", dtype=dtype)
